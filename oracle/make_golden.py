@@ -1,0 +1,187 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference.  TEST INFRASTRUCTURE.
+
+Run in the build container (where /root/reference exists):
+
+    python oracle/make_golden.py
+
+The reference is imported from /root/reference (never copied); every case is
+seeded, so re-running reproduces the committed files.  Two labelled shims, both
+in this harness only:
+  * cheby ViT: the reference crashes at model.py:150 because ChebyKANLayer
+    returns 2-D; the harness wraps linear_mapper so its output is reshaped to
+    (B, P^2, d).
+  * fourier: model.py:74 passes a wrong kwarg; fourier is layer-level only.
+The KAN-MLP extension case replaces ``ff`` of a reference TransformerBlock by
+two reference KANLinear modules.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+REF = "/root/reference"
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def save_case(name, module, x, extra=None, out_fn=None):
+    """Run module fwd+bwd on x with a seeded upstream grad; dump everything."""
+    x = x.clone().requires_grad_(True)
+    y = module(x) if out_fn is None else out_fn(module, x)
+    g = torch.Generator().manual_seed(1234)
+    dy = torch.randn(y.shape, generator=g)
+    module.zero_grad()
+    y.backward(dy)
+    rec = {"x": _np(x), "dy": _np(dy), "y": _np(y), "gx": _np(x.grad)}
+    for k, v in module.state_dict().items():
+        rec["sd/" + k] = _np(v)
+    for k, p in module.named_parameters():
+        if p.grad is not None:
+            rec["g/" + k] = _np(p.grad)
+    # float64 ground truth of the forward (settles summation-order disputes)
+    m64 = module.double()
+    with torch.no_grad():
+        y64 = m64(x.detach().double()) if out_fn is None else out_fn(m64, x.detach().double())
+    rec["y64"] = _np(y64)
+    module.float()
+    if extra:
+        rec.update(extra)
+    os.makedirs(OUT, exist_ok=True)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
+    print(f"{name}: y{tuple(y.shape)} {sum(v.nbytes for v in rec.values())/1024:.1f} KiB")
+
+
+def main():
+    sys.path.insert(0, REF)
+    import model as ref_model  # noqa
+    from attention import MSA  # noqa
+    from models.cheby import ChebyKANLayer  # noqa
+    from models.effkan import KANLinear  # noqa
+    from models.fastkan import FastKANLayer  # noqa
+    from models.nfkan import NaiveFourierKANLayer  # noqa
+    from models.sinekan import SineKANLayer  # noqa
+
+    # ---------------- layers ----------------
+    def xin(shape, seed, scale=1.0):
+        return torch.randn(shape, generator=torch.Generator().manual_seed(seed)) * scale
+
+    torch.manual_seed(0)
+    m = KANLinear(16, 24)
+    x = xin((3, 5, 16), 1, 1.3)
+    # exact knots, out-of-span values and the span edges (effkan.py:115 half-open test)
+    x[0, 0, :8] = torch.tensor([-2.2, -1.0, -0.2, 0.6, 2.2, 2.5, -3.0, 1.0])
+    save_case("layer_effkan", m, x)
+
+    torch.manual_seed(1)
+    m = KANLinear(8, 12, grid_size=10, spline_order=2, enable_standalone_scale_spline=False)
+    with torch.no_grad():  # non-uniform, per-feature knots (what update_grid would leave behind)
+        jitter = torch.rand(m.grid.shape, generator=torch.Generator().manual_seed(5)) * 0.05
+        m.grid.add_(jitter.cumsum(1))
+    save_case("layer_effkan_g10k2_nonuniform", m, xin((7, 8), 2),
+              extra={"spline_order": np.int64(2)})
+
+    torch.manual_seed(2)
+    save_case("layer_cheby", ChebyKANLayer(16, 24, 4), xin((3, 5, 16), 3, 1.5))
+    torch.manual_seed(12)
+    save_case("layer_cheby_deg7", ChebyKANLayer(8, 8, 7), xin((9, 8), 13))
+
+    torch.manual_seed(3)
+    m = FastKANLayer(16, 24)
+    with torch.no_grad():
+        m.layernorm.weight.add_(0.1 * torch.randn(16))
+        m.layernorm.bias.add_(0.1 * torch.randn(16))
+    save_case("layer_fastkan", m, xin((3, 5, 16), 4))
+
+    torch.manual_seed(4)
+    save_case("layer_sine", SineKANLayer(16, 24), xin((3, 5, 16), 5))
+    torch.manual_seed(5)
+    save_case("layer_sine_g4", SineKANLayer(8, 8, grid_size=4), xin((6, 8), 6))
+
+    torch.manual_seed(6)
+    save_case("layer_fourier", NaiveFourierKANLayer(16, 24, 5), xin((3, 5, 16), 7))
+
+    # ---------------- MSA / block ----------------
+    for kind in ("vanilla", "efficientkan", "cheby", "fast", "sine"):
+        torch.manual_seed(20)
+        save_case(f"msa_{kind}", MSA(16, n_heads=2, type=kind), xin((3, 5, 16), 21))
+
+    torch.manual_seed(30)
+    blk = ref_model.TransformerBlock(16, 2, feedforward_dim=64, attn_type="efficientkan")
+    save_case("block_efficientkan", blk, xin((3, 5, 16), 31))
+
+    torch.manual_seed(32)
+    blk = ref_model.TransformerBlock(16, 2, feedforward_dim=64, attn_type="efficientkan")
+    blk.ff = torch.nn.Sequential(KANLinear(16, 64), KANLinear(64, 16))  # KAN-MLP extension
+    save_case("block_efficientkan_kanmlp", blk, xin((3, 5, 16), 33))
+
+    # ---------------- ViT ----------------
+    class ChebyShim(torch.nn.Module):  # labelled shim, harness only
+        def __init__(self, inner):
+            super().__init__()
+            self.inner = inner
+
+        def forward(self, patches):
+            return self.inner(patches).view(patches.shape[0], patches.shape[1], -1)
+
+    for kind in ("vanilla", "efficientkan", "fast", "sine", "cheby"):
+        torch.manual_seed(40)
+        if kind == "cheby":
+            vit = ref_model.VisionTransformer((1, 8, 8), n_patches=2, n_blocks=2, d_hidden=16,
+                                              n_heads=2, out_d=10, type=kind)
+            inner = vit.linear_mapper
+            vit.linear_mapper = ChebyShim(inner)
+            sd_fix = lambda k: k.replace("linear_mapper.inner.", "linear_mapper.")  # noqa
+        else:
+            vit = ref_model.VisionTransformer((1, 8, 8), n_patches=2, n_blocks=2, d_hidden=16,
+                                              n_heads=2, out_d=10, type=kind)
+            sd_fix = lambda k: k  # noqa
+        x = xin((3, 1, 8, 8), 41)
+        x = x.clone().requires_grad_(True)
+        y = vit(x)
+        dy = torch.randn(y.shape, generator=torch.Generator().manual_seed(1234))
+        y.backward(dy)
+        rec = {"x": _np(x), "dy": _np(dy), "y": _np(y), "gx": _np(x.grad),
+               "pos_embeddings": _np(vit.pos_embeddings)}
+        for k, v in vit.state_dict().items():
+            rec["sd/" + sd_fix(k)] = _np(v)
+        for k, p in vit.named_parameters():
+            if p.grad is not None:
+                rec["g/" + sd_fix(k)] = _np(p.grad)
+        np.savez_compressed(os.path.join(OUT, f"vit_{kind}.npz"), **rec)
+        print(f"vit_{kind}: y{tuple(y.shape)}")
+
+    # ---------------- bit-exact layout pieces ----------------
+    vit = ref_model.VisionTransformer((3, 32, 32), n_patches=4, n_blocks=1, d_hidden=24, n_heads=2)
+    img = xin((2, 3, 32, 32), 50)
+    vit7 = ref_model.VisionTransformer((1, 28, 28), n_patches=7, n_blocks=1, d_hidden=64, n_heads=2)
+    img7 = xin((2, 1, 28, 28), 51)
+    np.savez_compressed(
+        os.path.join(OUT, "layout.npz"),
+        img_3x32=_np(img), patches_3x32_np4=_np(vit.patchify(img, 4)),
+        img_1x28=_np(img7), patches_1x28_np7=_np(vit7.patchify(img7, 7)),
+        pos_17x24=_np(vit.pos_embeddings), pos_50x64=_np(vit7.pos_embeddings),
+    )
+    # state_dict key/shape lists for the BASELINE configs (host-logic tests)
+    import json
+    keys = {}
+    for name, args in {
+        "cfg1_efficientkan": dict(chw=(1, 28, 28), n_patches=7, n_blocks=4, d_hidden=64, n_heads=2, out_d=10, type="efficientkan"),
+        "cfg3_fast": dict(chw=(3, 32, 32), n_patches=4, n_blocks=6, d_hidden=192, n_heads=8, out_d=10, type="fast"),
+        "cfg3_sine": dict(chw=(3, 32, 32), n_patches=4, n_blocks=6, d_hidden=192, n_heads=8, out_d=10, type="sine"),
+        "cfg2_cheby": dict(chw=(1, 28, 28), n_patches=7, n_blocks=4, d_hidden=64, n_heads=2, out_d=10, type="cheby"),
+        "vanilla": dict(chw=(1, 28, 28), n_patches=7, n_blocks=2, d_hidden=64, n_heads=2, out_d=10, type="vanilla"),
+    }.items():
+        torch.manual_seed(0)
+        v = ref_model.VisionTransformer(**args)
+        keys[name] = {k: list(t.shape) for k, t in v.state_dict().items()}
+    with open(os.path.join(OUT, "state_dict_keys.json"), "w") as f:
+        json.dump(keys, f, indent=0, sort_keys=True)
+    print("done")
+
+
+if __name__ == "__main__":
+    main()

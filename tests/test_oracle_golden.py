@@ -1,0 +1,107 @@
+"""Pins oracle/kan_oracle.py to the reference's own outputs (tests/golden, made by
+oracle/make_golden.py from the unmodified /root/reference).  CPU only."""
+import pytest
+import torch
+
+from conftest import load_golden, relerr
+from oracle import kan_oracle as O
+
+TOL = 2e-6  # same fp32 arithmetic, restated; only einsum/linear summation order may differ
+
+
+def _leafify(sd):
+    return {k: (v.clone().requires_grad_(True) if v.is_floating_point() else v) for k, v in sd.items()}
+
+
+def _check(g, y, x, sd, tol=TOL, skip_nograd=()):
+    assert y.shape == g.t("y").shape
+    assert relerr(y, g.t("y")) < tol
+    y.backward(g.t("dy"))
+    assert relerr(x.grad, g.t("gx")) < 10 * tol
+    for k, ref in g.grads().items():
+        assert sd[k].grad is not None, k
+        if ref.abs().max() < 1e-6:  # analytically zero (e.g. key bias under softmax): noise only
+            assert sd[k].grad.abs().max() < 1e-6, k
+            continue
+        assert relerr(sd[k].grad, ref) < 10 * tol, k
+
+
+LAYERS = [
+    ("layer_effkan", "efficientkan"), ("layer_cheby", "cheby"), ("layer_cheby_deg7", "cheby"),
+    ("layer_fastkan", "fast"), ("layer_sine", "sine"), ("layer_sine_g4", "sine"),
+    ("layer_fourier", "fourier"),
+]
+
+
+@pytest.mark.parametrize("case,kind", LAYERS)
+def test_layer_matches_reference(case, kind):
+    g = load_golden(case)
+    sd = _leafify(g.sd())
+    x = g.t("x").requires_grad_(True)
+    y = O.layer_forward(kind, x, sd, "")
+    _check(g, y, x, sd)
+    # and the fp64 ground truth: fp32 oracle is as close to it as the reference is
+    assert relerr(y, g.t("y64")) < 1e-5
+
+
+def test_effkan_nonuniform_grid_any_order():
+    g = load_golden("layer_effkan_g10k2_nonuniform")
+    sd = _leafify(g.sd())
+    x = g.t("x").requires_grad_(True)
+    y = O.effkan_forward(x, sd["base_weight"], sd["spline_weight"], None, sd["grid"], spline_order=2)
+    _check(g, y, x, sd)
+
+
+def test_bspline_partition_of_unity_and_support():
+    grid = O.effkan_default_grid(3)
+    x = torch.linspace(-1, 1, 41)[:, None].repeat(1, 3)
+    b = O.b_splines(x, grid, 3)
+    assert torch.allclose(b.sum(-1), torch.ones(41, 3), atol=1e-6)
+    out = O.b_splines(torch.tensor([[2.2, -2.3, 5.0]]), grid, 3)
+    assert out.abs().max() == 0  # half-open span, zero outside (effkan.py:115)
+
+
+def test_default_buffers_match_reference():
+    g = load_golden("layer_effkan")
+    assert torch.equal(O.effkan_default_grid(16), g.t("sd/grid"))
+    s = load_golden("layer_sine")
+    assert torch.equal(O.sinekan_phase(16, 5), s.t("sd/phase"))
+    assert torch.equal(O.sinekan_default_freq(5), s.t("sd/freq"))
+    s4 = load_golden("layer_sine_g4")
+    assert torch.equal(O.sinekan_phase(8, 4), s4.t("sd/phase"))
+
+
+@pytest.mark.parametrize("kind", ["vanilla", "efficientkan", "cheby", "fast", "sine"])
+def test_msa_matches_reference(kind):
+    g = load_golden(f"msa_{kind}")
+    sd = _leafify(g.sd())
+    x = g.t("x").requires_grad_(True)
+    y = O.msa_forward(x, sd, "", 2, kind)
+    _check(g, y, x, sd)
+
+
+@pytest.mark.parametrize("case,kan_mlp", [("block_efficientkan", False), ("block_efficientkan_kanmlp", True)])
+def test_block_matches_reference(case, kan_mlp):
+    g = load_golden(case)
+    sd = _leafify(g.sd())
+    x = g.t("x").requires_grad_(True)
+    y = O.block_forward(x, sd, "", 2, "efficientkan", kan_mlp)
+    _check(g, y, x, sd, tol=5e-6)
+
+
+@pytest.mark.parametrize("kind", ["vanilla", "efficientkan", "fast", "sine", "cheby"])
+def test_vit_matches_reference(kind):
+    g = load_golden(f"vit_{kind}")
+    sd = _leafify(g.sd())
+    x = g.t("x").requires_grad_(True)
+    y = O.vit_forward(x, sd, n_patches=2, n_blocks=2, n_heads=2, kind=kind)
+    _check(g, y, x, sd, tol=1e-5)
+    assert torch.equal(O.positional_embeddings(5, 16), g.t("pos_embeddings"))
+
+
+def test_layout_bit_exact():
+    g = load_golden("layout")
+    assert torch.equal(O.patchify(g.t("img_3x32"), 4), g.t("patches_3x32_np4"))
+    assert torch.equal(O.patchify(g.t("img_1x28"), 7), g.t("patches_1x28_np7"))
+    assert torch.equal(O.positional_embeddings(17, 24), g.t("pos_17x24"))
+    assert torch.equal(O.positional_embeddings(50, 64), g.t("pos_50x64"))
