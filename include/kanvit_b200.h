@@ -1,0 +1,211 @@
+/* kanvit_b200.h -- C ABI of the B200-native KAN-ViT hot path (libkanvit_b200.so).
+ *
+ * The reference (akshathmangudi/KAN-ViT) has no FFI / operator layer: its hot path is
+ * the torch.nn.Module API of model.py / attention.py / models/*.py, every op a stock
+ * ATen call.  The entry points below are what a binding for that path replaces; each
+ * one cites the reference code whose arithmetic it takes over (paths are relative to
+ * the reference tree).  INTEGRATION.md shows the ctypes stub a maintainer adds.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless the
+ *     name ends in _host; all activations are row-major float32; the tensor-core
+ *     path additionally takes bf16 copies of the packed weights (made by kv_kan_pack)
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), does
+ *     no allocation and no synchronisation; the caller owns all memory
+ *   - return value: 0 on success, a negative kv_status otherwise (never aborts)
+ *   - re-entrant: no mutable global state
+ */
+#ifndef KANVIT_B200_H
+#define KANVIT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KV_ABI_VERSION 1
+
+typedef enum {
+  KV_OK = 0,
+  KV_ERR_BAD_ARG = -1,      /* null pointer / negative size */
+  KV_ERR_BAD_SHAPE = -2,    /* shape the kernels cannot serve (e.g. M > KV_MAX_M) */
+  KV_ERR_BAD_FAMILY = -3,
+  KV_ERR_ALIGNMENT = -4,    /* pointer / leading dimension not aligned for the path */
+  KV_ERR_UNSUPPORTED = -5,  /* combination not available in this precision mode */
+  KV_ERR_CUDA = -6          /* launch failed; see kv_last_cuda_error() */
+} kv_status;
+
+/* Basis family of a KAN layer:  Y[T,out] = Phi(X)[T, in*M] . Wp[out, in*M]^T (+ bias). */
+typedef enum {
+  KV_LINEAR = 0,   /* nn.Linear (model.py:25-29,68,108; attention.py:137-143): M=1, Phi=x            */
+  KV_EFFKAN = 1,   /* models/effkan.py:99-132,166-187: M = G+k (B-splines) + 1 (SiLU base)          */
+  KV_CHEBY = 2,    /* models/cheby.py:36-48:           M = degree+1, T_n(tanh x)                    */
+  KV_FASTKAN = 3,  /* models/fastkan.py:15-30,66-76:   M = num_grids (RBF of LayerNorm(x)) + 1 base */
+  KV_SINE = 4,     /* models/sinekan.py:81-91:         M = G, sin(x*freq_g + phase_{i,g})           */
+  KV_FOURIER = 5   /* models/nfkan.py:36-52:           M = 2G, cos(kx) then sin(kx), k=1..G         */
+} kv_family;
+
+#define KV_MAX_M 64          /* basis functions per input scalar                         */
+#define KV_MAX_SPLINE_ORDER 7
+#define KV_PTRS_PER_GROUP 8  /* slots of the parameter pointer table (see kv_kan_pack)   */
+
+/* flags */
+#define KV_FLAG_RELU          1u  /* forward: Y = max(Y,0) (model.py:27); backward: dY *= (act_mask>0) */
+#define KV_FLAG_NO_LAYERNORM  2u  /* fastkan time_benchmark=True (models/fastkan.py:69-70)            */
+#define KV_FLAG_NO_BASE       4u  /* fastkan use_base_update=False (models/fastkan.py:60-63)          */
+#define KV_FLAG_BF16_TC       8u  /* tcgen05 bf16 tensor-core path (fp32 accumulate) instead of fp32 SIMT */
+
+/* One KAN (or Linear) layer, or a batch of `n_groups` independent layers of equal
+ * shape applied to column slices of the same activation matrix (the per-head Q/K/V
+ * maps of MSA, attention.py:136-170,196-197).
+ *
+ *   group g reads  X[t, (g / x_share) * in_features + i]      (ldx = row stride)
+ *   group g writes Y[row(t), g * out_features + o]            (ldy = row stride)
+ *   row(t) = t                                  if rows_in == 0
+ *          = (t / rows_in) * rows_out + row_shift + t % rows_in   otherwise
+ * (the row map writes patch tokens behind the class token, model.py:148-150; `pos`,
+ *  if given, is added with row index row_shift + t % rows_in, model.py:152).
+ */
+typedef struct {
+  int32_t family;        /* kv_family */
+  int32_t T;             /* rows (all leading dims flattened) */
+  int32_t in_features;   /* per group */
+  int32_t out_features;  /* per group */
+  int32_t n_groups;      /* 1 = dense layer */
+  int32_t x_share;       /* consecutive groups sharing one input slice (3 for q,k,v); >=1 */
+  int32_t M;             /* basis functions per input incl. base branch */
+  int32_t grid_size;     /* G | degree | num_grids */
+  int32_t spline_order;  /* effkan only */
+  int32_t ldx, ldy;      /* row strides in elements */
+  int32_t rows_in, rows_out, row_shift;
+  uint32_t flags;
+  float rbf_denom;       /* fastkan: rbf.denominator (models/fastkan.py:26-27) */
+  int32_t fparam_stride; /* floats of prologue parameters per group (kv_kan_fparam_count) */
+  int32_t reserved;
+} kv_kan_desc_t;
+
+int kv_version(void);
+const char* kv_status_string(int status);
+const char* kv_last_cuda_error(void);
+
+/* Number of fp32 prologue parameters per group for a family:
+ *   effkan  in*(G+2k+1)  knot vectors `grid` (models/effkan.py:45-54)
+ *   fastkan 2*in+G       layernorm weight, bias, rbf.grid (models/fastkan.py:24-27,57)
+ *   sine    G+in*G       freq, phase (models/sinekan.py:59-75)
+ *   others  0                                                                     */
+int kv_kan_fparam_count(const kv_kan_desc_t* d);
+
+/* Gather the reference-layout parameters of n_groups modules into the packed form
+ * the kernels read.  ptr_table: device array [n_groups][KV_PTRS_PER_GROUP] of device
+ * pointers (uint64), slot meaning per family:
+ *   linear  0 weight(out,in)            1 bias(out)|0
+ *   effkan  0 base_weight(out,in)       1 spline_weight(out,in,G+k) 2 spline_scaler(out,in)|0 3 grid(in,G+2k+1)
+ *   cheby   0 cheby_coeffs(in,out,deg+1)
+ *   fastkan 0 layernorm.weight 1 layernorm.bias 2 rbf.grid 3 spline_linear.weight(out,in*G)
+ *           4 base_linear.weight|0 5 base_linear.bias|0
+ *   sine    0 amplitudes(out,in,G) 1 freq(G) 2 phase(in,G) 3 bias(out)|0
+ *   fourier 0 fouriercoeffs(2,out,in,G) 1 bias(out)|0
+ * Outputs (any may be NULL to skip): wp_f32 [g][out][in*M] (K index i*M+m, effkan's
+ * spline_scaler folded in -- models/effkan.py:166-172,180-183), wp_bf16 same layout
+ * in bf16, wpt_bf16 [g][in*M][out] bf16 (transposed, for the input-gradient GEMM),
+ * fparams [g][fparam_stride], bias [g][out] (zeros where the module has none). */
+int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32,
+                void* wp_bf16, void* wpt_bf16, float* fparams, float* bias, void* stream);
+
+/* Per-(row, slice) mean and 1/sqrt(var+eps) over `width` consecutive columns:
+ * the LayerNorm statistics of FastKANLayer.layernorm (models/fastkan.py:57,68).
+ * mean/rstd: [T][n_slices]. */
+int kv_row_stats(const float* X, int T, int ldx, int n_slices, int width, float eps,
+                 float* mean, float* rstd, void* stream);
+
+/* Forward of the layer(s): replaces KANLinear.forward (models/effkan.py:174-187),
+ * ChebyKANLayer.forward (models/cheby.py:36-48), FastKANLayer.forward
+ * (models/fastkan.py:66-76), SineKANLayer.forward (models/sinekan.py:81-91),
+ * NaiveFourierKANLayer.forward (models/nfkan.py:36-52) and F.linear.  The basis
+ * expansion is evaluated on the fly in the GEMM prologue and never stored.
+ * residual (nullable, same addressing as Y) and pos (nullable, [rows_out][n_groups*out])
+ * are added in the epilogue; mean/rstd only for fastkan. */
+int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, const void* wp_bf16,
+               const float* fparams, const float* bias, const float* mean, const float* rstd,
+               const float* residual, const float* pos, float* Y, void* stream);
+
+/* Input gradient: dX[t, slice+i] = sum_g sum_m Phi'_m(x) * (dY_g . Wp_g)[t, i*M+m]
+ * (what autograd derives from the modules above; basis recomputed, not stored).
+ * act_mask (nullable): the layer's own forward output when KV_FLAG_RELU is set.
+ * dXn (fastkan only): [T][n_groups*in] gradient w.r.t. the LayerNorm output, consumed
+ * by kv_fastkan_ln_bwd.  dfparams [g][fparam_stride] (sine: d freq accumulated with
+ * atomics, must be zeroed by the caller; others untouched).  dX is OVERWRITTEN. */
+int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
+                     const float* wp_f32, const void* wpt_bf16, const float* fparams,
+                     const float* mean, const float* rstd, float* dX, float* dXn,
+                     float* dfparams, void* stream);
+
+/* Weight gradient in packed layout: dWp[g][o][i*M+m] = sum_t dY[t,o] * Phi_m(x[t,i]),
+ * dbias[g][o] = sum_t dY[t,o] (nullable).  dWp and dbias must be ZEROED by the caller
+ * (split over row ranges, accumulated with fp32 atomics). */
+int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
+                      const float* fparams, const float* mean, const float* rstd,
+                      float* dWp, float* dbias, void* stream);
+
+/* FastKAN: LayerNorm backward of the RBF branch (models/fastkan.py:57,68):
+ * dX[t, slice+i] += LN'(dXn_g)[t,i] for every group on that slice; d layernorm.weight
+ * / bias accumulated into dfparams[g][0:in] / [in:2in] (zeroed by the caller). */
+int kv_fastkan_ln_bwd(const kv_kan_desc_t* d, const float* X, const float* dXn, const float* fparams,
+                      const float* mean, const float* rstd, float* dX, float* dfparams, void* stream);
+
+/* Scatter packed gradients back to the reference parameter layouts.  grad_table:
+ * device array [n_groups][KV_PTRS_PER_GROUP] of OUTPUT pointers with the same slot
+ * meaning as kv_kan_pack (0 = skip); ptr_table = the forward parameters (effkan
+ * needs spline_weight and spline_scaler for the product rule, models/effkan.py:166-172). */
+int kv_kan_unpack_grads(const kv_kan_desc_t* d, const float* dWp, const float* dfparams,
+                        const float* dbias, const uint64_t* ptr_table, const uint64_t* grad_table,
+                        void* stream);
+
+/* softmax(q k^T / sqrt(d_h)) v per (sample, head): attention.py:199-200, with the
+ * online-softmax / log-sum-exp bookkeeping of utils.py:137-227.
+ * qkv: [B*N][H][3][d_h] (the grouped layer's output), out: [B*N][H*d_h] (heads
+ * concatenated in order, attention.py:201), residual nullable (model.py:34),
+ * lse: [B][H][N] saved for the backward. */
+int kv_attn_fwd(const float* qkv, const float* residual, float* out, float* lse,
+                int B, int N, int H, int d_head, void* stream);
+
+/* Recompute backward (utils.py:229-295): p = exp(s - lse), ds = p * scale * (dp - D);
+ * D_i = sum_j p_ij dp_ij is recomputed in the row pass (equal to sum(do * o),
+ * utils.py:277), so the forward output is not needed.  dqkv: same layout as qkv,
+ * overwritten.  dout: [B*N][H*d_h]. */
+int kv_attn_bwd(const float* qkv, const float* dout, const float* lse, float* dqkv,
+                int B, int N, int H, int d_head, void* stream);
+
+/* nn.LayerNorm(d), eps 1e-5, affine (model.py:22,24,107).  mean/rstd [T] saved. */
+int kv_layernorm_fwd(const float* X, const float* gamma, const float* beta, float* Y,
+                     float* mean, float* rstd, int T, int d, int ldx, float eps, void* stream);
+/* dX = LN'(dY) (+ dresidual if non-null: the skip path of model.py:34,36);
+ * dgamma/dbeta accumulated with atomics (zeroed by the caller). */
+int kv_layernorm_bwd(const float* X, const float* dY, const float* gamma, const float* mean,
+                     const float* rstd, const float* dresidual, float* dX, float* dgamma,
+                     float* dbeta, int T, int d, int ldx, float eps, void* stream);
+
+/* VisionTransformer.patchify (model.py:111-126), bit-exact index map:
+ * patches[b, i*np+j, c*ph*pw + y*pw + x] = images[b, c, i*ph+y, j*pw+x]. */
+int kv_patchify(const float* images, float* patches, int B, int C, int H, int W, int n_patches,
+                void* stream);
+/* its adjoint (gradient w.r.t. the images) */
+int kv_patchify_bwd(const float* dpatches, float* dimages, int B, int C, int H, int W,
+                    int n_patches, void* stream);
+
+/* Class-token rows: tokens[b, 0, :] = v_class + pos[0] (model.py:148-152). */
+int kv_cls_rows_fwd(const float* v_class, const float* pos, float* tokens, int B, int N, int d,
+                    void* stream);
+/* d v_class = sum_b dtokens[b,0,:] */
+int kv_cls_rows_bwd(const float* dtokens, float* dv_class, int B, int N, int d, void* stream);
+
+/* Strided row gather / scatter-add used for out[:,0] (model.py:165): Y[b,:] = X[b*stride_rows,:]. */
+int kv_gather_rows(const float* X, float* Y, int B, int row_stride, int d, void* stream);
+int kv_scatter_rows(const float* dY, float* dX, int B, int row_stride, int d, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KANVIT_B200_H */
