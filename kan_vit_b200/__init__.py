@@ -1,0 +1,14 @@
+"""kan_vit_b200 -- B200-native (sm_100a) implementation of the ViKANformer hot path behind the
+reference's own nn.Module API (akshathmangudi/KAN-ViT: model.py, attention.py, models/*.py).
+
+    from kan_vit_b200.model import VisionTransformer, TransformerBlock
+    from kan_vit_b200.attention import MSA
+    from kan_vit_b200.models import KANLinear, ChebyKANLayer, FastKANLayer, SineKANLayer, NaiveFourierKANLayer
+"""
+from . import _lib  # noqa: F401
+from .attention import MSA
+from .model import TransformerBlock, VisionTransformer
+from .models import (ChebyKANLayer, FastKANLayer, KANLinear, NaiveFourierKANLayer, SineKANLayer)
+
+__all__ = ["MSA", "TransformerBlock", "VisionTransformer", "KANLinear", "ChebyKANLayer", "FastKANLayer",
+           "SineKANLayer", "NaiveFourierKANLayer"]

@@ -1,0 +1,107 @@
+"""ctypes binding of libkanvit_b200.so (the C ABI declared in include/kanvit_b200.h).
+
+There is no CPU fallback: importing the ops on a machine without the built library, or
+calling them with non-CUDA tensors, raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libkanvit_b200.so")
+
+# kv_family
+KV_LINEAR, KV_EFFKAN, KV_CHEBY, KV_FASTKAN, KV_SINE, KV_FOURIER = range(6)
+KV_MAX_M = 64
+KV_PTRS_PER_GROUP = 8
+KV_FLAG_RELU = 1
+KV_FLAG_NO_LAYERNORM = 2
+KV_FLAG_NO_BASE = 4
+KV_FLAG_BF16_TC = 8
+
+
+class KanDesc(C.Structure):
+    """kv_kan_desc_t"""
+    _fields_ = [
+        ("family", C.c_int32), ("T", C.c_int32), ("in_features", C.c_int32),
+        ("out_features", C.c_int32), ("n_groups", C.c_int32), ("x_share", C.c_int32),
+        ("M", C.c_int32), ("grid_size", C.c_int32), ("spline_order", C.c_int32),
+        ("ldx", C.c_int32), ("ldy", C.c_int32),
+        ("rows_in", C.c_int32), ("rows_out", C.c_int32), ("row_shift", C.c_int32),
+        ("flags", C.c_uint32), ("rbf_denom", C.c_float),
+        ("fparam_stride", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+_P = C.c_void_p
+_I = C.c_int
+_DP = C.POINTER(KanDesc)
+
+# name -> argtypes; every function returns int (kv_status) unless noted
+_SIGNATURES = {
+    "kv_kan_fparam_count": [_DP],
+    "kv_kan_pack": [_DP, _P, _P, _P, _P, _P, _P, _P],
+    "kv_row_stats": [_P, _I, _I, _I, _I, C.c_float, _P, _P, _P],
+    "kv_kan_fwd": [_DP] + [_P] * 11,
+    "kv_kan_bwd_input": [_DP] + [_P] * 12,
+    "kv_kan_bwd_weight": [_DP] + [_P] * 9,
+    "kv_fastkan_ln_bwd": [_DP] + [_P] * 8,
+    "kv_kan_unpack_grads": [_DP] + [_P] * 6,
+    "kv_attn_fwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
+    "kv_attn_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
+    "kv_layernorm_fwd": [_P, _P, _P, _P, _P, _P, _I, _I, _I, C.c_float, _P],
+    "kv_layernorm_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, C.c_float, _P],
+    "kv_patchify": [_P, _P, _I, _I, _I, _I, _I, _P],
+    "kv_patchify_bwd": [_P, _P, _I, _I, _I, _I, _I, _P],
+    "kv_cls_rows_fwd": [_P, _P, _P, _I, _I, _I, _P],
+    "kv_cls_rows_bwd": [_P, _P, _I, _I, _I, _P],
+    "kv_gather_rows": [_P, _P, _I, _I, _I, _P],
+    "kv_scatter_rows": [_P, _P, _I, _I, _I, _P],
+}
+EXPORTS = ["kv_version", "kv_status_string", "kv_last_cuda_error"] + list(_SIGNATURES)
+
+_lib = None
+
+
+class KanVitError(RuntimeError):
+    pass
+
+
+def load():
+    """Load the shared library once; raise if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise KanVitError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C kan_vit_b200/csrc` (there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    lib.kv_version.restype = C.c_int
+    lib.kv_version.argtypes = []
+    lib.kv_status_string.restype = C.c_char_p
+    lib.kv_status_string.argtypes = [C.c_int]
+    lib.kv_last_cuda_error.restype = C.c_char_p
+    lib.kv_last_cuda_error.argtypes = []
+    for name, args in _SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = C.c_int
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str):
+    if rc == 0:
+        return
+    lib = load()
+    msg = lib.kv_status_string(rc).decode()
+    if rc == -6:
+        msg += ": " + lib.kv_last_cuda_error().decode()
+    raise KanVitError(f"{what} failed: {msg} ({rc})")
+
+
+def ptr(t):
+    """Device pointer of a tensor or None."""
+    return None if t is None else t.data_ptr()

@@ -1,0 +1,427 @@
+// C-ABI surface of libkanvit_b200: validation, parameter packing / gradient unpacking,
+// and dispatch of the KAN entry points to the SIMT (fp32) or tcgen05 (bf16) kernels.
+#include <cstdio>
+#include <cstring>
+#include "internal.cuh"
+
+namespace kv {
+
+thread_local char g_cuda_err[256] = "";
+
+int record_cuda_error(cudaError_t e, const char* where) {
+  snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s", where, cudaGetErrorString(e));
+  return KV_ERR_CUDA;
+}
+
+static int family_M(const kv_kan_desc_t& d) {
+  switch (d.family) {
+    case KV_LINEAR: return 1;
+    case KV_EFFKAN: return d.grid_size + d.spline_order + 1;
+    case KV_CHEBY: return d.grid_size + 1;
+    case KV_FASTKAN: return d.grid_size + ((d.flags & KV_FLAG_NO_BASE) ? 0 : 1);
+    case KV_SINE: return d.grid_size;
+    case KV_FOURIER: return 2 * d.grid_size;
+    default: return -1;
+  }
+}
+
+static int fparam_count(const kv_kan_desc_t& d) {
+  switch (d.family) {
+    case KV_EFFKAN: return d.in_features * (d.grid_size + 2 * d.spline_order + 1);
+    case KV_FASTKAN: return 2 * d.in_features + d.grid_size;
+    case KV_SINE: return d.grid_size + d.in_features * d.grid_size;
+    default: return 0;
+  }
+}
+
+int check_desc(const kv_kan_desc_t* d) {
+  if (d == nullptr) return KV_ERR_BAD_ARG;
+  if (d->family < KV_LINEAR || d->family > KV_FOURIER) return KV_ERR_BAD_FAMILY;
+  if (d->T < 0 || d->in_features <= 0 || d->out_features <= 0 || d->n_groups <= 0 || d->x_share <= 0)
+    return KV_ERR_BAD_ARG;
+  if (d->n_groups % d->x_share != 0) return KV_ERR_BAD_SHAPE;
+  if (d->family != KV_LINEAR && d->grid_size <= 0 && d->family != KV_CHEBY) return KV_ERR_BAD_SHAPE;
+  if (d->family == KV_EFFKAN && (d->spline_order < 0 || d->spline_order > KV_MAX_SPLINE_ORDER))
+    return KV_ERR_BAD_SHAPE;
+  const int M = family_M(*d);
+  if (M <= 0 || M > KV_MAX_M || M != d->M) return KV_ERR_BAD_SHAPE;
+  if (d->fparam_stride < fparam_count(*d)) return KV_ERR_BAD_SHAPE;
+  const int n_slices = d->n_groups / d->x_share;
+  if (d->ldx < n_slices * d->in_features || d->ldy < d->n_groups * d->out_features) return KV_ERR_BAD_SHAPE;
+  if (d->rows_in < 0 || (d->rows_in > 0 && (d->rows_out < d->rows_in + d->row_shift || d->row_shift < 0)))
+    return KV_ERR_BAD_SHAPE;
+  if (d->family == KV_FASTKAN && !(d->rbf_denom != 0.0f)) return KV_ERR_BAD_ARG;
+  return KV_OK;
+}
+
+// ------------------------------------------------------------------------------
+// pack: reference parameter layouts -> [g][out][in*M] (K index i*M+m)
+// ------------------------------------------------------------------------------
+__device__ __forceinline__ const float* slot(const uint64_t* tbl, int g, int s) {
+  return reinterpret_cast<const float*>(tbl[(size_t)g * KV_PTRS_PER_GROUP + s]);
+}
+__device__ __forceinline__ float* slot_out(const uint64_t* tbl, int g, int s) {
+  return reinterpret_cast<float*>(tbl[(size_t)g * KV_PTRS_PER_GROUP + s]);
+}
+
+// packed weight element (g, o, i, m) read from the module's own tensors
+__device__ __forceinline__ float load_packed_weight(const kv_kan_desc_t& d, const uint64_t* tbl, int g,
+                                                    int o, int i, int m) {
+  const int in = d.in_features, out = d.out_features, G = d.grid_size;
+  switch (d.family) {
+    case KV_LINEAR:
+      return slot(tbl, g, 0)[(size_t)o * in + i];
+    case KV_EFFKAN: {
+      const int nb = G + d.spline_order;
+      if (m == nb) return slot(tbl, g, 0)[(size_t)o * in + i];
+      float w = slot(tbl, g, 1)[((size_t)o * in + i) * nb + m];
+      const float* sc = slot(tbl, g, 2);
+      if (sc) w *= sc[(size_t)o * in + i];  // scaled_spline_weight, models/effkan.py:166-172
+      return w;
+    }
+    case KV_CHEBY:
+      return slot(tbl, g, 0)[((size_t)i * out + o) * (G + 1) + m];
+    case KV_FASTKAN:
+      if (m < G) return slot(tbl, g, 3)[(size_t)o * in * G + (size_t)i * G + m];
+      return slot(tbl, g, 4)[(size_t)o * in + i];
+    case KV_SINE:
+      return slot(tbl, g, 0)[((size_t)o * in + i) * G + m];
+    case KV_FOURIER: {
+      const int part = m / G, k = m % G;
+      return slot(tbl, g, 0)[(((size_t)part * out + o) * in + i) * G + k];
+    }
+  }
+  return 0.0f;
+}
+
+__global__ void pack_weights_kernel(const kv_kan_desc_t d, const uint64_t* __restrict__ tbl,
+                                    float* __restrict__ wp_f32) {
+  const int g = blockIdx.y;
+  const int M = d.M, in = d.in_features, out = d.out_features;
+  const size_t per_group = (size_t)out * in * M;
+  for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < per_group;
+       p += (size_t)gridDim.x * blockDim.x) {
+    const int m = (int)(p % M);
+    const size_t r = p / M;
+    const int i = (int)(r % in);
+    const int o = (int)(r / in);
+    wp_f32[(size_t)g * per_group + p] = load_packed_weight(d, tbl, g, o, i, m);
+  }
+}
+
+__global__ void pack_fparams_kernel(const kv_kan_desc_t d, const uint64_t* __restrict__ tbl,
+                                    float* __restrict__ fparams, float* __restrict__ bias) {
+  const int g = blockIdx.y;
+  const int in = d.in_features, out = d.out_features, G = d.grid_size;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nth = gridDim.x * blockDim.x;
+  if (fparams != nullptr) {
+    float* fp = fparams + (size_t)g * d.fparam_stride;
+    if (d.family == KV_EFFKAN) {
+      const int n = in * (G + 2 * d.spline_order + 1);
+      const float* grid = slot(tbl, g, 3);
+      for (int p = tid; p < n; p += nth) fp[p] = grid[p];
+    } else if (d.family == KV_FASTKAN) {
+      const float* w = slot(tbl, g, 0);
+      const float* b = slot(tbl, g, 1);
+      const float* gr = slot(tbl, g, 2);
+      for (int p = tid; p < in; p += nth) {
+        fp[p] = w ? w[p] : 1.0f;
+        fp[in + p] = b ? b[p] : 0.0f;
+      }
+      for (int p = tid; p < G; p += nth) fp[2 * in + p] = gr[p];
+    } else if (d.family == KV_SINE) {
+      const float* fr = slot(tbl, g, 1);
+      const float* ph = slot(tbl, g, 2);
+      for (int p = tid; p < G; p += nth) fp[p] = fr[p];
+      for (int p = tid; p < in * G; p += nth) fp[G + p] = ph[p];
+    }
+  }
+  if (bias != nullptr) {
+    int s = -1;
+    if (d.family == KV_LINEAR) s = 1;
+    else if (d.family == KV_FASTKAN) s = 5;
+    else if (d.family == KV_SINE) s = 3;
+    else if (d.family == KV_FOURIER) s = 1;
+    const float* b = s >= 0 ? slot(tbl, g, s) : nullptr;
+    for (int p = tid; p < out; p += nth) bias[(size_t)g * out + p] = b ? b[p] : 0.0f;
+  }
+}
+
+// ------------------------------------------------------------------------------
+// unpack: packed gradients -> reference parameter layouts
+// ------------------------------------------------------------------------------
+__global__ void unpack_grads_kernel(const kv_kan_desc_t d, const float* __restrict__ dWp,
+                                    const float* __restrict__ dfparams, const float* __restrict__ dbias,
+                                    const uint64_t* __restrict__ tbl, const uint64_t* __restrict__ gtbl) {
+  const int g = blockIdx.y;
+  const int M = d.M, in = d.in_features, out = d.out_features, G = d.grid_size;
+  const size_t n_oi = (size_t)out * in;
+  const float* dW = dWp ? dWp + (size_t)g * n_oi * M : nullptr;
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t nth = (size_t)gridDim.x * blockDim.x;
+  if (dW != nullptr) {
+    for (size_t p = tid; p < n_oi; p += nth) {  // one (o,i) pair per iteration
+      const int i = (int)(p % in), o = (int)(p / in);
+      const float* src = dW + p * M;
+      switch (d.family) {
+        case KV_LINEAR: {
+          float* gw = slot_out(gtbl, g, 0);
+          if (gw) gw[p] = src[0];
+          break;
+        }
+        case KV_EFFKAN: {
+          const int nb = G + d.spline_order;
+          float* gb = slot_out(gtbl, g, 0);
+          float* gs = slot_out(gtbl, g, 1);
+          float* gsc = slot_out(gtbl, g, 2);
+          const float* sw = slot(tbl, g, 1);
+          const float* sc = slot(tbl, g, 2);
+          if (gb) gb[p] = src[nb];
+          const float scale = sc ? sc[p] : 1.0f;
+          float acc = 0.0f;
+          for (int m = 0; m < nb; ++m) {
+            const float gv = src[m];
+            if (gs) gs[p * nb + m] = gv * scale;
+            acc += gv * sw[p * nb + m];
+          }
+          if (gsc) gsc[p] = acc;
+          break;
+        }
+        case KV_CHEBY: {
+          float* gc = slot_out(gtbl, g, 0);
+          if (gc)
+            for (int m = 0; m < M; ++m) gc[((size_t)i * out + o) * M + m] = src[m];
+          break;
+        }
+        case KV_FASTKAN: {
+          float* gs = slot_out(gtbl, g, 3);
+          float* gb = slot_out(gtbl, g, 4);
+          if (gs)
+            for (int m = 0; m < G; ++m) gs[(size_t)o * in * G + (size_t)i * G + m] = src[m];
+          if (gb && M > G) gb[p] = src[G];
+          break;
+        }
+        case KV_SINE: {
+          float* ga = slot_out(gtbl, g, 0);
+          if (ga)
+            for (int m = 0; m < G; ++m) ga[p * G + m] = src[m];
+          break;
+        }
+        case KV_FOURIER: {
+          float* gf = slot_out(gtbl, g, 0);
+          if (gf)
+            for (int m = 0; m < M; ++m) {
+              const int part = m / G, k = m % G;
+              gf[(((size_t)part * out + o) * in + i) * G + k] = src[m];
+            }
+          break;
+        }
+      }
+    }
+  }
+  if (dbias != nullptr) {
+    int s = -1;
+    if (d.family == KV_LINEAR) s = 1;
+    else if (d.family == KV_FASTKAN) s = 5;
+    else if (d.family == KV_SINE) s = 3;
+    else if (d.family == KV_FOURIER) s = 1;
+    float* gb = s >= 0 ? slot_out(gtbl, g, s) : nullptr;
+    if (gb)
+      for (size_t p = tid; p < (size_t)out; p += nth) gb[p] = dbias[(size_t)g * out + p];
+  }
+  if (dfparams != nullptr) {
+    const float* dfp = dfparams + (size_t)g * d.fparam_stride;
+    if (d.family == KV_FASTKAN) {
+      float* gw = slot_out(gtbl, g, 0);
+      float* gbb = slot_out(gtbl, g, 1);
+      for (size_t p = tid; p < (size_t)in; p += nth) {
+        if (gw) gw[p] = dfp[p];
+        if (gbb) gbb[p] = dfp[in + p];
+      }
+    } else if (d.family == KV_SINE) {
+      float* gf = slot_out(gtbl, g, 1);
+      if (gf)
+        for (size_t p = tid; p < (size_t)G; p += nth) gf[p] = dfp[p];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------
+// per-(row, slice) LayerNorm statistics
+// ------------------------------------------------------------------------------
+__global__ void row_stats_kernel(const float* __restrict__ X, int T, int ldx, int n_slices, int width,
+                                 float eps, float* __restrict__ mean, float* __restrict__ rstd) {
+  const int warps_per_block = blockDim.x / 32;
+  const int lane = threadIdx.x & 31;
+  const long long total = (long long)T * n_slices;
+  for (long long w = (long long)blockIdx.x * warps_per_block + threadIdx.x / 32; w < total;
+       w += (long long)gridDim.x * warps_per_block) {
+    const int s = (int)(w % n_slices);
+    const long long t = w / n_slices;
+    const float* row = X + t * ldx + (size_t)s * width;
+    float sum = 0.0f;
+    for (int c = lane; c < width; c += 32) sum += row[c];
+    const float mu = warp_sum(sum) / (float)width;
+    float sq = 0.0f;
+    for (int c = lane; c < width; c += 32) {
+      const float dlt = row[c] - mu;
+      sq += dlt * dlt;
+    }
+    const float var = warp_sum(sq) / (float)width;
+    if (lane == 0) {
+      mean[w] = mu;
+      rstd[w] = rsqrtf(var + eps);
+    }
+  }
+}
+
+}  // namespace kv
+
+// ================================================================================
+// extern "C"
+// ================================================================================
+using namespace kv;
+
+extern "C" {
+
+int kv_version(void) { return KV_ABI_VERSION; }
+
+const char* kv_status_string(int status) {
+  switch (status) {
+    case KV_OK: return "ok";
+    case KV_ERR_BAD_ARG: return "bad argument (null pointer or negative size)";
+    case KV_ERR_BAD_SHAPE: return "shape not supported";
+    case KV_ERR_BAD_FAMILY: return "unknown basis family";
+    case KV_ERR_ALIGNMENT: return "pointer or leading dimension misaligned";
+    case KV_ERR_UNSUPPORTED: return "combination not supported in this precision mode";
+    case KV_ERR_CUDA: return "CUDA error";
+    default: return "unknown status";
+  }
+}
+
+const char* kv_last_cuda_error(void) { return g_cuda_err; }
+
+int kv_kan_fparam_count(const kv_kan_desc_t* d) {
+  if (d == nullptr) return KV_ERR_BAD_ARG;
+  if (d->family < KV_LINEAR || d->family > KV_FOURIER) return KV_ERR_BAD_FAMILY;
+  return fparam_count(*d);
+}
+
+int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32, void* wtiles_bf16,
+                void* wtiles_t_bf16, float* fparams, float* bias, void* stream) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  if (ptr_table == nullptr) return KV_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (wp_f32 != nullptr) {
+    const size_t per_group = (size_t)d->out_features * d->in_features * d->M;
+    int bx = (int)((per_group + 255) / 256);
+    if (bx > 2048) bx = 2048;
+    pack_weights_kernel<<<dim3(bx, d->n_groups), 256, 0, st>>>(*d, ptr_table, wp_f32);
+    KV_CHECK_LAUNCH("pack_weights");
+  }
+  if (fparams != nullptr || bias != nullptr) {
+    pack_fparams_kernel<<<dim3(8, d->n_groups), 256, 0, st>>>(*d, ptr_table, fparams, bias);
+    KV_CHECK_LAUNCH("pack_fparams");
+  }
+  if (wtiles_bf16 != nullptr || wtiles_t_bf16 != nullptr) {
+    rc = tc_pack(*d, ptr_table, wtiles_bf16, wtiles_t_bf16, st);
+    if (rc != KV_OK) return rc;
+  }
+  return KV_OK;
+}
+
+int kv_row_stats(const float* X, int T, int ldx, int n_slices, int width, float eps, float* mean,
+                 float* rstd, void* stream) {
+  if (X == nullptr || mean == nullptr || rstd == nullptr || T < 0 || n_slices <= 0 || width <= 0)
+    return KV_ERR_BAD_ARG;
+  if (T == 0) return KV_OK;
+  const long long total = (long long)T * n_slices;
+  int blocks = (int)((total + 7) / 8);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  row_stats_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(X, T, ldx, n_slices, width, eps, mean, rstd);
+  KV_CHECK_LAUNCH("row_stats");
+  return KV_OK;
+}
+
+int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, const void* wtiles_bf16,
+               const float* fparams, const float* bias, const float* mean, const float* rstd,
+               const float* residual, const float* pos, float* Y, void* stream) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  if (X == nullptr || Y == nullptr) return KV_ERR_BAD_ARG;
+  if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;
+  if (d->family == KV_FASTKAN && !(d->flags & KV_FLAG_NO_LAYERNORM) && (mean == nullptr || rstd == nullptr))
+    return KV_ERR_BAD_ARG;
+  if (d->T == 0) return KV_OK;
+  if (d->flags & KV_FLAG_BF16_TC) {
+    if (wtiles_bf16 == nullptr) return KV_ERR_BAD_ARG;
+    rc = tc_supported(*d);
+    if (rc != KV_OK) return rc;
+    return tc_fwd(*d, X, wtiles_bf16, fparams, bias, mean, rstd, residual, pos, Y, (cudaStream_t)stream);
+  }
+  if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;
+  return simt_fwd(*d, X, wp_f32, fparams, bias, mean, rstd, residual, pos, Y, (cudaStream_t)stream);
+}
+
+int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
+                     const float* wp_f32, const void* wtiles_t_bf16, const float* fparams,
+                     const float* mean, const float* rstd, float* dX, float* dXn, float* dfparams,
+                     void* stream) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  if (X == nullptr || dY == nullptr || dX == nullptr) return KV_ERR_BAD_ARG;
+  if ((d->flags & KV_FLAG_RELU) && act_mask == nullptr) return KV_ERR_BAD_ARG;
+  if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;
+  if (d->family == KV_FASTKAN && !(d->flags & KV_FLAG_NO_LAYERNORM) &&
+      (mean == nullptr || rstd == nullptr || dXn == nullptr))
+    return KV_ERR_BAD_ARG;
+  if (d->T == 0) return KV_OK;
+  if (d->flags & KV_FLAG_BF16_TC) {
+    if (wtiles_t_bf16 == nullptr) return KV_ERR_BAD_ARG;
+    rc = tc_supported(*d);
+    if (rc != KV_OK) return rc;
+    return tc_bwd_input(*d, X, dY, act_mask, wtiles_t_bf16, fparams, mean, rstd, dX, dXn, dfparams,
+                        (cudaStream_t)stream);
+  }
+  if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;
+  return simt_bwd_input(*d, X, dY, act_mask, wp_f32, fparams, mean, rstd, dX, dXn, dfparams,
+                        (cudaStream_t)stream);
+}
+
+int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
+                      const float* fparams, const float* mean, const float* rstd, float* dWp,
+                      float* dbias, void* stream) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  if (X == nullptr || dY == nullptr || dWp == nullptr) return KV_ERR_BAD_ARG;
+  if ((d->flags & KV_FLAG_RELU) && act_mask == nullptr) return KV_ERR_BAD_ARG;
+  if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;
+  if (d->family == KV_FASTKAN && !(d->flags & KV_FLAG_NO_LAYERNORM) && (mean == nullptr || rstd == nullptr))
+    return KV_ERR_BAD_ARG;
+  if (d->T == 0) return KV_OK;
+  if (d->flags & KV_FLAG_BF16_TC) {
+    rc = tc_supported(*d);
+    if (rc != KV_OK) return rc;
+    return tc_bwd_weight(*d, X, dY, act_mask, fparams, mean, rstd, dWp, dbias, (cudaStream_t)stream);
+  }
+  return simt_bwd_weight(*d, X, dY, act_mask, fparams, mean, rstd, dWp, dbias, (cudaStream_t)stream);
+}
+
+int kv_kan_unpack_grads(const kv_kan_desc_t* d, const float* dWp, const float* dfparams,
+                        const float* dbias, const uint64_t* ptr_table, const uint64_t* grad_table,
+                        void* stream) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  if (ptr_table == nullptr || grad_table == nullptr) return KV_ERR_BAD_ARG;
+  const size_t n_oi = (size_t)d->out_features * d->in_features;
+  int bx = (int)((n_oi + 255) / 256);
+  if (bx > 1024) bx = 1024;
+  unpack_grads_kernel<<<dim3(bx, d->n_groups), 256, 0, (cudaStream_t)stream>>>(*d, dWp, dfparams, dbias,
+                                                                               ptr_table, grad_table);
+  KV_CHECK_LAUNCH("unpack_grads");
+  return KV_OK;
+}
+
+}  // extern "C"

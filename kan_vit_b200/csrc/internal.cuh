@@ -1,0 +1,35 @@
+// Internal entry points shared between the translation units of libkanvit_b200.
+#pragma once
+#include "common.cuh"
+
+namespace kv {
+
+// kan_simt.cu -- fp32 SIMT basis-prologue GEMMs
+int simt_fwd(const kv_kan_desc_t& d, const float* X, const float* Wp, const float* fparams,
+             const float* bias, const float* mean, const float* rstd, const float* residual,
+             const float* pos, float* Y, cudaStream_t st);
+int simt_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const float* mask,
+                   const float* Wp, const float* fparams, const float* mean, const float* rstd,
+                   float* dX, float* dXn, float* dfparams, cudaStream_t st);
+int simt_bwd_weight(const kv_kan_desc_t& d, const float* X, const float* dY, const float* mask,
+                    const float* fparams, const float* mean, const float* rstd, float* dWp,
+                    float* dbias, cudaStream_t st);
+
+// kan_tc.cu -- tcgen05 / TMEM bf16 basis-prologue GEMMs
+int tc_supported(const kv_kan_desc_t& d);
+int tc_pack(const kv_kan_desc_t& d, const uint64_t* ptr_table, void* wtiles, void* wtiles_t,
+            cudaStream_t st);
+int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const float* fparams,
+           const float* bias, const float* mean, const float* rstd, const float* residual,
+           const float* pos, float* Y, cudaStream_t st);
+int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const float* mask,
+                 const void* wtiles_t, const float* fparams, const float* mean, const float* rstd,
+                 float* dX, float* dXn, float* dfparams, cudaStream_t st);
+int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const float* dY, const float* mask,
+                  const float* fparams, const float* mean, const float* rstd, float* dWp,
+                  float* dbias, cudaStream_t st);
+
+// validation shared by every kan entry point
+int check_desc(const kv_kan_desc_t* d);
+
+}  // namespace kv

@@ -1,0 +1,356 @@
+"""torch.autograd.Function wrappers around the C ABI (include/kanvit_b200.h).
+
+PyTorch is plumbing here: it owns the device memory, the stream and the autograd graph.
+All arithmetic of the path runs in libkanvit_b200.so.  No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib as L
+
+_FAMILY_GRAD_SLOTS = {
+    L.KV_LINEAR: (0, 1),
+    L.KV_EFFKAN: (0, 1, 2),
+    L.KV_CHEBY: (0,),
+    L.KV_FASTKAN: (0, 1, 3, 4, 5),
+    L.KV_SINE: (0, 1, 3),
+    L.KV_FOURIER: (0, 1),
+}
+_FAMILY_BIAS_SLOT = {L.KV_LINEAR: 1, L.KV_FASTKAN: 5, L.KV_SINE: 3, L.KV_FOURIER: 1}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise L.KanVitError("kan_vit_b200 ops need CUDA tensors (there is no CPU path)")
+
+
+class KanSpec:
+    """Static description of one KAN / Linear layer, or of n_groups equal-shaped layers
+    applied to column slices of one activation matrix (kv_kan_desc_t without T / strides)."""
+
+    def __init__(self, family: int, in_features: int, out_features: int, n_groups: int = 1,
+                 x_share: int = 1, grid_size: int = 0, spline_order: int = 0, flags: int = 0,
+                 rbf_denom: float = 1.0):
+        self.family = family
+        self.in_features = in_features
+        self.out_features = out_features
+        self.n_groups = n_groups
+        self.x_share = x_share
+        self.grid_size = grid_size
+        self.spline_order = spline_order
+        self.flags = flags
+        self.rbf_denom = float(rbf_denom)
+        if family == L.KV_LINEAR:
+            self.M = 1
+        elif family == L.KV_EFFKAN:
+            self.M = grid_size + spline_order + 1
+        elif family == L.KV_CHEBY:
+            self.M = grid_size + 1
+        elif family == L.KV_FASTKAN:
+            self.M = grid_size + (0 if flags & L.KV_FLAG_NO_BASE else 1)
+        elif family == L.KV_SINE:
+            self.M = grid_size
+        elif family == L.KV_FOURIER:
+            self.M = 2 * grid_size
+        else:
+            raise ValueError(f"unknown family {family}")
+        if self.M > L.KV_MAX_M:
+            raise L.KanVitError(f"{self.M} basis functions per input exceed KV_MAX_M={L.KV_MAX_M}")
+        d = self.desc(0, 0, 0)
+        self.fparam_stride = max(L.load().kv_kan_fparam_count(C.byref(d)), 0)
+        self._tbl_cache = None     # (ptrs, device tensor)
+        self._pack_cache = None    # (key, packed dict)
+        self._goff_cache = None    # (shapes key, offsets tensor, mask, total, views meta)
+
+    @property
+    def n_slices(self):
+        return self.n_groups // self.x_share
+
+    def desc(self, T, ldx, ldy, rows_in=0, rows_out=0, row_shift=0, extra_flags=0) -> L.KanDesc:
+        return L.KanDesc(self.family, T, self.in_features, self.out_features, self.n_groups,
+                         self.x_share, self.M, self.grid_size, self.spline_order, ldx, ldy,
+                         rows_in, rows_out, row_shift, self.flags | extra_flags, self.rbf_denom,
+                         getattr(self, "fparam_stride", 1 << 30), 0)
+
+    # -- parameter pointer table (device, cached while the parameter storages stay put)
+    def ptr_table(self, flat: Sequence[Optional[torch.Tensor]], device) -> torch.Tensor:
+        ptrs = tuple(0 if t is None else t.data_ptr() for t in flat)
+        if self._tbl_cache is None or self._tbl_cache[0] != ptrs or self._tbl_cache[1].device != device:
+            tbl = torch.tensor(ptrs, dtype=torch.int64).to(device)
+            self._tbl_cache = (ptrs, tbl)
+        return self._tbl_cache[1]
+
+    # -- packed weights / prologue parameters (cached until a parameter is modified)
+    def packed(self, flat, device, want_tc: bool):
+        key = (tuple(0 if t is None else (t.data_ptr(), t._version) for t in flat), want_tc)
+        if self._pack_cache is not None and self._pack_cache[0] == key:
+            return self._pack_cache[1]
+        lib = L.load()
+        g, o, K = self.n_groups, self.out_features, self.in_features * self.M
+        tbl = self.ptr_table(flat, device)
+        wp = torch.empty((g, o, K), dtype=torch.float32, device=device)
+        fp = torch.empty((g, max(self.fparam_stride, 1)), dtype=torch.float32, device=device)
+        has_bias = self.family in _FAMILY_BIAS_SLOT and any(
+            flat[q * L.KV_PTRS_PER_GROUP + _FAMILY_BIAS_SLOT[self.family]] is not None for q in range(g))
+        bias = torch.empty((g, o), dtype=torch.float32, device=device) if has_bias else None
+        d = self.desc(0, self.n_slices * self.in_features, g * o)
+        L.check(lib.kv_kan_pack(C.byref(d), tbl.data_ptr(), wp.data_ptr(), None, None,
+                                fp.data_ptr() if self.fparam_stride else None, L.ptr(bias), _stream()),
+                "kv_kan_pack")
+        pk = {"wp": wp, "fp": fp if self.fparam_stride else None, "bias": bias, "tbl": tbl}
+        self._pack_cache = (key, pk)
+        return pk
+
+    # -- flat gradient buffer layout (byte offsets per pointer-table slot)
+    def grad_layout(self, flat, device):
+        key = tuple(None if t is None else tuple(t.shape) for t in flat)
+        if self._goff_cache is not None and self._goff_cache[0] == key and self._goff_cache[1].device == device:
+            return self._goff_cache[1:]
+        offs, meta, total = [], [], 0
+        slots = _FAMILY_GRAD_SLOTS[self.family]
+        for idx, t in enumerate(flat):
+            s = idx % L.KV_PTRS_PER_GROUP
+            if t is None or s not in slots or not t.is_floating_point():
+                offs.append(-1)
+                meta.append(None)
+                continue
+            offs.append(total * 4)
+            meta.append((total, t.numel(), tuple(t.shape)))
+            total += (t.numel() + 3) // 4 * 4  # keep every gradient 16-byte aligned
+        off_t = torch.tensor(offs, dtype=torch.int64).to(device)
+        self._goff_cache = (key, off_t, meta, total)
+        return off_t, meta, total
+
+
+class _KanFn(torch.autograd.Function):
+    """Y = KAN(x) (+bias) (+pos) [relu] (+residual); optional class-token rows."""
+
+    @staticmethod
+    def forward(ctx, x, residual, v_class, pos, spec: KanSpec, cfg: dict, *flat):
+        lib = L.load()
+        _require_cuda(x, residual, v_class, pos, *flat)
+        assert x.dim() == 2 and x.dtype == torch.float32 and x.is_contiguous()
+        T = x.shape[0]
+        n_in = spec.n_slices * spec.in_features
+        n_out = spec.n_groups * spec.out_features
+        assert x.shape[1] == n_in
+        rows_in, rows_out, row_shift = cfg.get("rows_in", 0), cfg.get("rows_out", 0), cfg.get("row_shift", 0)
+        rows = T if rows_in == 0 else (T // rows_in) * rows_out
+        extra = L.KV_FLAG_RELU if cfg.get("relu") else 0
+        d = spec.desc(T, n_in, n_out, rows_in, rows_out, row_shift, extra)
+        pk = spec.packed(flat, x.device, False)
+        mean = rstd = None
+        if spec.family == L.KV_FASTKAN and not (spec.flags & L.KV_FLAG_NO_LAYERNORM):
+            mean = torch.empty((T, spec.n_slices), dtype=torch.float32, device=x.device)
+            rstd = torch.empty_like(mean)
+            L.check(lib.kv_row_stats(x.data_ptr(), T, n_in, spec.n_slices, spec.in_features, 1e-5,
+                                     mean.data_ptr(), rstd.data_ptr(), _stream()), "kv_row_stats")
+        y = torch.empty((rows, n_out), dtype=torch.float32, device=x.device)
+        if residual is not None:
+            assert residual.shape == y.shape and residual.is_contiguous()
+        if pos is not None:
+            assert pos.is_contiguous() and pos.shape[-1] == n_out
+        L.check(lib.kv_kan_fwd(C.byref(d), x.data_ptr(), pk["wp"].data_ptr(), None, L.ptr(pk["fp"]),
+                               L.ptr(pk["bias"]), L.ptr(mean), L.ptr(rstd), L.ptr(residual), L.ptr(pos),
+                               y.data_ptr(), _stream()), "kv_kan_fwd")
+        if v_class is not None:
+            assert rows_in > 0 and row_shift == 1 and spec.n_groups == 1
+            L.check(lib.kv_cls_rows_fwd(v_class.data_ptr(), L.ptr(pos), y.data_ptr(), T // rows_in,
+                                        rows_out, n_out, _stream()), "kv_cls_rows_fwd")
+        ctx.spec, ctx.cfg, ctx.flat, ctx.pk = spec, cfg, flat, pk
+        ctx.d = d
+        ctx.has_res, ctx.has_cls = residual is not None, v_class is not None
+        ctx.save_for_backward(x, y if cfg.get("relu") else None, mean, rstd)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = L.load()
+        spec, flat, pk, d = ctx.spec, ctx.flat, ctx.pk, ctx.d
+        x, ymask, mean, rstd = ctx.saved_tensors
+        dy = dy.contiguous()
+        dev = x.device
+        T = x.shape[0]
+        g, o, K = spec.n_groups, spec.out_features, spec.in_features * spec.M
+        st = _stream()
+        need_w = any(t is not None and t.requires_grad for t in flat)
+        grads: List[Optional[torch.Tensor]] = [None] * len(flat)
+        dfp = None
+        if spec.family in (L.KV_SINE, L.KV_FASTKAN):
+            dfp = torch.zeros((g, spec.fparam_stride), dtype=torch.float32, device=dev)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            dxn = None
+            if mean is not None:
+                dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
+            L.check(lib.kv_kan_bwd_input(C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
+                                         pk["wp"].data_ptr(), None, L.ptr(pk["fp"]), L.ptr(mean),
+                                         L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st),
+                    "kv_kan_bwd_input")
+            if dxn is not None:
+                L.check(lib.kv_fastkan_ln_bwd(C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
+                                              mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(),
+                                              dfp.data_ptr(), st), "kv_fastkan_ln_bwd")
+        elif need_w and spec.family in (L.KV_SINE, L.KV_FASTKAN):
+            # d freq / d layernorm.{weight,bias} come out of the input-gradient pass
+            dx_tmp = torch.empty_like(x)
+            dxn = None
+            if mean is not None:
+                dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
+            L.check(lib.kv_kan_bwd_input(C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
+                                         pk["wp"].data_ptr(), None, L.ptr(pk["fp"]), L.ptr(mean),
+                                         L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st),
+                    "kv_kan_bwd_input")
+            if dxn is not None:
+                L.check(lib.kv_fastkan_ln_bwd(C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
+                                              mean.data_ptr(), rstd.data_ptr(), dx_tmp.data_ptr(),
+                                              dfp.data_ptr(), st), "kv_fastkan_ln_bwd")
+        if need_w:
+            dwp = torch.zeros((g, o, K), dtype=torch.float32, device=dev)
+            dbias = torch.zeros((g, o), dtype=torch.float32, device=dev) if pk["bias"] is not None else None
+            L.check(lib.kv_kan_bwd_weight(C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
+                                          L.ptr(pk["fp"]), L.ptr(mean), L.ptr(rstd), dwp.data_ptr(),
+                                          L.ptr(dbias), st), "kv_kan_bwd_weight")
+            off_t, meta, total = spec.grad_layout(flat, dev)
+            gflat = torch.empty((total,), dtype=torch.float32, device=dev)
+            gtbl = torch.where(off_t >= 0, off_t + gflat.data_ptr(), torch.zeros_like(off_t))
+            L.check(lib.kv_kan_unpack_grads(C.byref(d), dwp.data_ptr(), L.ptr(dfp), L.ptr(dbias),
+                                            pk["tbl"].data_ptr(), gtbl.data_ptr(), st),
+                    "kv_kan_unpack_grads")
+            for idx, m in enumerate(meta):
+                if m is not None and flat[idx].requires_grad:
+                    grads[idx] = gflat[m[0]:m[0] + m[1]].view(m[2])
+        dres = dy if ctx.has_res else None
+        dcls = None
+        if ctx.has_cls:
+            n_out = g * o
+            dcls = torch.empty((1, n_out), dtype=torch.float32, device=dev)
+            L.check(lib.kv_cls_rows_bwd(dy.data_ptr(), dcls.data_ptr(), T // d.rows_in, d.rows_out, n_out, st),
+                    "kv_cls_rows_bwd")
+        return (dx, dres, dcls, None, None, None) + tuple(grads)
+
+
+def kan_apply(x2d, spec: KanSpec, group_slots: Sequence[Sequence[Optional[torch.Tensor]]], *,
+              relu=False, residual=None, pos=None, v_class=None, rows_in=0, rows_out=0, row_shift=0):
+    """Apply the layer(s) described by ``spec``; ``group_slots[g]`` lists the group's tensors in
+    pointer-table slot order (see kv_kan_pack in include/kanvit_b200.h)."""
+    flat = []
+    for slots in group_slots:
+        s = list(slots) + [None] * (L.KV_PTRS_PER_GROUP - len(slots))
+        flat.extend(s)
+    cfg = {"relu": relu, "rows_in": rows_in, "rows_out": rows_out, "row_shift": row_shift}
+    if not x2d.is_contiguous():
+        x2d = x2d.contiguous()
+    if x2d.dtype != torch.float32:
+        x2d = x2d.float()
+    return _KanFn.apply(x2d, residual, v_class, pos, spec, cfg, *flat)
+
+
+class _AttnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, residual, B, N, H, dh):
+        lib = L.load()
+        _require_cuda(qkv, residual)
+        assert qkv.is_contiguous() and qkv.shape == (B * N, 3 * H * dh)
+        out = torch.empty((B * N, H * dh), dtype=torch.float32, device=qkv.device)
+        lse = torch.empty((B, H, N), dtype=torch.float32, device=qkv.device)
+        L.check(lib.kv_attn_fwd(qkv.data_ptr(), L.ptr(residual), out.data_ptr(), lse.data_ptr(),
+                                B, N, H, dh, _stream()), "kv_attn_fwd")
+        ctx.save_for_backward(qkv, lse)
+        ctx.dims = (B, N, H, dh)
+        ctx.has_res = residual is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = L.load()
+        qkv, lse = ctx.saved_tensors
+        B, N, H, dh = ctx.dims
+        dout = dout.contiguous()
+        dqkv = torch.empty_like(qkv)
+        L.check(lib.kv_attn_bwd(qkv.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
+                                B, N, H, dh, _stream()), "kv_attn_bwd")
+        return dqkv, (dout if ctx.has_res else None), None, None, None, None
+
+
+def attention(qkv, B, N, H, dh, residual=None):
+    """softmax(q k^T / sqrt(dh)) v per (sample, head) on qkv [B*N, H*3*dh] -> [B*N, H*dh] (+residual)."""
+    return _AttnFn.apply(qkv.contiguous(), residual, B, N, H, dh)
+
+
+class _LayerNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps, ldx):
+        lib = L.load()
+        _require_cuda(x, gamma, beta)
+        T, d = x.shape
+        assert x.stride(1) == 1 and x.stride(0) == ldx and x.dtype == torch.float32
+        y = torch.empty((T, d), dtype=torch.float32, device=x.device)
+        mean = torch.empty((T,), dtype=torch.float32, device=x.device)
+        rstd = torch.empty_like(mean)
+        L.check(lib.kv_layernorm_fwd(x.data_ptr(), L.ptr(gamma), L.ptr(beta), y.data_ptr(), mean.data_ptr(),
+                                     rstd.data_ptr(), T, d, ldx, eps, _stream()), "kv_layernorm_fwd")
+        ctx.save_for_backward(x, gamma, mean, rstd)
+        ctx.eps, ctx.ldx = eps, ldx
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = L.load()
+        x, gamma, mean, rstd = ctx.saved_tensors
+        T, d = x.shape
+        dy = dy.contiguous()
+        dx = torch.empty((T, d), dtype=torch.float32, device=x.device)
+        dgamma = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
+        dbeta = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
+        L.check(lib.kv_layernorm_bwd(x.data_ptr(), dy.data_ptr(), L.ptr(gamma), mean.data_ptr(),
+                                     rstd.data_ptr(), None, dx.data_ptr(), L.ptr(dgamma), L.ptr(dbeta),
+                                     T, d, ctx.ldx, ctx.eps, _stream()), "kv_layernorm_bwd")
+        return dx, dgamma, dbeta, None, None
+
+
+def layer_norm(x2d, gamma, beta, eps=1e-5):
+    """nn.LayerNorm over the last dim of a 2-D (possibly row-strided) fp32 matrix."""
+    if x2d.stride(1) != 1:
+        x2d = x2d.contiguous()
+    return _LayerNormFn.apply(x2d, gamma, beta, eps, x2d.stride(0))
+
+
+class _PatchifyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, images, n_patches):
+        lib = L.load()
+        _require_cuda(images)
+        B, Cc, H, W = images.shape
+        ph, pw = H // n_patches, W // n_patches
+        patches = torch.empty((B, n_patches * n_patches, Cc * ph * pw), dtype=torch.float32,
+                              device=images.device)
+        L.check(lib.kv_patchify(images.data_ptr(), patches.data_ptr(), B, Cc, H, W, n_patches, _stream()),
+                "kv_patchify")
+        ctx.dims = (B, Cc, H, W, n_patches)
+        return patches
+
+    @staticmethod
+    def backward(ctx, dpatches):
+        lib = L.load()
+        B, Cc, H, W, n_patches = ctx.dims
+        dpatches = dpatches.contiguous()
+        dimg = torch.empty((B, Cc, H, W), dtype=torch.float32, device=dpatches.device)
+        L.check(lib.kv_patchify_bwd(dpatches.data_ptr(), dimg.data_ptr(), B, Cc, H, W, n_patches, _stream()),
+                "kv_patchify_bwd")
+        return dimg, None
+
+
+def patchify(images, n_patches):
+    """VisionTransformer.patchify (model.py:111-126): (B,C,H,W) -> (B, np^2, C*ph*pw) float32."""
+    return _PatchifyFn.apply(images.contiguous().float(), n_patches)

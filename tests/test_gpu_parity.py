@@ -1,0 +1,208 @@
+"""GPU parity: the CUDA path (through the C ABI) against the golden vectors generated from the
+unmodified reference, and against the oracle on larger seeded inputs.
+
+Tolerance (BASELINE.json north_star): fp32 path within 1e-5 relative, measured norm-wise
+(max|a-b| / max|b| per tensor); layout pieces bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, relerr
+
+pytestmark = pytest.mark.gpu
+
+TOL_FP32 = 1e-5
+TOL_GRAD = 2e-5  # gradients pass through one more fp32 reduction (over T) than outputs
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _build(case):
+    import kan_vit_b200 as K
+    mk = {
+        "layer_effkan": lambda: K.KANLinear(16, 24),
+        "layer_effkan_g10k2_nonuniform": lambda: K.KANLinear(8, 12, grid_size=10, spline_order=2,
+                                                             enable_standalone_scale_spline=False),
+        "layer_cheby": lambda: K.ChebyKANLayer(16, 24, 4),
+        "layer_cheby_deg7": lambda: K.ChebyKANLayer(8, 8, 7),
+        "layer_fastkan": lambda: K.FastKANLayer(16, 24),
+        "layer_sine": lambda: K.SineKANLayer(16, 24),
+        "layer_sine_g4": lambda: K.SineKANLayer(8, 8, grid_size=4),
+        "layer_fourier": lambda: K.NaiveFourierKANLayer(16, 24, 5),
+        "block_efficientkan": lambda: K.TransformerBlock(16, 2, feedforward_dim=64, attn_type="efficientkan"),
+        "block_efficientkan_kanmlp": lambda: K.TransformerBlock(16, 2, feedforward_dim=64,
+                                                                attn_type="efficientkan", kan_mlp=True),
+    }
+    if case.startswith("msa_"):
+        return K.MSA(16, n_heads=2, type=case[4:])
+    if case.startswith("vit_"):
+        return K.VisionTransformer((1, 8, 8), n_patches=2, n_blocks=2, d_hidden=16, n_heads=2, out_d=10,
+                                   type=case[4:])
+    return mk[case]()
+
+
+CASES = ["layer_effkan", "layer_effkan_g10k2_nonuniform", "layer_cheby", "layer_cheby_deg7",
+         "layer_fastkan", "layer_sine", "layer_sine_g4", "layer_fourier",
+         "msa_vanilla", "msa_efficientkan", "msa_cheby", "msa_fast", "msa_sine",
+         "block_efficientkan", "block_efficientkan_kanmlp",
+         "vit_vanilla", "vit_efficientkan", "vit_fast", "vit_sine", "vit_cheby"]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_matches_reference_golden(case):
+    g = load_golden(case)
+    m = _build(case)
+    missing, unexpected = m.load_state_dict(g.sd(), strict=False)
+    assert not unexpected, unexpected
+    assert all(k.endswith("pos_embeddings") for k in missing), missing
+    m = m.to(_dev())
+    x = g.t("x", _dev()).requires_grad_(True)
+    y = m(x)
+    ref_y = g.t("y")
+    assert y.shape == ref_y.shape
+    assert relerr(y, ref_y) < TOL_FP32
+    y.backward(g.t("dy", _dev()))
+    assert relerr(x.grad, g.t("gx")) < TOL_GRAD
+    params = dict(m.named_parameters())
+    for k, ref in g.grads().items():
+        got = params[k].grad
+        assert got is not None, k
+        if ref.abs().max() < 1e-6:  # analytically zero (key bias under softmax)
+            assert got.abs().max() < 1e-5, k
+            continue
+        assert relerr(got, ref) < TOL_GRAD, k
+
+
+def test_patchify_and_pos_bit_exact():
+    import kan_vit_b200 as K
+    z = np.load(__import__("os").path.join(__import__("conftest").GOLDEN, "layout.npz"))
+    v = K.VisionTransformer((3, 32, 32), n_patches=4, n_blocks=1, d_hidden=24, n_heads=2).to(_dev())
+    got = v.patchify(torch.from_numpy(z["img_3x32"]).to(_dev()), 4).cpu()
+    assert torch.equal(got, torch.from_numpy(z["patches_3x32_np4"]))
+    assert torch.equal(v.pos_embeddings.cpu(), torch.from_numpy(z["pos_17x24"]))
+    v7 = K.VisionTransformer((1, 28, 28), n_patches=7, n_blocks=1, d_hidden=64, n_heads=2).to(_dev())
+    got = v7.patchify(torch.from_numpy(z["img_1x28"]).to(_dev()), 7).cpu()
+    assert torch.equal(got, torch.from_numpy(z["patches_1x28_np7"]))
+    assert torch.equal(v7.pos_embeddings.cpu(), torch.from_numpy(z["pos_50x64"]))
+
+
+# ---------------------------------------------------------------------------------------------
+# larger seeded inputs against the oracle (CPU, fp32), incl. ragged T and edge values
+# ---------------------------------------------------------------------------------------------
+def _oracle_layer(kind, m, x):
+    from oracle import kan_oracle as O
+    sd = {k: v.detach().cpu().clone().requires_grad_(v.is_floating_point()) for k, v in m.state_dict().items()}
+    xc = x.detach().cpu().clone().requires_grad_(True)
+    y = O.layer_forward(kind, xc, sd, "")
+    return y, xc, sd
+
+
+LAYER_SWEEP = [
+    ("efficientkan", lambda K: K.KANLinear(37, 70), 37),
+    ("efficientkan", lambda K: K.KANLinear(64, 64, grid_size=20), 64),
+    ("cheby", lambda K: K.ChebyKANLayer(33, 65, 6), 33),
+    ("fast", lambda K: K.FastKANLayer(48, 40), 48),
+    ("sine", lambda K: K.SineKANLayer(40, 72, grid_size=10), 40),
+    ("fourier", lambda K: K.NaiveFourierKANLayer(24, 40, 7), 24),
+    ("vanilla", lambda K: torch.nn.Linear(50, 77), 50),
+]
+
+
+@pytest.mark.parametrize("kind,make,n_in", LAYER_SWEEP)
+@pytest.mark.parametrize("T", [1, 63, 1000])
+def test_layer_vs_oracle(kind, make, n_in, T):
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(7)
+    m = make(K).to(_dev())
+    x = (torch.randn(T, n_in, generator=torch.Generator().manual_seed(T)) * 1.2)
+    if kind == "efficientkan" and x.numel() >= 6:  # knots, span edges, outside the span
+        x.view(-1)[:6] = torch.tensor([-2.2, 2.2, -1.0, 0.2, 3.0, -2.6])
+    xg = x.to(_dev()).requires_grad_(True)
+    if kind == "vanilla":
+        y = ops.kan_apply(xg, make_spec([m]), [slots_of(m)])
+    else:
+        y = m(xg)
+    yo, xc, sd = _oracle_layer(kind, m, x)
+    assert y.shape == yo.shape
+    assert relerr(y, yo) < TOL_FP32
+    dy = torch.randn(y.shape, generator=torch.Generator().manual_seed(99))
+    y.backward(dy.to(_dev()))
+    yo.backward(dy)
+    assert relerr(xg.grad, xc.grad) < TOL_GRAD
+    for k, p in m.named_parameters():
+        if not p.requires_grad:
+            continue
+        assert relerr(p.grad, sd[k].grad) < TOL_GRAD, k
+
+
+def test_empty_batch():
+    import kan_vit_b200 as K
+    m = K.KANLinear(8, 8).to(_dev())
+    y = m(torch.empty(0, 8, device=_dev()))
+    assert y.shape == (0, 8)
+
+
+def test_shape_mismatch_raises_like_reference():
+    import kan_vit_b200 as K
+    m = K.KANLinear(8, 8).to(_dev())
+    with pytest.raises(AssertionError):
+        m(torch.zeros(4, 9, device=_dev()))
+    with pytest.raises(ValueError):
+        K.VisionTransformer((1, 28, 28), type="nope")
+    with pytest.raises(AssertionError):
+        K.VisionTransformer((1, 28, 28), n_patches=5)
+
+
+@pytest.mark.parametrize("kind", ["efficientkan", "cheby", "fast", "sine", "vanilla"])
+def test_vit_cfg_shapes_vs_oracle(kind):
+    """BASELINE config 1/2 geometry (1x28x28, n_patches 7, d 64, depth 4, heads 2) at batch 8."""
+    import kan_vit_b200 as K
+    from oracle import kan_oracle as O
+    torch.manual_seed(3)
+    v = K.VisionTransformer((1, 28, 28), 7, 4, 64, 2, 10, kind).to(_dev())
+    img = torch.randn(8, 1, 28, 28, generator=torch.Generator().manual_seed(5))
+    y = v(img.to(_dev()))
+    sd = {k: t.detach().cpu().clone().requires_grad_(t.is_floating_point()) for k, t in v.state_dict().items()}
+    yo = O.vit_forward(img, sd, n_patches=7, n_blocks=4, n_heads=2, kind=kind)
+    assert relerr(y, yo) < TOL_FP32
+    dy = torch.randn(y.shape, generator=torch.Generator().manual_seed(6))
+    y.backward(dy.to(_dev()))
+    yo.backward(dy)
+    for k, p in v.named_parameters():
+        if not p.requires_grad:
+            continue
+        ref = sd[k].grad
+        if ref.abs().max() < 1e-6:
+            assert p.grad.abs().max() < 1e-5, k
+            continue
+        assert relerr(p.grad, ref) < 5e-5, k  # depth-4 chain of fp32 reductions
+
+
+def test_full_size_row_independence_cfg2():
+    """Size-independent property at BASELINE config 2's full batch (cheby ViT, B=1024): every op of
+    the path is per-sample, so the logits of a sub-batch must equal the same rows of the full
+    batch bit for bit, and weight gradients must add over a split of the batch."""
+    import kan_vit_b200 as K
+    torch.manual_seed(11)
+    v = K.VisionTransformer((1, 28, 28), 7, 4, 64, 2, 10, "cheby").to(_dev())
+    img = torch.randn(1024, 1, 28, 28, device=_dev())
+    with torch.no_grad():
+        full = v(img)
+        part = v(img[100:228])
+    assert torch.equal(full[100:228], part)
+    dy = torch.randn_like(full)
+    v.zero_grad()
+    v(img).backward(dy)
+    g_full = {k: p.grad.clone() for k, p in v.named_parameters() if p.grad is not None}
+    v.zero_grad()
+    v(img[:512]).backward(dy[:512])
+    v(img[512:]).backward(dy[512:])
+    for k, p in v.named_parameters():
+        if p.grad is None or g_full[k].abs().max() < 1e-6:
+            continue
+        assert relerr(p.grad, g_full[k]) < 1e-4, k

@@ -1,0 +1,106 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/kanvit_b200.h
+declares (no compute calls), the modules mirror the reference's state_dict, argument validation
+returns error codes instead of aborting."""
+import ctypes as C
+import json
+import os
+import re
+
+import pytest
+import torch
+
+from conftest import GOLDEN, ROOT
+
+
+def _lib():
+    from kan_vit_b200 import _lib as L
+    return L, L.load()
+
+
+def test_library_exports_every_declared_symbol():
+    L, lib = _lib()
+    header = open(os.path.join(ROOT, "include", "kanvit_b200.h")).read()
+    declared = set(re.findall(r"\b(kv_[a-z0-9_]+)\s*\(", header))
+    declared -= {"kv_status", "kv_family"}
+    assert declared, "no declarations found"
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in the header but not exported"
+    for name in L.EXPORTS:
+        assert name in declared, f"{name} bound in Python but not declared in the header"
+    assert lib.kv_version() == 1
+    assert lib.kv_status_string(-2).decode() == "shape not supported"
+
+
+def test_bad_arguments_return_codes_without_a_gpu():
+    L, lib = _lib()
+    d = L.KanDesc(L.KV_EFFKAN, 4, 8, 8, 1, 1, 9, 5, 3, 8, 8, 0, 0, 0, 0, 1.0, 8 * 12, 0)
+    assert lib.kv_kan_fparam_count(C.byref(d)) == 8 * 12
+    assert lib.kv_kan_fwd(C.byref(d), None, None, None, None, None, None, None, None, None, None, None) == -1
+    d.M = 7  # inconsistent with grid_size + spline_order + 1
+    assert lib.kv_kan_fwd(C.byref(d), 1, 1, None, 1, None, None, None, None, None, 1, None) == -2
+    d.family = 42
+    assert lib.kv_kan_fwd(C.byref(d), 1, 1, None, 1, None, None, None, None, None, 1, None) == -3
+    assert lib.kv_patchify(1, 1, 2, 1, 28, 28, 5, None) == -2  # 28 % 5 != 0 (model.py:58-59)
+    assert lib.kv_attn_fwd(1, None, 1, 1, 1, 50, 2, 4096, None) == -2
+
+
+@pytest.mark.parametrize("name,args", [
+    ("cfg1_efficientkan", dict(chw=(1, 28, 28), n_patches=7, n_blocks=4, d_hidden=64, n_heads=2, out_d=10, type="efficientkan")),
+    ("cfg3_fast", dict(chw=(3, 32, 32), n_patches=4, n_blocks=6, d_hidden=192, n_heads=8, out_d=10, type="fast")),
+    ("cfg3_sine", dict(chw=(3, 32, 32), n_patches=4, n_blocks=6, d_hidden=192, n_heads=8, out_d=10, type="sine")),
+    ("cfg2_cheby", dict(chw=(1, 28, 28), n_patches=7, n_blocks=4, d_hidden=64, n_heads=2, out_d=10, type="cheby")),
+    ("vanilla", dict(chw=(1, 28, 28), n_patches=7, n_blocks=2, d_hidden=64, n_heads=2, out_d=10, type="vanilla")),
+])
+def test_state_dict_matches_reference(name, args):
+    import kan_vit_b200 as K
+    keys = json.load(open(os.path.join(GOLDEN, "state_dict_keys.json")))[name]
+    sd = K.VisionTransformer(**args).state_dict()
+    assert list(sd) == list(keys) or set(sd) == set(keys)
+    for k, shape in keys.items():
+        assert list(sd[k].shape) == shape, k
+
+
+def test_same_seed_same_init_as_reference():
+    """reset_parameters draws in the reference's order: with the reference's seed the golden
+    weights are reproduced exactly (KANLinear lstsq fit included, within solver noise)."""
+    import kan_vit_b200 as K
+    from conftest import load_golden
+    g = load_golden("layer_cheby")
+    torch.manual_seed(2)
+    m = K.ChebyKANLayer(16, 24, 4)
+    assert torch.equal(m.cheby_coeffs.detach(), g.t("sd/cheby_coeffs"))
+    g = load_golden("layer_sine")
+    torch.manual_seed(4)
+    m = K.SineKANLayer(16, 24)
+    for k, v in m.state_dict().items():
+        assert torch.equal(v, g.t("sd/" + k)), k
+    g = load_golden("layer_effkan")
+    torch.manual_seed(0)
+    m = K.KANLinear(16, 24)
+    assert torch.equal(m.base_weight.detach(), g.t("sd/base_weight"))
+    assert torch.allclose(m.spline_weight.detach(), g.t("sd/spline_weight"), atol=1e-6)
+    assert torch.equal(m.spline_scaler.detach(), g.t("sd/spline_scaler"))
+
+
+def test_no_cpu_fallback():
+    import kan_vit_b200 as K
+    from kan_vit_b200._lib import KanVitError
+    if torch.cuda.is_available():
+        pytest.skip("checks the CPU-tensor error path")
+    m = K.ChebyKANLayer(4, 4, 3)
+    with pytest.raises(KanVitError):
+        m(torch.zeros(2, 4))
+
+
+def test_reference_quirks_kept():
+    import kan_vit_b200 as K
+    m = K.NaiveFourierKANLayer(4, 4, 3, smootorch_initialization=True)
+    assert m.fouriercoeffs.shape == (2, 4, 4, 3)
+    assert K.ChebyKANLayer(4, 6, 3).arange.dtype == torch.int64
+    f = K.FastKANLayer(4, 6)
+    assert not f.rbf.grid.requires_grad and "rbf.grid" in f.state_dict()
+    s = K.SineKANLayer(4, 6, 'cpu', 5)
+    assert s.freq.shape == (1, 1, 1, 5) and s.phase.shape == (1, 1, 4, 5) and "phase" in s.state_dict()
+    v = K.VisionTransformer((1, 28, 28))
+    assert "pos_embeddings" not in v.state_dict()
+    K.MSA(16, 2, type="bogus")  # the reference swallows the error at construction (attention.py:174-176)
