@@ -13,7 +13,7 @@
  *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), does
  *     no allocation and no synchronisation; the caller owns all memory
  *   - return value: 0 on success, a negative kv_status otherwise (never aborts)
- *   - re-entrant: no mutable global state
+ *   - re-entrant: no mutable global state besides a launch counter and a per-thread error string
  */
 #ifndef KANVIT_B200_H
 #define KANVIT_B200_H
@@ -89,6 +89,8 @@ typedef struct {
 int kv_version(void);
 const char* kv_status_string(int status);
 const char* kv_last_cuda_error(void);
+/* Kernels launched by this library since it was loaded (diagnostic counter; bench.py reports it). */
+unsigned long long kv_launch_count(void);
 
 /* Number of fp32 prologue parameters per group for a family:
  *   effkan  in*(G+2k+1)  knot vectors `grid` (models/effkan.py:45-54)

@@ -59,7 +59,7 @@ _SIGNATURES = {
     "kv_gather_rows": [_P, _P, _I, _I, _I, _P],
     "kv_scatter_rows": [_P, _P, _I, _I, _I, _P],
 }
-EXPORTS = ["kv_version", "kv_status_string", "kv_last_cuda_error"] + list(_SIGNATURES)
+EXPORTS = ["kv_version", "kv_status_string", "kv_last_cuda_error", "kv_launch_count"] + list(_SIGNATURES)
 
 _lib = None
 
@@ -84,6 +84,8 @@ def load():
     lib.kv_status_string.argtypes = [C.c_int]
     lib.kv_last_cuda_error.restype = C.c_char_p
     lib.kv_last_cuda_error.argtypes = []
+    lib.kv_launch_count.restype = C.c_ulonglong
+    lib.kv_launch_count.argtypes = []
     for name, args in _SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype = C.c_int

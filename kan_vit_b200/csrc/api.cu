@@ -7,6 +7,7 @@
 namespace kv {
 
 thread_local char g_cuda_err[256] = "";
+unsigned long long g_launches = 0;
 
 int record_cuda_error(cudaError_t e, const char* where) {
   snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s", where, cudaGetErrorString(e));
@@ -302,6 +303,8 @@ const char* kv_status_string(int status) {
 
 const char* kv_last_cuda_error(void) { return g_cuda_err; }
 
+unsigned long long kv_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
 int kv_kan_fparam_count(const kv_kan_desc_t* d) {
   if (d == nullptr) return KV_ERR_BAD_ARG;
   if (d->family < KV_LINEAR || d->family > KV_FOURIER) return KV_ERR_BAD_FAMILY;
@@ -334,9 +337,9 @@ int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32
 
 int kv_row_stats(const float* X, int T, int ldx, int n_slices, int width, float eps, float* mean,
                  float* rstd, void* stream) {
+  if (T == 0) return KV_OK;
   if (X == nullptr || mean == nullptr || rstd == nullptr || T < 0 || n_slices <= 0 || width <= 0)
     return KV_ERR_BAD_ARG;
-  if (T == 0) return KV_OK;
   const long long total = (long long)T * n_slices;
   int blocks = (int)((total + 7) / 8);
   if (blocks > 148 * 8) blocks = 148 * 8;
@@ -350,6 +353,7 @@ int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, cons
                const float* residual, const float* pos, float* Y, void* stream) {
   int rc = check_desc(d);
   if (rc != KV_OK) return rc;
+  if (d->T == 0) return KV_OK;
   if (X == nullptr || Y == nullptr) return KV_ERR_BAD_ARG;
   if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;
   if (d->family == KV_FASTKAN && !(d->flags & KV_FLAG_NO_LAYERNORM) && (mean == nullptr || rstd == nullptr))
@@ -371,6 +375,7 @@ int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, co
                      void* stream) {
   int rc = check_desc(d);
   if (rc != KV_OK) return rc;
+  if (d->T == 0) return KV_OK;
   if (X == nullptr || dY == nullptr || dX == nullptr) return KV_ERR_BAD_ARG;
   if ((d->flags & KV_FLAG_RELU) && act_mask == nullptr) return KV_ERR_BAD_ARG;
   if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;
@@ -395,6 +400,7 @@ int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, c
                       float* dbias, void* stream) {
   int rc = check_desc(d);
   if (rc != KV_OK) return rc;
+  if (d->T == 0) return KV_OK;
   if (X == nullptr || dY == nullptr || dWp == nullptr) return KV_ERR_BAD_ARG;
   if ((d->flags & KV_FLAG_RELU) && act_mask == nullptr) return KV_ERR_BAD_ARG;
   if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;

@@ -11,8 +11,12 @@ namespace kv {
 extern thread_local char g_cuda_err[256];
 int record_cuda_error(cudaError_t e, const char* where);
 
+// kernels launched by this library since load (diagnostic; read by kv_launch_count)
+extern unsigned long long g_launches;
+
 #define KV_CHECK_LAUNCH(where)                                   \
   do {                                                           \
+    __atomic_fetch_add(&kv::g_launches, 1ull, __ATOMIC_RELAXED); \
     cudaError_t _e = cudaGetLastError();                         \
     if (_e != cudaSuccess) return kv::record_cuda_error(_e, where); \
   } while (0)

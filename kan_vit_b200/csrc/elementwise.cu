@@ -181,8 +181,8 @@ using namespace kv;
 
 extern "C" int kv_layernorm_fwd(const float* X, const float* gamma, const float* beta, float* Y,
                                 float* mean, float* rstd, int T, int d, int ldx, float eps, void* stream) {
-  if (X == nullptr || Y == nullptr || T < 0 || d <= 0 || ldx < d) return KV_ERR_BAD_ARG;
   if (T == 0) return KV_OK;
+  if (X == nullptr || Y == nullptr || T < 0 || d <= 0 || ldx < d) return KV_ERR_BAD_ARG;
   int blocks = ceil_div(T, LN_WARPS);
   if (blocks > 148 * 8) blocks = 148 * 8;
   layernorm_fwd_kernel<<<blocks, LN_THREADS, 0, (cudaStream_t)stream>>>(X, gamma, beta, Y, mean, rstd, T, d, ldx, eps);
@@ -194,6 +194,7 @@ extern "C" int kv_layernorm_bwd(const float* X, const float* dY, const float* ga
                                 const float* rstd, const float* dresidual, float* dX, float* dgamma,
                                 float* dbeta, int T, int d, int ldx, float eps, void* stream) {
   (void)eps;
+  if (T == 0) return KV_OK;
   if (X == nullptr || dY == nullptr || mean == nullptr || rstd == nullptr || dX == nullptr || T < 0 ||
       d <= 0 || ldx < d)
     return KV_ERR_BAD_ARG;

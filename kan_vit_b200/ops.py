@@ -33,6 +33,29 @@ def _require_cuda(*tensors):
             raise L.KanVitError("kan_vit_b200 ops need CUDA tensors (there is no CPU path)")
 
 
+# Optional kernel timing hook (bench.py): when PROFILE is a dict, calls whose name it selects
+# are bracketed by CUDA events on the launching stream; entries are (start, end, work) with
+# work = algorithmic FLOPs (GEMM-like kernels) or bytes (memory-bound kernels) of that call.
+PROFILE = None
+PROFILE_ONLY = None  # None = every call, else a set of names
+
+
+def _call(name, fn, *args, work=0.0):
+    if PROFILE is None or (PROFILE_ONLY is not None and name not in PROFILE_ONLY):
+        L.check(fn(*args), name)
+        return
+    s = torch.cuda.Event(enable_timing=True)
+    e = torch.cuda.Event(enable_timing=True)
+    s.record()
+    L.check(fn(*args), name)
+    e.record()
+    PROFILE.setdefault(name, []).append((s, e, work))
+
+
+def _kan_flops(spec, T):
+    return 2.0 * T * spec.in_features * spec.out_features * spec.M * spec.n_groups
+
+
 class KanSpec:
     """Static description of one KAN / Linear layer, or of n_groups equal-shaped layers
     applied to column slices of one activation matrix (kv_kan_desc_t without T / strides)."""
@@ -103,9 +126,8 @@ class KanSpec:
             flat[q * L.KV_PTRS_PER_GROUP + _FAMILY_BIAS_SLOT[self.family]] is not None for q in range(g))
         bias = torch.empty((g, o), dtype=torch.float32, device=device) if has_bias else None
         d = self.desc(0, self.n_slices * self.in_features, g * o)
-        L.check(lib.kv_kan_pack(C.byref(d), tbl.data_ptr(), wp.data_ptr(), None, None,
-                                fp.data_ptr() if self.fparam_stride else None, L.ptr(bias), _stream()),
-                "kv_kan_pack")
+        _call("kv_kan_pack", lib.kv_kan_pack, C.byref(d), tbl.data_ptr(), wp.data_ptr(), None, None,
+                                fp.data_ptr() if self.fparam_stride else None, L.ptr(bias), _stream())
         pk = {"wp": wp, "fp": fp if self.fparam_stride else None, "bias": bias, "tbl": tbl}
         self._pack_cache = (key, pk)
         return pk
@@ -152,20 +174,20 @@ class _KanFn(torch.autograd.Function):
         if spec.family == L.KV_FASTKAN and not (spec.flags & L.KV_FLAG_NO_LAYERNORM):
             mean = torch.empty((T, spec.n_slices), dtype=torch.float32, device=x.device)
             rstd = torch.empty_like(mean)
-            L.check(lib.kv_row_stats(x.data_ptr(), T, n_in, spec.n_slices, spec.in_features, 1e-5,
-                                     mean.data_ptr(), rstd.data_ptr(), _stream()), "kv_row_stats")
+            _call("kv_row_stats", lib.kv_row_stats, x.data_ptr(), T, n_in, spec.n_slices, spec.in_features, 1e-5,
+                                     mean.data_ptr(), rstd.data_ptr(), _stream())
         y = torch.empty((rows, n_out), dtype=torch.float32, device=x.device)
         if residual is not None:
             assert residual.shape == y.shape and residual.is_contiguous()
         if pos is not None:
             assert pos.is_contiguous() and pos.shape[-1] == n_out
-        L.check(lib.kv_kan_fwd(C.byref(d), x.data_ptr(), pk["wp"].data_ptr(), None, L.ptr(pk["fp"]),
+        _call("kv_kan_fwd", lib.kv_kan_fwd, C.byref(d), x.data_ptr(), pk["wp"].data_ptr(), None, L.ptr(pk["fp"]),
                                L.ptr(pk["bias"]), L.ptr(mean), L.ptr(rstd), L.ptr(residual), L.ptr(pos),
-                               y.data_ptr(), _stream()), "kv_kan_fwd")
+                               y.data_ptr(), _stream())
         if v_class is not None:
             assert rows_in > 0 and row_shift == 1 and spec.n_groups == 1
-            L.check(lib.kv_cls_rows_fwd(v_class.data_ptr(), L.ptr(pos), y.data_ptr(), T // rows_in,
-                                        rows_out, n_out, _stream()), "kv_cls_rows_fwd")
+            _call("kv_cls_rows_fwd", lib.kv_cls_rows_fwd, v_class.data_ptr(), L.ptr(pos), y.data_ptr(), T // rows_in,
+                                        rows_out, n_out, _stream())
         ctx.spec, ctx.cfg, ctx.flat, ctx.pk = spec, cfg, flat, pk
         ctx.d = d
         ctx.has_res, ctx.has_cls = residual is not None, v_class is not None
@@ -193,40 +215,37 @@ class _KanFn(torch.autograd.Function):
             dxn = None
             if mean is not None:
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
-            L.check(lib.kv_kan_bwd_input(C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
+            _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
                                          pk["wp"].data_ptr(), None, L.ptr(pk["fp"]), L.ptr(mean),
-                                         L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st),
-                    "kv_kan_bwd_input")
+                                         L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st)
             if dxn is not None:
-                L.check(lib.kv_fastkan_ln_bwd(C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
+                _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
                                               mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(),
-                                              dfp.data_ptr(), st), "kv_fastkan_ln_bwd")
+                                              dfp.data_ptr(), st)
         elif need_w and spec.family in (L.KV_SINE, L.KV_FASTKAN):
             # d freq / d layernorm.{weight,bias} come out of the input-gradient pass
             dx_tmp = torch.empty_like(x)
             dxn = None
             if mean is not None:
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
-            L.check(lib.kv_kan_bwd_input(C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
+            _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
                                          pk["wp"].data_ptr(), None, L.ptr(pk["fp"]), L.ptr(mean),
-                                         L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st),
-                    "kv_kan_bwd_input")
+                                         L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st)
             if dxn is not None:
-                L.check(lib.kv_fastkan_ln_bwd(C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
+                _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
                                               mean.data_ptr(), rstd.data_ptr(), dx_tmp.data_ptr(),
-                                              dfp.data_ptr(), st), "kv_fastkan_ln_bwd")
+                                              dfp.data_ptr(), st)
         if need_w:
             dwp = torch.zeros((g, o, K), dtype=torch.float32, device=dev)
             dbias = torch.zeros((g, o), dtype=torch.float32, device=dev) if pk["bias"] is not None else None
-            L.check(lib.kv_kan_bwd_weight(C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
+            _call("kv_kan_bwd_weight", lib.kv_kan_bwd_weight, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
                                           L.ptr(pk["fp"]), L.ptr(mean), L.ptr(rstd), dwp.data_ptr(),
-                                          L.ptr(dbias), st), "kv_kan_bwd_weight")
+                                          L.ptr(dbias), st)
             off_t, meta, total = spec.grad_layout(flat, dev)
             gflat = torch.empty((total,), dtype=torch.float32, device=dev)
             gtbl = torch.where(off_t >= 0, off_t + gflat.data_ptr(), torch.zeros_like(off_t))
-            L.check(lib.kv_kan_unpack_grads(C.byref(d), dwp.data_ptr(), L.ptr(dfp), L.ptr(dbias),
-                                            pk["tbl"].data_ptr(), gtbl.data_ptr(), st),
-                    "kv_kan_unpack_grads")
+            _call("kv_kan_unpack_grads", lib.kv_kan_unpack_grads, C.byref(d), dwp.data_ptr(), L.ptr(dfp), L.ptr(dbias),
+                                            pk["tbl"].data_ptr(), gtbl.data_ptr(), st)
             for idx, m in enumerate(meta):
                 if m is not None and flat[idx].requires_grad:
                     grads[idx] = gflat[m[0]:m[0] + m[1]].view(m[2])
@@ -235,8 +254,7 @@ class _KanFn(torch.autograd.Function):
         if ctx.has_cls:
             n_out = g * o
             dcls = torch.empty((1, n_out), dtype=torch.float32, device=dev)
-            L.check(lib.kv_cls_rows_bwd(dy.data_ptr(), dcls.data_ptr(), T // d.rows_in, d.rows_out, n_out, st),
-                    "kv_cls_rows_bwd")
+            _call("kv_cls_rows_bwd", lib.kv_cls_rows_bwd, dy.data_ptr(), dcls.data_ptr(), T // d.rows_in, d.rows_out, n_out, st)
         return (dx, dres, dcls, None, None, None) + tuple(grads)
 
 
@@ -264,8 +282,8 @@ class _AttnFn(torch.autograd.Function):
         assert qkv.is_contiguous() and qkv.shape == (B * N, 3 * H * dh)
         out = torch.empty((B * N, H * dh), dtype=torch.float32, device=qkv.device)
         lse = torch.empty((B, H, N), dtype=torch.float32, device=qkv.device)
-        L.check(lib.kv_attn_fwd(qkv.data_ptr(), L.ptr(residual), out.data_ptr(), lse.data_ptr(),
-                                B, N, H, dh, _stream()), "kv_attn_fwd")
+        _call("kv_attn_fwd", lib.kv_attn_fwd, qkv.data_ptr(), L.ptr(residual), out.data_ptr(), lse.data_ptr(),
+                                B, N, H, dh, _stream())
         ctx.save_for_backward(qkv, lse)
         ctx.dims = (B, N, H, dh)
         ctx.has_res = residual is not None
@@ -278,8 +296,8 @@ class _AttnFn(torch.autograd.Function):
         B, N, H, dh = ctx.dims
         dout = dout.contiguous()
         dqkv = torch.empty_like(qkv)
-        L.check(lib.kv_attn_bwd(qkv.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
-                                B, N, H, dh, _stream()), "kv_attn_bwd")
+        _call("kv_attn_bwd", lib.kv_attn_bwd, qkv.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
+                                B, N, H, dh, _stream())
         return dqkv, (dout if ctx.has_res else None), None, None, None, None
 
 
@@ -298,8 +316,8 @@ class _LayerNormFn(torch.autograd.Function):
         y = torch.empty((T, d), dtype=torch.float32, device=x.device)
         mean = torch.empty((T,), dtype=torch.float32, device=x.device)
         rstd = torch.empty_like(mean)
-        L.check(lib.kv_layernorm_fwd(x.data_ptr(), L.ptr(gamma), L.ptr(beta), y.data_ptr(), mean.data_ptr(),
-                                     rstd.data_ptr(), T, d, ldx, eps, _stream()), "kv_layernorm_fwd")
+        _call("kv_layernorm_fwd", lib.kv_layernorm_fwd, x.data_ptr(), L.ptr(gamma), L.ptr(beta), y.data_ptr(), mean.data_ptr(),
+                                     rstd.data_ptr(), T, d, ldx, eps, _stream())
         ctx.save_for_backward(x, gamma, mean, rstd)
         ctx.eps, ctx.ldx = eps, ldx
         return y
@@ -313,9 +331,9 @@ class _LayerNormFn(torch.autograd.Function):
         dx = torch.empty((T, d), dtype=torch.float32, device=x.device)
         dgamma = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
         dbeta = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
-        L.check(lib.kv_layernorm_bwd(x.data_ptr(), dy.data_ptr(), L.ptr(gamma), mean.data_ptr(),
+        _call("kv_layernorm_bwd", lib.kv_layernorm_bwd, x.data_ptr(), dy.data_ptr(), L.ptr(gamma), mean.data_ptr(),
                                      rstd.data_ptr(), None, dx.data_ptr(), L.ptr(dgamma), L.ptr(dbeta),
-                                     T, d, ctx.ldx, ctx.eps, _stream()), "kv_layernorm_bwd")
+                                     T, d, ctx.ldx, ctx.eps, _stream())
         return dx, dgamma, dbeta, None, None
 
 
@@ -335,8 +353,7 @@ class _PatchifyFn(torch.autograd.Function):
         ph, pw = H // n_patches, W // n_patches
         patches = torch.empty((B, n_patches * n_patches, Cc * ph * pw), dtype=torch.float32,
                               device=images.device)
-        L.check(lib.kv_patchify(images.data_ptr(), patches.data_ptr(), B, Cc, H, W, n_patches, _stream()),
-                "kv_patchify")
+        _call("kv_patchify", lib.kv_patchify, images.data_ptr(), patches.data_ptr(), B, Cc, H, W, n_patches, _stream())
         ctx.dims = (B, Cc, H, W, n_patches)
         return patches
 
@@ -346,8 +363,7 @@ class _PatchifyFn(torch.autograd.Function):
         B, Cc, H, W, n_patches = ctx.dims
         dpatches = dpatches.contiguous()
         dimg = torch.empty((B, Cc, H, W), dtype=torch.float32, device=dpatches.device)
-        L.check(lib.kv_patchify_bwd(dpatches.data_ptr(), dimg.data_ptr(), B, Cc, H, W, n_patches, _stream()),
-                "kv_patchify_bwd")
+        _call("kv_patchify_bwd", lib.kv_patchify_bwd, dpatches.data_ptr(), dimg.data_ptr(), B, Cc, H, W, n_patches, _stream())
         return dimg, None
 
 

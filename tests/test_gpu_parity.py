@@ -14,6 +14,12 @@ pytestmark = pytest.mark.gpu
 
 TOL_FP32 = 1e-5
 TOL_GRAD = 2e-5  # gradients pass through one more fp32 reduction (over T) than outputs
+ATOL_GRAD = 1e-8  # floor for gradients that are a cancelling sum (SineKAN d freq ~1e-5 from terms ~1e-2)
+
+
+def grad_close(got, ref, tol=TOL_GRAD):
+    got, ref = got.detach().double().cpu(), ref.detach().double().cpu()
+    return (got - ref).abs().max().item() <= tol * ref.abs().max().item() + ATOL_GRAD
 
 
 def _dev():
@@ -73,7 +79,7 @@ def test_matches_reference_golden(case):
         if ref.abs().max() < 1e-6:  # analytically zero (key bias under softmax)
             assert got.abs().max() < 1e-5, k
             continue
-        assert relerr(got, ref) < TOL_GRAD, k
+        assert grad_close(got, ref), (k, relerr(got, ref))
 
 
 def test_patchify_and_pos_bit_exact():
@@ -137,7 +143,7 @@ def test_layer_vs_oracle(kind, make, n_in, T):
     for k, p in m.named_parameters():
         if not p.requires_grad:
             continue
-        assert relerr(p.grad, sd[k].grad) < TOL_GRAD, k
+        assert grad_close(p.grad, sd[k].grad), (k, relerr(p.grad, sd[k].grad))
 
 
 def test_empty_batch():
@@ -160,27 +166,40 @@ def test_shape_mismatch_raises_like_reference():
 
 @pytest.mark.parametrize("kind", ["efficientkan", "cheby", "fast", "sine", "vanilla"])
 def test_vit_cfg_shapes_vs_oracle(kind):
-    """BASELINE config 1/2 geometry (1x28x28, n_patches 7, d 64, depth 4, heads 2) at batch 8."""
+    """BASELINE config 1/2 geometry (1x28x28, n_patches 7, d 64, depth 4, heads 2) at batch 8.
+
+    Through 4 blocks the fp32 oracle itself drifts from exact arithmetic (summation order, ReLU
+    units whose pre-activation is ~0 flip their mask), so gradients are judged against the
+    float64 oracle: our error must be within 5e-5, or no worse than twice the fp32 oracle's own
+    error against float64 ("who is closer to fp64 settles the dispute")."""
     import kan_vit_b200 as K
     from oracle import kan_oracle as O
     torch.manual_seed(3)
     v = K.VisionTransformer((1, 28, 28), 7, 4, 64, 2, 10, kind).to(_dev())
     img = torch.randn(8, 1, 28, 28, generator=torch.Generator().manual_seed(5))
     y = v(img.to(_dev()))
-    sd = {k: t.detach().cpu().clone().requires_grad_(t.is_floating_point()) for k, t in v.state_dict().items()}
-    yo = O.vit_forward(img, sd, n_patches=7, n_blocks=4, n_heads=2, kind=kind)
-    assert relerr(y, yo) < TOL_FP32
     dy = torch.randn(y.shape, generator=torch.Generator().manual_seed(6))
     y.backward(dy.to(_dev()))
-    yo.backward(dy)
+
+    def run_oracle(dtype):
+        sd = {k: t.detach().cpu().to(dtype if t.is_floating_point() else t.dtype).clone()
+              .requires_grad_(t.is_floating_point()) for k, t in v.state_dict().items()}
+        yo = O.vit_forward(img.to(dtype), sd, n_patches=7, n_blocks=4, n_heads=2, kind=kind)
+        yo.backward(dy.to(dtype))
+        return yo, sd
+
+    y32, sd32 = run_oracle(torch.float32)
+    y64, sd64 = run_oracle(torch.float64)
+    assert relerr(y, y32) < TOL_FP32 or relerr(y, y64) <= 2 * relerr(y32, y64)
     for k, p in v.named_parameters():
         if not p.requires_grad:
             continue
-        ref = sd[k].grad
-        if ref.abs().max() < 1e-6:
+        truth = sd64[k].grad
+        if truth.abs().max() < 1e-6:
             assert p.grad.abs().max() < 1e-5, k
             continue
-        assert relerr(p.grad, ref) < 5e-5, k  # depth-4 chain of fp32 reductions
+        ours, theirs = relerr(p.grad, truth), relerr(sd32[k].grad, truth)
+        assert ours < 5e-5 or ours <= 2 * theirs, (k, ours, theirs)
 
 
 def test_full_size_row_independence_cfg2():
