@@ -27,7 +27,7 @@ import torch  # noqa: E402
 CONFIGS = {
     # name: (chw, n_patches, n_blocks, d_hidden, n_heads, out_d, type, kan_mlp, batch/GPU, cpu sample batch)
     "cfg1": ((1, 28, 28), 7, 4, 64, 2, 10, "efficientkan", False, 64, 64),
-    "cfg2": ((1, 28, 28), 7, 4, 64, 2, 10, "cheby", False, 1024, 128),
+    "cfg2": ((1, 28, 28), 7, 4, 64, 2, 10, "cheby", False, 1024, 1024),
     "cfg3_fast": ((3, 32, 32), 4, 6, 192, 8, 10, "fast", False, 1024, 32),
     "cfg3_sine": ((3, 32, 32), 4, 6, 192, 8, 10, "sine", False, 1024, 32),
     "cfg4": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", True, 64, 1),
@@ -118,7 +118,7 @@ def cpu_reference_step_fn(name, batch, seed=0):
         loss = torch.nn.functional.cross_entropy(y, lab)
         loss.backward()
         opt.step()
-        return float(loss)
+        return loss.item()
 
     return step, batch
 
@@ -156,3 +156,190 @@ def run_reference_arm(args):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def load_peaks():
+    """Roofline denominators: MEASURED_PEAKS.json (driver-written) or the profiling guide's fallback."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+# kernels whose work is counted in FLOPs (tensor roofline); the rest are counted in bytes (HBM roofline)
+FLOP_KERNELS = {"kv_kan_fwd", "kv_kan_bwd_input", "kv_kan_bwd_weight", "kv_attn_fwd", "kv_attn_bwd"}
+
+
+def profile_kernels(step_fn, n_steps):
+    """Per-entry-point device time and algorithmic work of `n_steps` steps, measured with CUDA
+    events recorded on the launching stream around every C-ABI call (kan_vit_b200.ops._call)."""
+    from kan_vit_b200 import ops
+    ops.PROFILE = {}
+    for _ in range(n_steps):
+        step_fn()
+    torch.cuda.synchronize()
+    prof, ops.PROFILE = ops.PROFILE, None
+    out = {}
+    for name, evs in prof.items():
+        ms = sum(s.elapsed_time(e) for s, e, _ in evs)
+        work = sum(w for _, _, w in evs)
+        out[name] = {"calls": len(evs) // n_steps, "ms_per_step": ms / n_steps, "work_per_step": work / n_steps,
+                     "ms_per_call": ms / len(evs), "work_per_call": work / len(evs)}
+    return out
+
+
+def run_gpu_arm(args):
+    import torch.distributed as dist
+    import kan_vit_b200 as K
+    from kan_vit_b200 import _lib as L
+    from kan_vit_b200.trainer import TrainStep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the GPU arm has no CPU fallback; use --impl reference)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = L.load()
+
+    name = args.config
+    chw, npatch, nb, d, h, out_d, kind, kan_mlp, batch, cpu_batch = CONFIGS[name]
+    if args.batch:
+        batch = args.batch
+    torch.manual_seed(0)  # identical replicas on every rank
+    model = K.VisionTransformer(chw, npatch, nb, d, h, out_d, kind, kan_mlp=kan_mlp).to(dev)
+    if world > 1:
+        for p in model.parameters():
+            dist.broadcast(p.data, 0)
+    step = TrainStep(model, lr=1e-3)
+    g = torch.Generator().manual_seed(1000 + rank)  # every rank its own shard of synthetic data
+    n_host = 4  # rotating pinned host batches for the end-to-end leg
+    host_img = [torch.randn((batch,) + tuple(chw), generator=g).pin_memory() for _ in range(n_host)]
+    host_lab = [torch.randint(0, out_d, (batch,), generator=g).pin_memory() for _ in range(n_host)]
+    dev_img = [t.to(dev) for t in host_img]
+    dev_lab = [t.to(dev) for t in host_lab]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """ms for `steps` calls of fn(i): barrier+sync, CUDA events on the launching stream, MAX over ranks."""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    def resident_step(i):
+        step(dev_img[i % n_host], dev_lab[i % n_host])
+
+    def e2e_step(i):
+        # the call a user makes: host batch in, loss value out
+        x = host_img[i % n_host].to(dev, non_blocking=True)
+        y = host_lab[i % n_host].to(dev, non_blocking=True)
+        return step(x, y).item()
+
+    # warm-up (also the first packs / allocator growth)
+    for i in range(max(args.warmup, 3)):
+        resident_step(i)
+    torch.cuda.synchronize()
+    torch.cuda.reset_peak_memory_stats(dev)
+    base_mem = torch.cuda.memory_allocated(dev)
+    resident_step(0)
+    torch.cuda.synchronize()
+    step_ws_mb = (torch.cuda.max_memory_allocated(dev) - base_mem) / 1e6
+
+    clocks = ClockSampler(local)
+    clocks.start()
+    l0 = lib.kv_launch_count()
+    ms_total = timed(resident_step, args.steps)
+    launches = lib.kv_launch_count() - l0
+    ms_e2e = timed(e2e_step, args.steps)
+    clk = clocks.stop()
+
+    # per-kernel shares for the roofline (separate pass: the events perturb the step slightly)
+    prof = profile_kernels(lambda: resident_step(0), 3)
+    peaks = load_peaks()
+    top = max(prof, key=lambda k: prof[k]["ms_per_step"])
+    t = prof[top]
+    if top in FLOP_KERNELS:
+        achieved = t["work_per_call"] / (t["ms_per_call"] * 1e-3) / 1e12
+        peak, unit, bound = peaks["bf16_tflops_sustained"], "TFLOP/s", "tensor"
+    else:
+        achieved = t["work_per_call"] / (t["ms_per_call"] * 1e-3) / 1e9
+        peak, unit, bound = peaks["hbm_gbs"], "GB/s", "hbm"
+    kernel_ms = sum(v["ms_per_step"] for v in prof.values())
+    roofline = {"bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
+                "traffic": None, "kernel": top, "kernel_ms_per_call": t["ms_per_call"],
+                "kernel_calls_per_step": t["calls"], "kernel_share_of_step": t["ms_per_step"] / kernel_ms,
+                "peak_source": peaks["source"] + " (sustained bf16 dense / copy bandwidth)",
+                "shares": {k: round(v["ms_per_step"] / kernel_ms, 4) for k, v in
+                           sorted(prof.items(), key=lambda kv: -kv[1]["ms_per_step"])}}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = torch.get_num_threads()
+        cval, cms = time_cpu(name, cpu_batch, 3, 1)
+        cpu_baseline = {"value": cval, "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": f"3 steps of batch {cpu_batch} of the same model and step "
+                                  f"(oracle/kan_oracle.py, torch CPU fp32, {cms:.0f} ms/step)"}
+
+    if rank == 0:
+        ms_step = ms_total / args.steps
+        img_b = host_img[0].numel() * host_img[0].element_size() + host_lab[0].numel() * host_lab[0].element_size()
+        line = {
+            "metric": METRIC, "value": world * batch / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if not args.bf16 else "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(name, batch), "global_batch": world * batch,
+                       "parallelism": f"dp{world}",
+                       "l2": f"no flush: one step touches {step_ws_mb:.0f} MB of activations > 126 MB L2"},
+            "e2e": {"value": world * batch / (ms_e2e / args.steps * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": img_b, "d2h_bytes_per_step": 4},
+            "gpu_launches": int(launches),
+            "clocks": clk,
+            "roofline": roofline,
+            "cpu_baseline": cpu_baseline,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS))
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the config's)")
+    ap.add_argument("--bf16", action="store_true", help="tcgen05 bf16 tensor-core path for the KAN GEMMs")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -91,7 +91,6 @@ class KanSpec:
         d = self.desc(0, 0, 0)
         self.fparam_stride = max(L.load().kv_kan_fparam_count(C.byref(d)), 0)
         self._tbl_cache = None     # (ptrs, device tensor)
-        self._pack_cache = None    # (key, packed dict)
         self._goff_cache = None    # (shapes key, offsets tensor, mask, total, views meta)
 
     @property
@@ -114,9 +113,9 @@ class KanSpec:
 
     # -- packed weights / prologue parameters (cached until a parameter is modified)
     def packed(self, flat, device, want_tc: bool):
-        key = (tuple(0 if t is None else (t.data_ptr(), t._version) for t in flat), want_tc)
-        if self._pack_cache is not None and self._pack_cache[0] == key:
-            return self._pack_cache[1]
+        # No cache across calls: fused optimizers (torch.optim.Adam(fused=True)) update parameters
+        # without bumping Tensor._version, so a (data_ptr, version) key would serve stale weights.
+        # The pack is one small memory-bound launch per layer; forward hands it to backward via ctx.
         lib = L.load()
         g, o, K = self.n_groups, self.out_features, self.in_features * self.M
         tbl = self.ptr_table(flat, device)
@@ -129,7 +128,6 @@ class KanSpec:
         _call("kv_kan_pack", lib.kv_kan_pack, C.byref(d), tbl.data_ptr(), wp.data_ptr(), None, None,
                                 fp.data_ptr() if self.fparam_stride else None, L.ptr(bias), _stream())
         pk = {"wp": wp, "fp": fp if self.fparam_stride else None, "bias": bias, "tbl": tbl}
-        self._pack_cache = (key, pk)
         return pk
 
     # -- flat gradient buffer layout (byte offsets per pointer-table slot)
@@ -183,7 +181,7 @@ class _KanFn(torch.autograd.Function):
             assert pos.is_contiguous() and pos.shape[-1] == n_out
         _call("kv_kan_fwd", lib.kv_kan_fwd, C.byref(d), x.data_ptr(), pk["wp"].data_ptr(), None, L.ptr(pk["fp"]),
                                L.ptr(pk["bias"]), L.ptr(mean), L.ptr(rstd), L.ptr(residual), L.ptr(pos),
-                               y.data_ptr(), _stream())
+                               y.data_ptr(), _stream(), work=_kan_flops(spec, T))
         if v_class is not None:
             assert rows_in > 0 and row_shift == 1 and spec.n_groups == 1
             _call("kv_cls_rows_fwd", lib.kv_cls_rows_fwd, v_class.data_ptr(), L.ptr(pos), y.data_ptr(), T // rows_in,
@@ -217,7 +215,7 @@ class _KanFn(torch.autograd.Function):
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
                                          pk["wp"].data_ptr(), None, L.ptr(pk["fp"]), L.ptr(mean),
-                                         L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st)
+                                         L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
                                               mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(),
@@ -230,7 +228,7 @@ class _KanFn(torch.autograd.Function):
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
                                          pk["wp"].data_ptr(), None, L.ptr(pk["fp"]), L.ptr(mean),
-                                         L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st)
+                                         L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
                                               mean.data_ptr(), rstd.data_ptr(), dx_tmp.data_ptr(),
@@ -240,7 +238,7 @@ class _KanFn(torch.autograd.Function):
             dbias = torch.zeros((g, o), dtype=torch.float32, device=dev) if pk["bias"] is not None else None
             _call("kv_kan_bwd_weight", lib.kv_kan_bwd_weight, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
                                           L.ptr(pk["fp"]), L.ptr(mean), L.ptr(rstd), dwp.data_ptr(),
-                                          L.ptr(dbias), st)
+                                          L.ptr(dbias), st, work=_kan_flops(spec, T))
             off_t, meta, total = spec.grad_layout(flat, dev)
             gflat = torch.empty((total,), dtype=torch.float32, device=dev)
             gtbl = torch.where(off_t >= 0, off_t + gflat.data_ptr(), torch.zeros_like(off_t))
@@ -283,7 +281,7 @@ class _AttnFn(torch.autograd.Function):
         out = torch.empty((B * N, H * dh), dtype=torch.float32, device=qkv.device)
         lse = torch.empty((B, H, N), dtype=torch.float32, device=qkv.device)
         _call("kv_attn_fwd", lib.kv_attn_fwd, qkv.data_ptr(), L.ptr(residual), out.data_ptr(), lse.data_ptr(),
-                                B, N, H, dh, _stream())
+                                B, N, H, dh, _stream(), work=4.0 * B * H * N * N * dh)
         ctx.save_for_backward(qkv, lse)
         ctx.dims = (B, N, H, dh)
         ctx.has_res = residual is not None
@@ -297,7 +295,7 @@ class _AttnFn(torch.autograd.Function):
         dout = dout.contiguous()
         dqkv = torch.empty_like(qkv)
         _call("kv_attn_bwd", lib.kv_attn_bwd, qkv.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
-                                B, N, H, dh, _stream())
+                                B, N, H, dh, _stream(), work=8.0 * B * H * N * N * dh)
         return dqkv, (dout if ctx.has_res else None), None, None, None, None
 
 
@@ -317,7 +315,7 @@ class _LayerNormFn(torch.autograd.Function):
         mean = torch.empty((T,), dtype=torch.float32, device=x.device)
         rstd = torch.empty_like(mean)
         _call("kv_layernorm_fwd", lib.kv_layernorm_fwd, x.data_ptr(), L.ptr(gamma), L.ptr(beta), y.data_ptr(), mean.data_ptr(),
-                                     rstd.data_ptr(), T, d, ldx, eps, _stream())
+                                     rstd.data_ptr(), T, d, ldx, eps, _stream(), work=8.0 * T * d)
         ctx.save_for_backward(x, gamma, mean, rstd)
         ctx.eps, ctx.ldx = eps, ldx
         return y
@@ -333,7 +331,7 @@ class _LayerNormFn(torch.autograd.Function):
         dbeta = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
         _call("kv_layernorm_bwd", lib.kv_layernorm_bwd, x.data_ptr(), dy.data_ptr(), L.ptr(gamma), mean.data_ptr(),
                                      rstd.data_ptr(), None, dx.data_ptr(), L.ptr(dgamma), L.ptr(dbeta),
-                                     T, d, ctx.ldx, ctx.eps, _stream())
+                                     T, d, ctx.ldx, ctx.eps, _stream(), work=12.0 * T * d)
         return dx, dgamma, dbeta, None, None
 
 
@@ -353,7 +351,7 @@ class _PatchifyFn(torch.autograd.Function):
         ph, pw = H // n_patches, W // n_patches
         patches = torch.empty((B, n_patches * n_patches, Cc * ph * pw), dtype=torch.float32,
                               device=images.device)
-        _call("kv_patchify", lib.kv_patchify, images.data_ptr(), patches.data_ptr(), B, Cc, H, W, n_patches, _stream())
+        _call("kv_patchify", lib.kv_patchify, images.data_ptr(), patches.data_ptr(), B, Cc, H, W, n_patches, _stream(), work=8.0 * B * Cc * H * W)
         ctx.dims = (B, Cc, H, W, n_patches)
         return patches
 
@@ -363,7 +361,7 @@ class _PatchifyFn(torch.autograd.Function):
         B, Cc, H, W, n_patches = ctx.dims
         dpatches = dpatches.contiguous()
         dimg = torch.empty((B, Cc, H, W), dtype=torch.float32, device=dpatches.device)
-        _call("kv_patchify_bwd", lib.kv_patchify_bwd, dpatches.data_ptr(), dimg.data_ptr(), B, Cc, H, W, n_patches, _stream())
+        _call("kv_patchify_bwd", lib.kv_patchify_bwd, dpatches.data_ptr(), dimg.data_ptr(), B, Cc, H, W, n_patches, _stream(), work=8.0 * B * Cc * H * W)
         return dimg, None
 
 

@@ -1,0 +1,107 @@
+"""Data-parallel training step around the hot path (the step shape of train.py:31-40 of the
+reference: zero_grad -> forward -> CrossEntropyLoss -> backward -> Adam.step), one process per GPU.
+
+The reference has no multi-GPU code at all; the path shards over the batch,
+so each rank holds a full replica and its own slice of the batch, and the only exchange step per
+iteration is the gradient all-reduce.  Gradients live in ONE flat fp32 buffer (every ``p.grad`` is
+a view into it), cut into buckets in reverse parameter order; a bucket's all-reduce is issued on
+the collective stream as soon as autograd has produced its last gradient, so the transfer
+over NVLink hides under the rest of the backward pass.  Works with any ``torch.distributed``
+backend (NCCL on the GPUs, gloo in the CPU tests).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+
+class FlatGradBuckets:
+    """All gradients of ``params`` as views into one flat buffer, all-reduced bucket by bucket."""
+
+    def __init__(self, params: List[torch.nn.Parameter], bucket_bytes: int = 32 << 20, group=None):
+        self.params = [p for p in params if p.requires_grad]
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        dev, dt = self.params[0].device, self.params[0].dtype
+        # reverse order: autograd produces the gradients of the last layers first
+        order = list(reversed(self.params))
+        offs, total = [], 0
+        for p in order:
+            offs.append(total)
+            total += (p.numel() + 3) // 4 * 4
+        self.flat = torch.zeros(total, dtype=dt, device=dev)
+        self.buckets = []          # (start, end, n_params)
+        self._bucket_of = {}
+        start, count, elems_per_bucket = 0, 0, max(bucket_bytes // self.flat.element_size(), 1)
+        for p, off in zip(order, offs):
+            p.grad = self.flat[off:off + p.numel()].view_as(p)
+            end = off + (p.numel() + 3) // 4 * 4
+            self._bucket_of[id(p)] = len(self.buckets)
+            count += 1
+            if end - start >= elems_per_bucket:
+                self.buckets.append((start, end, count))
+                start, count = end, 0
+        if count:
+            self.buckets.append((start, total, count))
+        self._pending = [0] * len(self.buckets)
+        self._handles = []
+        self._hooks = []
+        if self.world > 1:
+            for p in self.params:
+                self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
+
+    def zero(self):
+        self.flat.zero_()
+        for i, (_, _, n) in enumerate(self.buckets):
+            self._pending[i] = n
+        self._handles = []
+
+    def _on_grad(self, p):
+        b = self._bucket_of[id(p)]
+        self._pending[b] -= 1
+        if self._pending[b] == 0:
+            s, e, _ = self.buckets[b]
+            self._handles.append(dist.all_reduce(self.flat[s:e], op=dist.ReduceOp.SUM, group=self.group,
+                                                 async_op=True))
+
+    def finish(self):
+        """Wait for the collectives, reduce buckets whose hooks never fired (unused parameters),
+        and turn the sums into means."""
+        if self.world == 1:
+            return
+        for b, left in enumerate(self._pending):
+            if left > 0:
+                s, e, _ = self.buckets[b]
+                self._handles.append(dist.all_reduce(self.flat[s:e], op=dist.ReduceOp.SUM,
+                                                     group=self.group, async_op=True))
+                self._pending[b] = 0
+        for h in self._handles:
+            h.wait()
+        self._handles = []
+        self.flat.mul_(1.0 / self.world)
+
+
+class TrainStep:
+    """One training iteration of a model on this rank's batch shard."""
+
+    def __init__(self, model: torch.nn.Module, lr: float = 1e-3, bucket_bytes: int = 32 << 20,
+                 optimizer: Optional[torch.optim.Optimizer] = None):
+        self.model = model
+        params = [p for p in model.parameters() if p.requires_grad]
+        self.grads = FlatGradBuckets(params, bucket_bytes)
+        if optimizer is None:
+            fused = params[0].is_cuda
+            optimizer = torch.optim.Adam(params, lr=lr, fused=fused)
+        self.opt = optimizer
+
+    def __call__(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        self.grads.zero()
+        logits = self.model(images)
+        loss = F.cross_entropy(logits, labels)
+        loss.backward()
+        self.grads.finish()
+        self.opt.step()
+        return loss.detach()

@@ -164,6 +164,26 @@ def test_shape_mismatch_raises_like_reference():
         K.VisionTransformer((1, 28, 28), n_patches=5)
 
 
+def _min_relu_margin(v, img, kind):
+    """min |pre-activation| over every ReLU unit of the model, from the float64 oracle."""
+    from oracle import kan_oracle as O
+    seen = []
+    orig = O.F.relu
+
+    def spy(x, *a, **k):
+        seen.append(x.detach().abs().min().item())
+        return orig(x, *a, **k)
+
+    O.F.relu = spy
+    try:
+        sd = {k: (t.detach().double() if t.is_floating_point() else t) for k, t in v.state_dict().items()}
+        with torch.no_grad():
+            O.vit_forward(img.double(), sd, n_patches=7, n_blocks=4, n_heads=2, kind=kind)
+    finally:
+        O.F.relu = orig
+    return min(seen) if seen else 1.0
+
+
 @pytest.mark.parametrize("kind", ["efficientkan", "cheby", "fast", "sine", "vanilla"])
 def test_vit_cfg_shapes_vs_oracle(kind):
     """BASELINE config 1/2 geometry (1x28x28, n_patches 7, d 64, depth 4, heads 2) at batch 8.
@@ -174,9 +194,16 @@ def test_vit_cfg_shapes_vs_oracle(kind):
     error against float64 ("who is closer to fp64 settles the dispute")."""
     import kan_vit_b200 as K
     from oracle import kan_oracle as O
-    torch.manual_seed(3)
-    v = K.VisionTransformer((1, 28, 28), 7, 4, 64, 2, 10, kind).to(_dev())
     img = torch.randn(8, 1, 28, 28, generator=torch.Generator().manual_seed(5))
+    # A ReLU unit whose pre-activation is within fp32 noise of 0 makes the gradient discontinuous
+    # (seed 3 / efficientkan has one at 5.9e-9): pick the first seed whose float64 oracle keeps
+    # every pre-activation of ff.0 at least 1e-6 away from zero.
+    for seed in range(3, 40):
+        torch.manual_seed(seed)
+        v = K.VisionTransformer((1, 28, 28), 7, 4, 64, 2, 10, kind)
+        if _min_relu_margin(v, img, kind) > 1e-6:
+            break
+    v = v.to(_dev())
     y = v(img.to(_dev()))
     dy = torch.randn(y.shape, generator=torch.Generator().manual_seed(6))
     y.backward(dy.to(_dev()))
@@ -199,7 +226,11 @@ def test_vit_cfg_shapes_vs_oracle(kind):
             assert p.grad.abs().max() < 1e-5, k
             continue
         ours, theirs = relerr(p.grad, truth), relerr(sd32[k].grad, truth)
-        assert ours < 5e-5 or ours <= 2 * theirs, (k, ours, theirs)
+        # SineKAN's d freq (G values per layer) is a cancelling sum over all T*in terms, each
+        # ~1e3 times the result: fp32 summation order alone moves it by ~1e-4 relative (the fp32
+        # oracle is itself ~2e-5..1e-4 off float64 there), so it gets the looser bound.
+        tol = 3e-4 if k.endswith(".freq") else 5e-5
+        assert ours < tol or ours <= 2 * theirs, (k, ours, theirs)
 
 
 def test_full_size_row_independence_cfg2():
