@@ -110,11 +110,17 @@ int kv_kan_fparam_count(const kv_kan_desc_t* d);
  *   sine    0 amplitudes(out,in,G) 1 freq(G) 2 phase(in,G) 3 bias(out)|0
  *   fourier 0 fouriercoeffs(2,out,in,G) 1 bias(out)|0
  * Outputs (any may be NULL to skip): wp_f32 [g][out][in*M] (K index i*M+m, effkan's
- * spline_scaler folded in -- models/effkan.py:166-172,180-183), wp_bf16 same layout
- * in bf16, wpt_bf16 [g][in*M][out] bf16 (transposed, for the input-gradient GEMM),
+ * spline_scaler folded in -- models/effkan.py:166-172,180-183); wtiles_bf16 / wtiles_t_bf16:
+ * the bf16 tcgen05 operand images of the same weights for the forward / input-gradient
+ * tensor-core kernels (opaque pre-tiled layouts, sizes from kv_kan_tc_bytes; need wp_f32);
  * fparams [g][fparam_stride], bias [g][out] (zeros where the module has none). */
 int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32,
-                void* wp_bf16, void* wpt_bf16, float* fparams, float* bias, void* stream);
+                void* wtiles_bf16, void* wtiles_t_bf16, float* fparams, float* bias, void* stream);
+
+/* Bytes of the tensor-core operand images of kv_kan_pack (KV_FLAG_BF16_TC path).  Returns
+ * KV_ERR_UNSUPPORTED when the layer cannot run on the tensor-core kernels (M > 24);
+ * *wtiles_t_bytes == 0 means the input gradient runs on the fp32 kernels for this layer. */
+int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles_t_bytes);
 
 /* Per-(row, slice) mean and 1/sqrt(var+eps) over `width` consecutive columns:
  * the LayerNorm statistics of FastKANLayer.layernorm (models/fastkan.py:57,68).
@@ -129,7 +135,7 @@ int kv_row_stats(const float* X, int T, int ldx, int n_slices, int width, float 
  * expansion is evaluated on the fly in the GEMM prologue and never stored.
  * residual (nullable, same addressing as Y) and pos (nullable, [rows_out][n_groups*out])
  * are added in the epilogue; mean/rstd only for fastkan. */
-int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, const void* wp_bf16,
+int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, const void* wtiles_bf16,
                const float* fparams, const float* bias, const float* mean, const float* rstd,
                const float* residual, const float* pos, float* Y, void* stream);
 
@@ -140,7 +146,7 @@ int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, cons
  * by kv_fastkan_ln_bwd.  dfparams [g][fparam_stride] (sine: d freq accumulated with
  * atomics, must be zeroed by the caller; others untouched).  dX is OVERWRITTEN. */
 int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
-                     const float* wp_f32, const void* wpt_bf16, const float* fparams,
+                     const float* wp_f32, const void* wtiles_t_bf16, const float* fparams,
                      const float* mean, const float* rstd, float* dX, float* dXn,
                      float* dfparams, void* stream);
 

@@ -8,7 +8,8 @@ reference's own nn.Module API (akshathmangudi/KAN-ViT: model.py, attention.py, m
 from . import _lib  # noqa: F401
 from .attention import MSA
 from .model import TransformerBlock, VisionTransformer
+from .ops import get_precision, precision, set_precision
 from .models import (ChebyKANLayer, FastKANLayer, KANLinear, NaiveFourierKANLayer, SineKANLayer)
 
 __all__ = ["MSA", "TransformerBlock", "VisionTransformer", "KANLinear", "ChebyKANLayer", "FastKANLayer",
-           "SineKANLayer", "NaiveFourierKANLayer"]
+           "SineKANLayer", "NaiveFourierKANLayer", "set_precision", "get_precision", "precision"]

@@ -42,6 +42,7 @@ _DP = C.POINTER(KanDesc)
 _SIGNATURES = {
     "kv_kan_fparam_count": [_DP],
     "kv_kan_pack": [_DP, _P, _P, _P, _P, _P, _P, _P],
+    "kv_kan_tc_bytes": [_DP, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],
     "kv_row_stats": [_P, _I, _I, _I, _I, C.c_float, _P, _P, _P],
     "kv_kan_fwd": [_DP] + [_P] * 11,
     "kv_kan_bwd_input": [_DP] + [_P] * 12,

@@ -329,9 +329,22 @@ int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32
     KV_CHECK_LAUNCH("pack_fparams");
   }
   if (wtiles_bf16 != nullptr || wtiles_t_bf16 != nullptr) {
-    rc = tc_pack(*d, ptr_table, wtiles_bf16, wtiles_t_bf16, st);
+    if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;  // the operand images are cut from the fp32 pack
+    rc = tc_supported(*d);
+    if (rc != KV_OK) return rc;
+    rc = tc_pack(*d, wp_f32, wtiles_bf16, wtiles_t_bf16, st);
     if (rc != KV_OK) return rc;
   }
+  return KV_OK;
+}
+
+int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles_t_bytes) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  rc = tc_supported(*d);
+  if (rc != KV_OK) return rc;
+  if (wtiles_bytes) *wtiles_bytes = tc_wtiles_bytes(*d);
+  if (wtiles_t_bytes) *wtiles_t_bytes = tc_wtiles_t_bytes(*d);
   return KV_OK;
 }
 
@@ -383,8 +396,7 @@ int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, co
       (mean == nullptr || rstd == nullptr || dXn == nullptr))
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
-  if (d->flags & KV_FLAG_BF16_TC) {
-    if (wtiles_t_bf16 == nullptr) return KV_ERR_BAD_ARG;
+  if ((d->flags & KV_FLAG_BF16_TC) && wtiles_t_bf16 != nullptr) {
     rc = tc_supported(*d);
     if (rc != KV_OK) return rc;
     return tc_bwd_input(*d, X, dY, act_mask, wtiles_t_bf16, fparams, mean, rstd, dX, dXn, dfparams,
@@ -407,7 +419,7 @@ int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, c
   if (d->family == KV_FASTKAN && !(d->flags & KV_FLAG_NO_LAYERNORM) && (mean == nullptr || rstd == nullptr))
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
-  if (d->flags & KV_FLAG_BF16_TC) {
+  if ((d->flags & KV_FLAG_BF16_TC) && tc_bwd_weight_available(*d)) {
     rc = tc_supported(*d);
     if (rc != KV_OK) return rc;
     return tc_bwd_weight(*d, X, dY, act_mask, fparams, mean, rstd, dWp, dbias, (cudaStream_t)stream);

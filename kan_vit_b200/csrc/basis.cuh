@@ -19,6 +19,18 @@ struct BasisCtx {
   uint32_t flags;
 };
 
+__device__ __forceinline__ BasisCtx make_ctx(const kv_kan_desc_t& d, const float* fparams, int g) {
+  BasisCtx c;
+  c.fp = fparams ? fparams + (size_t)g * d.fparam_stride : nullptr;
+  c.in = d.in_features;
+  c.G = d.grid_size;
+  c.k = d.spline_order;
+  c.M = d.M;
+  c.rbf_denom = d.rbf_denom;
+  c.flags = d.flags;
+  return c;
+}
+
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 __device__ __forceinline__ float silu_grad_f(float x) {
   float s = 1.0f / (1.0f + expf(-x));

@@ -42,18 +42,6 @@ struct FastkanDotSink {  // RBF part (m < G) and base part (m == G) kept apart
   }
 };
 
-__device__ __forceinline__ BasisCtx make_ctx(const kv_kan_desc_t& d, const float* fparams, int g) {
-  BasisCtx c;
-  c.fp = fparams ? fparams + (size_t)g * d.fparam_stride : nullptr;
-  c.in = d.in_features;
-  c.G = d.grid_size;
-  c.k = d.spline_order;
-  c.M = d.M;
-  c.rbf_denom = d.rbf_denom;
-  c.flags = d.flags;
-  return c;
-}
-
 // ------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------

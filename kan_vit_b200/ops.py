@@ -39,6 +39,37 @@ def _require_cuda(*tensors):
 PROFILE = None
 PROFILE_ONLY = None  # None = every call, else a set of names
 
+# Arithmetic of the KAN / Linear GEMMs: "fp32" = exact SIMT kernels (parity 1e-5), "bf16" = tcgen05
+# tensor-core kernels with bf16 operands and fp32 accumulation in TMEM (parity 2e-2).  Activations
+# stay fp32 in HBM in both modes.
+_PRECISION = "fp32"
+
+
+def set_precision(mode: str):
+    """Select the GEMM arithmetic for subsequent forward passes: "fp32" or "bf16"."""
+    global _PRECISION
+    if mode not in ("fp32", "bf16"):
+        raise ValueError(f"precision must be 'fp32' or 'bf16', not {mode!r}")
+    _PRECISION = mode
+
+
+def get_precision() -> str:
+    return _PRECISION
+
+
+class precision:
+    """Context manager: ``with kan_vit_b200.precision("bf16"): ...``"""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        self.prev = _PRECISION
+        set_precision(self.mode)
+
+    def __exit__(self, *exc):
+        set_precision(self.prev)
+
 
 def _call(name, fn, *args, work=0.0):
     if PROFILE is None or (PROFILE_ONLY is not None and name not in PROFILE_ONLY):
@@ -91,6 +122,10 @@ class KanSpec:
         d = self.desc(0, 0, 0)
         self.fparam_stride = max(L.load().kv_kan_fparam_count(C.byref(d)), 0)
         self._tbl_cache = None     # (ptrs, device tensor)
+        a, b = C.c_size_t(0), C.c_size_t(0)
+        rc = L.load().kv_kan_tc_bytes(C.byref(self.desc(0, self.n_slices * in_features, n_groups * out_features)),
+                                      C.byref(a), C.byref(b))
+        self.tc_bytes = (a.value, b.value) if rc == 0 else None   # None: no tensor-core kernel for this shape
         self._goff_cache = None    # (shapes key, offsets tensor, mask, total, views meta)
 
     @property
@@ -125,9 +160,14 @@ class KanSpec:
             flat[q * L.KV_PTRS_PER_GROUP + _FAMILY_BIAS_SLOT[self.family]] is not None for q in range(g))
         bias = torch.empty((g, o), dtype=torch.float32, device=device) if has_bias else None
         d = self.desc(0, self.n_slices * self.in_features, g * o)
-        _call("kv_kan_pack", lib.kv_kan_pack, C.byref(d), tbl.data_ptr(), wp.data_ptr(), None, None,
+        wt = wtt = None
+        if want_tc:
+            wt = torch.empty((self.tc_bytes[0],), dtype=torch.uint8, device=device)
+            if self.tc_bytes[1]:
+                wtt = torch.empty((self.tc_bytes[1],), dtype=torch.uint8, device=device)
+        _call("kv_kan_pack", lib.kv_kan_pack, C.byref(d), tbl.data_ptr(), wp.data_ptr(), L.ptr(wt), L.ptr(wtt),
                                 fp.data_ptr() if self.fparam_stride else None, L.ptr(bias), _stream())
-        pk = {"wp": wp, "fp": fp if self.fparam_stride else None, "bias": bias, "tbl": tbl}
+        pk = {"wp": wp, "fp": fp if self.fparam_stride else None, "bias": bias, "tbl": tbl, "wt": wt, "wtt": wtt}
         return pk
 
     # -- flat gradient buffer layout (byte offsets per pointer-table slot)
@@ -166,8 +206,11 @@ class _KanFn(torch.autograd.Function):
         rows_in, rows_out, row_shift = cfg.get("rows_in", 0), cfg.get("rows_out", 0), cfg.get("row_shift", 0)
         rows = T if rows_in == 0 else (T // rows_in) * rows_out
         extra = L.KV_FLAG_RELU if cfg.get("relu") else 0
+        use_tc = _PRECISION == "bf16" and spec.tc_bytes is not None
+        if use_tc:
+            extra |= L.KV_FLAG_BF16_TC
         d = spec.desc(T, n_in, n_out, rows_in, rows_out, row_shift, extra)
-        pk = spec.packed(flat, x.device, False)
+        pk = spec.packed(flat, x.device, use_tc)
         mean = rstd = None
         if spec.family == L.KV_FASTKAN and not (spec.flags & L.KV_FLAG_NO_LAYERNORM):
             mean = torch.empty((T, spec.n_slices), dtype=torch.float32, device=x.device)
@@ -179,7 +222,7 @@ class _KanFn(torch.autograd.Function):
             assert residual.shape == y.shape and residual.is_contiguous()
         if pos is not None:
             assert pos.is_contiguous() and pos.shape[-1] == n_out
-        _call("kv_kan_fwd", lib.kv_kan_fwd, C.byref(d), x.data_ptr(), pk["wp"].data_ptr(), None, L.ptr(pk["fp"]),
+        _call("kv_kan_fwd", lib.kv_kan_fwd, C.byref(d), x.data_ptr(), pk["wp"].data_ptr(), L.ptr(pk["wt"]), L.ptr(pk["fp"]),
                                L.ptr(pk["bias"]), L.ptr(mean), L.ptr(rstd), L.ptr(residual), L.ptr(pos),
                                y.data_ptr(), _stream(), work=_kan_flops(spec, T))
         if v_class is not None:
@@ -214,7 +257,7 @@ class _KanFn(torch.autograd.Function):
             if mean is not None:
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
-                                         pk["wp"].data_ptr(), None, L.ptr(pk["fp"]), L.ptr(mean),
+                                         pk["wp"].data_ptr(), L.ptr(pk["wtt"]), L.ptr(pk["fp"]), L.ptr(mean),
                                          L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
@@ -227,7 +270,7 @@ class _KanFn(torch.autograd.Function):
             if mean is not None:
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
-                                         pk["wp"].data_ptr(), None, L.ptr(pk["fp"]), L.ptr(mean),
+                                         pk["wp"].data_ptr(), L.ptr(pk["wtt"]), L.ptr(pk["fp"]), L.ptr(mean),
                                          L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
