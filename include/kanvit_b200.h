@@ -93,7 +93,7 @@ const char* kv_last_cuda_error(void);
 unsigned long long kv_launch_count(void);
 
 /* Number of fp32 prologue parameters per group for a family:
- *   effkan  in*(G+2k+1)  knot vectors `grid` (models/effkan.py:45-54)
+ *   effkan  in*(G+2k+1)+4  knot vectors `grid` (models/effkan.py:45-54) + {uniform?, t0, 1/h, 0}
  *   fastkan 2*in+G       layernorm weight, bias, rbf.grid (models/fastkan.py:24-27,57)
  *   sine    G+in*G       freq, phase (models/sinekan.py:59-75)
  *   others  0                                                                     */

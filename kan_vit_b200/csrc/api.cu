@@ -28,7 +28,7 @@ static int family_M(const kv_kan_desc_t& d) {
 
 static int fparam_count(const kv_kan_desc_t& d) {
   switch (d.family) {
-    case KV_EFFKAN: return d.in_features * (d.grid_size + 2 * d.spline_order + 1);
+    case KV_EFFKAN: return d.in_features * (d.grid_size + 2 * d.spline_order + 1) + 4;  // + grid probe
     case KV_FASTKAN: return 2 * d.in_features + d.grid_size;
     case KV_SINE: return d.grid_size + d.in_features * d.grid_size;
     default: return 0;
@@ -146,6 +146,31 @@ __global__ void pack_fparams_kernel(const kv_kan_desc_t d, const uint64_t* __res
     else if (d.family == KV_FOURIER) s = 1;
     const float* b = s >= 0 ? slot(tbl, g, s) : nullptr;
     for (int p = tid; p < out; p += nth) bias[(size_t)g * out + p] = b ? b[p] : 0.0f;
+  }
+}
+
+// effkan: is every feature's knot vector the same uniform grid t0 + j*h?  Written behind the knots as
+// {uniform ? 1 : 0, t0, 1/h, 0}; the tensor-core kernels pick their closed-form prologue from it.
+__global__ void effkan_probe_kernel(const kv_kan_desc_t d, const uint64_t* __restrict__ tbl,
+                                    float* __restrict__ fparams) {
+  const int g = blockIdx.x;
+  const int nk = d.grid_size + 2 * d.spline_order + 1;
+  const int n = d.in_features * nk;
+  const float* grid = slot(tbl, g, 3);
+  const float t0 = grid[0], span = grid[nk - 1] - grid[0];
+  const float h = span / (float)(nk - 1);
+  int ok = (span > 0.0f) ? 1 : 0;
+  for (int p = threadIdx.x; p < n; p += blockDim.x) {
+    const int j = p % nk;
+    if (!(fabsf(grid[p] - (t0 + (float)j * h)) <= 1e-5f * span)) ok = 0;
+  }
+  ok = __syncthreads_and(ok);
+  if (threadIdx.x == 0) {
+    float* fp = fparams + (size_t)g * d.fparam_stride + n;
+    fp[0] = ok ? 1.0f : 0.0f;
+    fp[1] = t0;
+    fp[2] = ok ? 1.0f / h : 0.0f;
+    fp[3] = 0.0f;
   }
 }
 
@@ -327,12 +352,17 @@ int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32
   if (fparams != nullptr || bias != nullptr) {
     pack_fparams_kernel<<<dim3(8, d->n_groups), 256, 0, st>>>(*d, ptr_table, fparams, bias);
     KV_CHECK_LAUNCH("pack_fparams");
+    if (fparams != nullptr && d->family == KV_EFFKAN) {
+      effkan_probe_kernel<<<d->n_groups, 256, 0, st>>>(*d, ptr_table, fparams);
+      KV_CHECK_LAUNCH("effkan_probe");
+    }
   }
   if (wtiles_bf16 != nullptr || wtiles_t_bf16 != nullptr) {
     if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;  // the operand images are cut from the fp32 pack
     rc = tc_supported(*d);
     if (rc != KV_OK) return rc;
-    rc = tc_pack(*d, wp_f32, wtiles_bf16, wtiles_t_bf16, st);
+    if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;  // layout choice reads the grid probe
+    rc = tc_pack(*d, wp_f32, fparams, wtiles_bf16, wtiles_t_bf16, st);
     if (rc != KV_OK) return rc;
   }
   return KV_OK;

@@ -20,7 +20,8 @@ int tc_supported(const kv_kan_desc_t& d);
 size_t tc_wtiles_bytes(const kv_kan_desc_t& d);    // forward operand image
 size_t tc_wtiles_t_bytes(const kv_kan_desc_t& d);  // input-gradient operand image (0 = kernel not available)
 bool tc_bwd_weight_available(const kv_kan_desc_t& d);
-int tc_pack(const kv_kan_desc_t& d, const float* wp_f32, void* wtiles, void* wtiles_t, cudaStream_t st);
+int tc_pack(const kv_kan_desc_t& d, const float* wp_f32, const float* fparams, void* wtiles, void* wtiles_t,
+            cudaStream_t st);
 int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const float* fparams,
            const float* bias, const float* mean, const float* rstd, const float* residual,
            const float* pos, float* Y, cudaStream_t st);

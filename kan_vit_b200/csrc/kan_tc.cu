@@ -25,36 +25,65 @@ namespace tc {
 constexpr int BM = 128;              // rows per CTA tile (UMMA M)
 constexpr int KU = 16;               // K per unit (UMMA K for bf16)
 constexpr int A_UNIT_BYTES = BM * KU * 2;
-constexpr int NA = 24;               // A ring slots (>= max M on this path)
-constexpr int A_RING_BYTES = NA * A_UNIT_BYTES;
+constexpr int A_UNITS = 27;          // A ring capacity in units; holds A_UNITS / M whole chunks
+constexpr int A_RING_BYTES = A_UNITS * A_UNIT_BYTES;
 constexpr int B_RING_BYTES = 96 * 1024;
 constexpr int NB_MAX = 16;
+constexpr int NCH_MAX = A_UNITS;
 constexpr int N_PRODUCER_WARPS = 8;
 constexpr int NTHREADS = 32 * (2 + N_PRODUCER_WARPS);
 constexpr int BAR_BYTES = 1024;
 constexpr int SMEM_BYTES = A_RING_BYTES + B_RING_BYTES + BAR_BYTES;
 constexpr int TMEM_COLS = 512;
-constexpr int MAX_M_TC = NA;
+constexpr int MAX_M_TC = 24;
+
+// K-order of the units inside a 16-feature chunk
+enum { LAYOUT_BASIS_MAJOR = 0,  // unit m = 16 features x basis m            (every family)
+       LAYOUT_EFFKAN8 = 1 };    // units 0..7 = feature pair (2q, 2q+1) x the 8 B-splines, unit 8 = 16 x SiLU
 
 struct Geom {
   int n_chunks;  // ceil(in / 16)
   int n_units;   // n_chunks * M
   int n_tiles;   // output tiles per group
   int BN;        // outputs per tile (multiple of 16, <= 512)
-  int NB;        // B ring slots
+  int NB;        // B ring slots (units)
+  int NCH;       // A ring slots (chunks)
+  int effkan8;   // host-side candidate for LAYOUT_EFFKAN8 (the device-side grid probe decides)
   __host__ __device__ size_t tile_elems() const { return (size_t)n_units * BN * KU; }
 };
 
-__host__ __device__ inline Geom make_geom(int in, int out, int M) {
+__host__ __device__ inline Geom make_geom(const kv_kan_desc_t& d) {
   Geom g;
-  g.n_chunks = (in + KU - 1) / KU;
-  g.n_units = g.n_chunks * M;
-  const int out16 = (out + 15) / 16 * 16;
+  g.n_chunks = (d.in_features + KU - 1) / KU;
+  g.n_units = g.n_chunks * d.M;
+  const int out16 = (d.out_features + 15) / 16 * 16;
   g.n_tiles = (out16 + 511) / 512;
   g.BN = ((out16 + g.n_tiles - 1) / g.n_tiles + 15) / 16 * 16;
   int nb = B_RING_BYTES / (g.BN * KU * 2);
   g.NB = nb > NB_MAX ? NB_MAX : nb;
+  g.NCH = A_UNITS / d.M;
+  g.effkan8 = (d.family == KV_EFFKAN && d.spline_order == 3 && d.grid_size == 5) ? 1 : 0;
   return g;
+}
+
+// The layout the kernels of one group use: LAYOUT_EFFKAN8 iff the layer is the default-shaped
+// effkan AND the grid probe (written by kv_kan_pack behind the knots) found one uniform grid.
+__device__ __forceinline__ int group_layout(const kv_kan_desc_t& d, const Geom& gm, const float* fparams, int g) {
+  if (!gm.effkan8 || fparams == nullptr) return LAYOUT_BASIS_MAJOR;
+  const float* probe = fparams + (size_t)g * d.fparam_stride +
+                       (size_t)d.in_features * (d.grid_size + 2 * d.spline_order + 1);
+  return probe[0] == 1.0f ? LAYOUT_EFFKAN8 : LAYOUT_BASIS_MAJOR;
+}
+
+// (feature i, basis m) of K element (unit q of chunk c, k-half h, element e)
+__device__ __forceinline__ void unit_to_im(int layout, int M, int c, int q, int h, int e, int& i, int& m) {
+  if (layout == LAYOUT_EFFKAN8 && q < 8) {
+    i = c * KU + 2 * q + h;
+    m = e;
+  } else {
+    i = c * KU + h * 8 + e;
+    m = (layout == LAYOUT_EFFKAN8) ? 8 : q;
+  }
 }
 
 // ----------------------------------------------------------------------------------------
@@ -62,10 +91,11 @@ __host__ __device__ inline Geom make_geom(int in, int out, int M) {
 //   [g][n_tile][unit][k-half h][row group rg = BN/8][8 rows][8 elements]
 // = for every unit the no-swizzle K-major operand image (core matrix = 8 rows x 16 B).
 // ----------------------------------------------------------------------------------------
-__global__ void tc_pack_kernel(const float* __restrict__ wp, __nv_bfloat16* __restrict__ wt, int n_groups,
-                               int in, int out, int M, Geom gm) {
+__global__ void tc_pack_kernel(const kv_kan_desc_t d, const float* __restrict__ wp,
+                               const float* __restrict__ fparams, __nv_bfloat16* __restrict__ wt, Geom gm) {
   const size_t per_tile = gm.tile_elems();
-  const size_t total = (size_t)n_groups * gm.n_tiles * per_tile;
+  const size_t total = (size_t)d.n_groups * gm.n_tiles * per_tile;
+  const int in = d.in_features, out = d.out_features, M = d.M;
   const int K = in * M;
   for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (size_t)gridDim.x * blockDim.x) {
@@ -78,26 +108,42 @@ __global__ void tc_pack_kernel(const float* __restrict__ wp, __nv_bfloat16* __re
     const int nt = r % gm.n_tiles; r /= gm.n_tiles;
     const int g = (int)r;
     const int o = nt * gm.BN + rg * 8 + r8;
-    const int c = u / M, m = u - c * M;
-    const int i = c * KU + h * 8 + e;
+    const int c = u / M, q = u - c * M;
+    int i, m;
+    unit_to_im(group_layout(d, gm, fparams, g), M, c, q, h, e, i, m);
     float v = 0.0f;
     if (o < out && i < in) v = wp[((size_t)g * out + o) * K + (size_t)i * M + m];
     wt[idx] = __float2bfloat16_rn(v);
   }
 }
 
-// writes Phi_m(x) as bf16 into the A ring: unit (u0 + m) -> slot (s0 + m) mod NA
+// scattered bf16 stores of Phi_m(x) into a chunk slot (basis-major layout): unit m at m * A_UNIT_BYTES
 struct UnitSink {
   static constexpr bool kDense = true;
-  uint8_t* sA;
-  int s0;   // slot of the chunk's unit m = 0
-  int off;  // byte offset of (row, feature) inside a unit
+  uint8_t* base;  // chunk slot + byte offset of (row, feature) inside a unit
   __device__ __forceinline__ void put(int m, float v) {
-    int s = s0 + m;
-    if (s >= NA) s -= NA;
-    *reinterpret_cast<__nv_bfloat16*>(sA + s * A_UNIT_BYTES + off) = __float2bfloat16_rn(v);
+    *reinterpret_cast<__nv_bfloat16*>(base + m * A_UNIT_BYTES) = __float2bfloat16_rn(v);
   }
 };
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float fast_silu(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+__device__ __forceinline__ uint64_t shl64(uint64_t v, int n) {  // PTX shifts clamp: n >= 64 (or "negative") -> 0
+  uint64_t r;
+  asm("shl.b64 %0, %1, %2;" : "=l"(r) : "l"(v), "r"(n));
+  return r;
+}
+__device__ __forceinline__ uint64_t shr64(uint64_t v, int n) {
+  uint64_t r;
+  asm("shr.u64 %0, %1, %2;" : "=l"(r) : "l"(v), "r"(n));
+  return r;
+}
+__device__ __forceinline__ void sts128(uint8_t* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  *reinterpret_cast<uint4*>(p) = make_uint4(a, b, c, d);
+}
 
 struct FwdParams {
   kv_kan_desc_t d;
@@ -113,20 +159,168 @@ struct FwdParams {
   Geom gm;
 };
 
+// 8 consecutive features of one row (zero beyond `in` / beyond T)
+__device__ __forceinline__ void load_x8(const float* __restrict__ xrow, int i0, int in, bool row_ok, bool vec,
+                                        float (&x)[8]) {
+  if (row_ok && vec && i0 + 8 <= in) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(xrow + i0));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(xrow + i0 + 4));
+    x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
+    x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
+  } else {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) x[q] = (row_ok && i0 + q < in) ? __ldg(xrow + i0 + q) : 0.0f;
+  }
+}
+
+// ---- A producers -------------------------------------------------------------------------
+// Every producer thread owns one row r of the tile and 8 consecutive features (k-half wg) of the
+// chunk; `base` = chunk slot + the row's 16-byte lane inside a core-matrix column.
+
+// Default effkan (G=5, k=3) on a uniform grid, LAYOUT_EFFKAN8: the 8 B-spline values of ONE input are
+// one 16-byte store.  The 4 non-zero cubic pieces are packed to bf16 and shifted into place.
+__device__ __forceinline__ void effkan8_chunk(uint8_t* base, int wg, const float (&x)[8], float t0, float inv_h) {
+  float sv[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const float xv = x[q];
+    const float u = (xv - t0) * inv_h;
+    const float jf = floorf(u);
+    const float s = u - jf;
+    const int j = (int)jf;
+    const bool ok = (u >= 0.0f) && (u < 11.0f);  // x in [t_0, t_11): models/effkan.py:115
+    const float s2 = s * s, s3 = s2 * s, om = 1.0f - s;
+    const float w0 = om * om * om * (1.0f / 6.0f);
+    const float w1 = fmaf(0.5f, s3, fmaf(-1.0f, s2, 2.0f / 3.0f));
+    const float w2 = fmaf(-0.5f, s3, fmaf(0.5f, s2, fmaf(0.5f, s, 1.0f / 6.0f)));
+    const float w3 = s3 * (1.0f / 6.0f);
+    uint64_t W = (uint64_t)pack_bf16(w0, w1) | ((uint64_t)pack_bf16(w2, w3) << 32);
+    if (!ok) W = 0;
+    const int b = (j - 3) * 16;  // basis a = j-3+r sits at 16-bit lane a of the 128-bit vector
+    const uint64_t lo = shl64(W, b) | shr64(W, -b);
+    const uint64_t hi = shl64(W, b - 64) | shr64(W, 64 - b);
+    sts128(base + (wg * 4 + (q >> 1)) * A_UNIT_BYTES + (q & 1) * 2048, (uint32_t)lo, (uint32_t)(lo >> 32),
+           (uint32_t)hi, (uint32_t)(hi >> 32));
+    sv[q] = fast_silu(xv);
+  }
+  sts128(base + 8 * A_UNIT_BYTES + wg * 2048, pack_bf16(sv[0], sv[1]), pack_bf16(sv[2], sv[3]),
+         pack_bf16(sv[4], sv[5]), pack_bf16(sv[6], sv[7]));
+}
+
+// Basis-major layout, basis index outermost: 8 features x one m = one 16-byte store.
+template <int F>
+__device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const float (&x)[8], const BasisCtx& c,
+                                                  int i0, float mu, float rs) {
+  uint8_t* dst = base + wg * 2048;
+  const int M = c.M;
+  float v[8];
+  auto emit = [&](int m) {
+    sts128(dst + m * A_UNIT_BYTES, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+           pack_bf16(v[6], v[7]));
+  };
+  if (F == KV_LINEAR) {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = x[q];
+    emit(0);
+  } else if (F == KV_CHEBY) {
+    float t[8], p0[8], p1[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      t[q] = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * x[q]));  // tanh
+      p0[q] = 1.0f;
+      p1[q] = t[q];
+      v[q] = 1.0f;
+    }
+    emit(0);
+    if (M > 1) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = t[q];
+      emit(1);
+    }
+    for (int m = 2; m < M; ++m) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        v[q] = 2.0f * t[q] * p1[q] - p0[q];
+        p0[q] = p1[q];
+        p1[q] = v[q];
+      }
+      emit(m);
+    }
+  } else if (F == KV_FASTKAN) {
+    float xn[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int i = min(i0 + q, c.in - 1);
+      xn[q] = fastkan_xn(c, i, x[q], mu, rs);
+    }
+    const float* gr = c.fp + 2 * c.in;
+    const float inv_den = 1.0f / c.rbf_denom;
+    for (int m = 0; m < c.G; ++m) {
+      const float gm = gr[m];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float z = (xn[q] - gm) * inv_den;
+        v[q] = __expf(-(z * z));
+      }
+      emit(m);
+    }
+    if (!(c.flags & KV_FLAG_NO_BASE)) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = fast_silu(x[q]);
+      emit(c.G);
+    }
+  } else if (F == KV_SINE) {
+    const float* freq = c.fp;
+    const float* ph = c.fp + c.G;
+    for (int m = 0; m < c.G; ++m) {
+      const float fr = freq[m];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const int i = min(i0 + q, c.in - 1);
+        v[q] = __sinf(fmaf(x[q], fr, ph[(size_t)i * c.G + m]));
+      }
+      emit(m);
+    }
+  } else if (F == KV_FOURIER) {
+    float c1[8], s1[8], ck[8], sk[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      __sincosf(x[q], &s1[q], &c1[q]);
+      ck[q] = c1[q];
+      sk[q] = s1[q];
+    }
+    for (int m = 0; m < 2 * c.G; ++m) {
+      if (m == c.G) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) { ck[q] = c1[q]; sk[q] = s1[q]; }
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        v[q] = (m < c.G) ? ck[q] : sk[q];
+        const float nc = ck[q] * c1[q] - sk[q] * s1[q];
+        const float ns = sk[q] * c1[q] + ck[q] * s1[q];
+        ck[q] = nc;
+        sk[q] = ns;
+      }
+      emit(m);
+    }
+  }
+}
+
 template <int F>
 __global__ void __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + A_RING_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A_RING_BYTES + B_RING_BYTES);
-  // barrier map: [0,NA) fullA, [NA,2NA) emptyA, [2NA, 2NA+NB_MAX) fullB, [.., +NB_MAX) emptyB, then tmem_full
+  // barrier map: fullA[NCH_MAX], emptyA[NCH_MAX], fullB[NB_MAX], emptyB[NB_MAX], tmem_full
   const uint32_t bar0 = ptx::smem_u32(bars);
   auto fullA = [&](int s) { return bar0 + 8u * s; };
-  auto emptyA = [&](int s) { return bar0 + 8u * (NA + s); };
-  auto fullB = [&](int s) { return bar0 + 8u * (2 * NA + s); };
-  auto emptyB = [&](int s) { return bar0 + 8u * (2 * NA + NB_MAX + s); };
-  const uint32_t tmem_full = bar0 + 8u * (2 * NA + 2 * NB_MAX);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NA + 2 * NB_MAX + 1);
+  auto emptyA = [&](int s) { return bar0 + 8u * (NCH_MAX + s); };
+  auto fullB = [&](int s) { return bar0 + 8u * (2 * NCH_MAX + s); };
+  auto emptyB = [&](int s) { return bar0 + 8u * (2 * NCH_MAX + NB_MAX + s); };
+  const uint32_t tmem_full = bar0 + 8u * (2 * NCH_MAX + 2 * NB_MAX);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NCH_MAX + 2 * NB_MAX + 1);
 
   const kv_kan_desc_t& d = p.d;
   const Geom gm = p.gm;
@@ -134,11 +328,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams
   const int m_tile = blockIdx.x, n_tile = blockIdx.y, g = blockIdx.z;
   const int M = d.M;
   const int n_units = gm.n_units;
-  const int BN = gm.BN, NB = gm.NB;
+  const int BN = gm.BN, NB = gm.NB, NCH = gm.NCH;
   const uint32_t b_unit_bytes = (uint32_t)BN * KU * 2;
+  const int t0 = m_tile * BM;
 
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < NA; ++s) {
+    for (int s = 0; s < NCH_MAX; ++s) {
       ptx::mbar_init(fullA(s), N_PRODUCER_WARPS);
       ptx::mbar_init(emptyA(s), 1);
     }
@@ -181,85 +376,108 @@ __global__ void __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams
       const uint32_t idesc1 = ptx::make_idesc_bf16(BM, n1);
       const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(BM, n2) : 0u;
       const uint32_t a_lbo = (BM / 8) * 128, b_lbo = (uint32_t)(BN / 8) * 128, sbo = 128;
-      for (int u = 0; u < n_units; ++u) {
-        const int sa = u % NA, sb = u % NB;
-        ptx::mbar_wait(fullA(sa), (u / NA) & 1);
-        ptx::mbar_wait(fullB(sb), (u / NB) & 1);
-        ptx::tc_fence_after();
-        const uint64_t da = ptx::make_smem_desc(ptx::smem_u32(sA) + sa * A_UNIT_BYTES, a_lbo, sbo);
-        const uint32_t b_addr = ptx::smem_u32(sB) + sb * b_unit_bytes;
-        ptx::mma_bf16_ss(tmem_base, da, ptx::make_smem_desc(b_addr, b_lbo, sbo), idesc1, u > 0);
-        if (n2)
-          ptx::mma_bf16_ss(tmem_base + 256, da, ptx::make_smem_desc(b_addr + 256 * 16, b_lbo, sbo), idesc2,
-                           u > 0);
-        ptx::tc_commit(emptyA(sa));
-        ptx::tc_commit(emptyB(sb));
+      int u = 0;
+      for (int ch = 0; ch < gm.n_chunks; ++ch) {
+        const int sc = ch % NCH;
+        ptx::mbar_wait(fullA(sc), (ch / NCH) & 1);
+        const uint32_t a_chunk = ptx::smem_u32(sA) + sc * M * A_UNIT_BYTES;
+        for (int q = 0; q < M; ++q, ++u) {
+          const int sb = u % NB;
+          ptx::mbar_wait(fullB(sb), (u / NB) & 1);
+          ptx::tc_fence_after();
+          const uint64_t da = ptx::make_smem_desc(a_chunk + q * A_UNIT_BYTES, a_lbo, sbo);
+          const uint32_t b_addr = ptx::smem_u32(sB) + sb * b_unit_bytes;
+          ptx::mma_bf16_ss(tmem_base, da, ptx::make_smem_desc(b_addr, b_lbo, sbo), idesc1, u > 0);
+          if (n2)
+            ptx::mma_bf16_ss(tmem_base + 256, da, ptx::make_smem_desc(b_addr + 256 * 16, b_lbo, sbo), idesc2,
+                             u > 0);
+          ptx::tc_commit(emptyB(sb));
+        }
+        ptx::tc_commit(emptyA(sc));
       }
       ptx::tc_commit(tmem_full);
     }
     __syncwarp();
   } else {
     // ================= A producers: basis prologue =================
-    const int pw = warp - 2;
-    const int f8 = lane & 7, r4 = lane >> 3;
+    const int ptid = threadIdx.x - 64;
+    const int r = ptid & (BM - 1), wg = ptid >> 7;
     const int n_slices = d.n_groups / d.x_share;
     const int slice = g / d.x_share;
     const int xoff = slice * d.in_features;
-    const int t0 = m_tile * BM;
+    const int in = d.in_features;
+    const int t = t0 + r;
+    const bool row_ok = t < d.T;
+    const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
+    const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0);
     const BasisCtx c = make_ctx(d, p.fparams, g);
+    const int layout = group_layout(d, gm, p.fparams, g);
+    float gt0 = 0.f, ginv_h = 0.f;
+    if (layout == LAYOUT_EFFKAN8) {
+      const float* probe = c.fp + (size_t)in * (d.grid_size + 2 * d.spline_order + 1);
+      gt0 = probe[1];
+      ginv_h = probe[2];
+    }
+    float mu = 0.f, rs = 1.f;
+    if (F == KV_FASTKAN && !(d.flags & KV_FLAG_NO_LAYERNORM) && row_ok) {
+      mu = p.mean[(size_t)t * n_slices + slice];
+      rs = p.rstd[(size_t)t * n_slices + slice];
+    }
+    const int row_off = (r >> 3) * 128 + (r & 7) * 16;
+    float cur[8];
+    load_x8(xrow, wg * 8, in, row_ok, vec, cur);
     for (int ch = 0; ch < gm.n_chunks; ++ch) {
-      const int u0 = ch * M;
-      const int s0 = u0 % NA;
-      // wait until the MMAs that read these slots one ring pass ago have completed
-      for (int m = 0; m < M; ++m) {
-        const int u = u0 + m;
-        ptx::mbar_wait(emptyA(u % NA), ((u / NA) & 1) ^ 1);
+      float nxt[8];
+      if (ch + 1 < gm.n_chunks) {
+        load_x8(xrow, (ch + 1) * KU + wg * 8, in, row_ok, vec, nxt);
+      } else {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) nxt[q] = 0.0f;
       }
-#pragma unroll 1
-      for (int step = 0; step < 8; ++step) {
-        const int row = pw * 16 + (step >> 1) * 4 + r4;
-        const int h = step & 1;
-        const int i = ch * KU + h * 8 + f8;
-        const int t = t0 + row;
-        UnitSink sink{sA, s0, h * 2048 + (row >> 3) * 128 + (row & 7) * 16 + f8 * 2};
-        if (i < d.in_features) {
-          const float x = (t < d.T) ? p.X[(size_t)t * d.ldx + xoff + i] : 0.0f;
-          float xn = x;
-          if (F == KV_FASTKAN) {
-            float mu = 0.f, rs = 1.f;
-            if (!(d.flags & KV_FLAG_NO_LAYERNORM) && t < d.T) {
-              mu = p.mean[(size_t)t * n_slices + slice];
-              rs = p.rstd[(size_t)t * n_slices + slice];
-            }
-            xn = fastkan_xn(c, i, x, mu, rs);
-          }
-          basis_eval<F>(c, i, x, xn, sink);
+      const int sc = ch % NCH;
+      ptx::mbar_wait(emptyA(sc), ((ch / NCH) & 1) ^ 1);
+      uint8_t* base = sA + sc * M * A_UNIT_BYTES + row_off;
+      const int i0 = ch * KU + wg * 8;
+      if (F == KV_EFFKAN) {
+        if (layout == LAYOUT_EFFKAN8) {
+          effkan8_chunk(base, wg, cur, gt0, ginv_h);
         } else {
-          for (int m = 0; m < M; ++m) sink.put(m, 0.0f);
+#pragma unroll 1
+          for (int q = 0; q < 8; ++q) {
+            UnitSink sink{base + wg * 2048 + q * 2};
+            if (i0 + q < in) {
+              basis_eval<F>(c, i0 + q, cur[q], cur[q], sink);
+            } else {
+              for (int m = 0; m < M; ++m) sink.put(m, 0.0f);
+            }
+          }
         }
+      } else {
+        basis_major_chunk<F>(base, wg, cur, c, i0, mu, rs);
       }
       ptx::fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
-        for (int m = 0; m < M; ++m) ptx::mbar_arrive(fullA((u0 + m) % NA));
-      }
+      if (lane == 0) ptx::mbar_arrive(fullA(sc));
+#pragma unroll
+      for (int q = 0; q < 8; ++q) cur[q] = nxt[q];
     }
     // ================= epilogue =================
     ptx::mbar_wait(tmem_full, 0);
     ptx::tc_fence_after();
-    const int q = warp & 3;             // TMEM lane quadrant this warp may read
+    const int pw = warp - 2;
+    const int q4 = warp & 3;            // TMEM lane quadrant this warp may read
     const int half = pw >> 2;           // two warps per quadrant split the column blocks
-    const int row = q * 32 + lane;
-    const int t = t0 + row;
+    const int row = q4 * 32 + lane;
+    const int te = t0 + row;
     const int out = d.out_features;
     const int ncols_total = d.n_groups * out;
-    const int prow = map_row(t < d.T ? t : 0, d.rows_in, d.rows_out, d.row_shift);
-    const int posrow = d.rows_in ? (d.row_shift + (t < d.T ? t : 0) % d.rows_in) : t;
+    const int prow = map_row(te < d.T ? te : 0, d.rows_in, d.rows_out, d.row_shift);
+    const int posrow = d.rows_in ? (d.row_shift + (te < d.T ? te : 0) % d.rows_in) : te;
     for (int cb = half; cb * 32 < BN; cb += 2) {
-      uint32_t r[32];
-      ptx::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + cb * 32, r);
+      uint32_t rr[32];
+      ptx::tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + cb * 32, rr);
       ptx::tmem_ld_wait();
-      if (t < d.T) {
+      if (te < d.T) {
         const int o0 = n_tile * BN + cb * 32;
         const int col0 = g * out + o0;
         float* yrow = p.Y + (size_t)prow * d.ldy + col0;
@@ -268,8 +486,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams
         const float* brow = p.bias ? p.bias + col0 : nullptr;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          if (o0 + j < out) {
-            float v = __uint_as_float(r[j]);
+          if (cb * 32 + j < BN && o0 + j < out) {
+            float v = __uint_as_float(rr[j]);
             if (brow) v += brow[j];
             if (prow_p) v += prow_p[j];
             if (d.flags & KV_FLAG_RELU) v = fmaxf(v, 0.0f);
@@ -310,22 +528,22 @@ int tc_supported(const kv_kan_desc_t& d) {
 }
 
 size_t tc_wtiles_bytes(const kv_kan_desc_t& d) {
-  const tc::Geom gm = tc::make_geom(d.in_features, d.out_features, d.M);
+  const tc::Geom gm = tc::make_geom(d);
   return (size_t)d.n_groups * gm.n_tiles * gm.tile_elems() * 2;
 }
 
 size_t tc_wtiles_t_bytes(const kv_kan_desc_t&) { return 0; }
 bool tc_bwd_weight_available(const kv_kan_desc_t&) { return false; }
 
-int tc_pack(const kv_kan_desc_t& d, const float* wp_f32, void* wtiles, void* wtiles_t, cudaStream_t st) {
+int tc_pack(const kv_kan_desc_t& d, const float* wp_f32, const float* fparams, void* wtiles, void* wtiles_t,
+            cudaStream_t st) {
   (void)wtiles_t;
   if (wtiles == nullptr) return KV_OK;
-  const tc::Geom gm = tc::make_geom(d.in_features, d.out_features, d.M);
+  const tc::Geom gm = tc::make_geom(d);
   const size_t total = (size_t)d.n_groups * gm.n_tiles * gm.tile_elems();
   const int threads = 256;
   const int blocks = (int)((total + threads - 1) / threads > 148 * 16 ? 148 * 16 : (total + threads - 1) / threads);
-  tc::tc_pack_kernel<<<blocks, threads, 0, st>>>(wp_f32, reinterpret_cast<__nv_bfloat16*>(wtiles), d.n_groups,
-                                                 d.in_features, d.out_features, d.M, gm);
+  tc::tc_pack_kernel<<<blocks, threads, 0, st>>>(d, wp_f32, fparams, reinterpret_cast<__nv_bfloat16*>(wtiles), gm);
   KV_CHECK_LAUNCH("tc_pack_kernel");
   return KV_OK;
 }
@@ -345,7 +563,7 @@ int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const flo
   p.residual = residual;
   p.pos = pos;
   p.Y = Y;
-  p.gm = tc::make_geom(d.in_features, d.out_features, d.M);
+  p.gm = tc::make_geom(d);
   switch (d.family) {
     case KV_LINEAR: return tc::launch_fwd<KV_LINEAR>(p, st);
     case KV_EFFKAN: return tc::launch_fwd<KV_EFFKAN>(p, st);

@@ -31,17 +31,27 @@ def test_bf16_matches_reference_golden(case):
     y = m(x)
     assert relerr(y, g.t("y")) < TOL_BF16
     y.backward(g.t("dy", _dev()))
-    # 2e-2 is the per-layer bound.  Gradients of the composite cases (MSA / block / ViT) pass through
-    # up to ~20 bf16-rounded GEMMs, softmax and LayerNorm backward, so their rounding noise adds up:
-    # they get 1e-1 (the single-layer cases keep 2e-2 for every tensor).
-    gtol = TOL_BF16 if case.startswith("layer_") else 1e-1
-    assert relerr(x.grad, g.t("gx")) < gtol
+    # 2e-2 norm-wise is the per-layer bound and is applied to every tensor of the single-layer
+    # cases.  Gradients of the composite cases (MSA / block / ViT, 10-50 token toy models) pass
+    # through up to ~20 bf16-rounded GEMMs, softmax and LayerNorm backward, and a ReLU unit whose
+    # pre-activation sits inside the bf16 noise flips its mask, which rewrites one whole row of
+    # ff.0's gradient: they are judged in the Frobenius norm, ||a-b|| / ||b|| < 1e-1.
+    layer = case.startswith("layer_")
+
+    def err(a, b):
+        if layer:
+            return relerr(a, b)
+        a, b = a.detach().double().cpu(), b.detach().double().cpu()
+        return ((a - b).norm() / b.norm()).item()
+
+    gtol = TOL_BF16 if layer else 1e-1
+    assert err(x.grad, g.t("gx")) < gtol
     params = dict(m.named_parameters())
     for k, ref in g.grads().items():
         if ref.abs().max() < 1e-6:
             continue
         tol = max(gtol, 5e-2) if k.endswith(".freq") else gtol  # cancelling sum, see test_gpu_parity
-        assert relerr(params[k].grad, ref) < tol, k
+        assert err(params[k].grad, ref) < tol, k
 
 
 SHAPES = [
