@@ -33,7 +33,8 @@ constexpr int NCH_MAX = A_UNITS;
 constexpr int N_PRODUCER_WARPS = 8;
 constexpr int NTHREADS = 32 * (2 + N_PRODUCER_WARPS);
 constexpr int BAR_BYTES = 1024;
-constexpr int SMEM_BYTES = A_RING_BYTES + B_RING_BYTES + BAR_BYTES;
+constexpr int DBG_BYTES = 16 * 1024;  // clock stamps of timing experiments (d.reserved & 32)
+constexpr int SMEM_BYTES = A_RING_BYTES + B_RING_BYTES + BAR_BYTES + DBG_BYTES;
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_M_TC = 24;
 
@@ -46,7 +47,8 @@ struct Geom {
   int n_units;   // n_chunks * M
   int n_tiles;   // output tiles per group
   int BN;        // outputs per tile (multiple of 16, <= 512)
-  int NB;        // B ring slots (units)
+  int S;         // units per B stage (one bulk copy, one barrier round trip)
+  int NB;        // B ring slots (stages)
   int NCH;       // A ring slots (chunks)
   int effkan8;   // host-side candidate for LAYOUT_EFFKAN8 (the device-side grid probe decides)
   __host__ __device__ size_t tile_elems() const { return (size_t)n_units * BN * KU; }
@@ -59,7 +61,10 @@ __host__ __device__ inline Geom make_geom(const kv_kan_desc_t& d) {
   const int out16 = (d.out_features + 15) / 16 * 16;
   g.n_tiles = (out16 + 511) / 512;
   g.BN = ((out16 + g.n_tiles - 1) / g.n_tiles + 15) / 16 * 16;
-  int nb = B_RING_BYTES / (g.BN * KU * 2);
+  const int half_unit = g.BN * KU;  // bytes; each CTA of the pair stages half of a unit: BN/2 rows
+  g.S = 24576 / half_unit;
+  g.S = g.S < 1 ? 1 : (g.S > 8 ? 8 : g.S);
+  int nb = B_RING_BYTES / (g.S * half_unit);
   g.NB = nb > NB_MAX ? NB_MAX : nb;
   g.NCH = A_UNITS / d.M;
   g.effkan8 = (d.family == KV_EFFKAN && d.spline_order == 3 && d.grid_size == 5) ? 1 : 0;
@@ -88,8 +93,9 @@ __device__ __forceinline__ void unit_to_im(int layout, int M, int c, int q, int 
 
 // ----------------------------------------------------------------------------------------
 // weight pre-tiling: wp_f32 [g][out][in*M] (K index i*M+m)  ->  wtiles bf16
-//   [g][n_tile][unit][k-half h][row group rg = BN/8][8 rows][8 elements]
-// = for every unit the no-swizzle K-major operand image (core matrix = 8 rows x 16 B).
+//   [g][n_tile][CTA rank][unit][sub-MMA j][k-half h][row group][8 rows][8 elements]
+// = for every unit and each CTA of the pair the no-swizzle K-major operand image of its half of the
+//   rows of each N<=256 sub-MMA (core matrix = 8 rows x 16 B).
 // ----------------------------------------------------------------------------------------
 __global__ void tc_pack_kernel(const kv_kan_desc_t d, const float* __restrict__ wp,
                                const float* __restrict__ fparams, __nv_bfloat16* __restrict__ wt, Geom gm) {
@@ -99,15 +105,20 @@ __global__ void tc_pack_kernel(const kv_kan_desc_t d, const float* __restrict__ 
   const int K = in * M;
   for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (size_t)gridDim.x * blockDim.x) {
+    // [g][n_tile][CTA rank][unit][sub-MMA j][k-half h][row group][8 rows][8 elements]
     size_t r = idx;
     const int e = r % 8; r /= 8;
     const int r8 = r % 8; r /= 8;
-    const int rg = r % (gm.BN / 8); r /= (gm.BN / 8);
-    const int h = r % 2; r /= 2;
+    int pr = r % (gm.BN / 8); r /= (gm.BN / 8);   // core-matrix position inside this rank's half unit
     const int u = r % gm.n_units; r /= gm.n_units;
+    const int rank = r % 2; r /= 2;
     const int nt = r % gm.n_tiles; r /= gm.n_tiles;
     const int g = (int)r;
-    const int o = nt * gm.BN + rg * 8 + r8;
+    const int n1 = gm.BN > 256 ? 256 : gm.BN, n2 = gm.BN - n1;
+    int j = 0, nj = n1;
+    if (pr >= n1 / 8) { pr -= n1 / 8; j = 1; nj = n2; }
+    const int h = pr / (nj / 16), rgl = pr % (nj / 16);
+    const int o = nt * gm.BN + (j ? n1 : 0) + rank * (nj / 2) + rgl * 8 + r8;
     const int c = u / M, q = u - c * M;
     int i, m;
     unit_to_im(group_layout(d, gm, fparams, g), M, c, q, h, e, i, m);
@@ -308,7 +319,7 @@ __device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const f
 }
 
 template <int F>
-__global__ void __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + A_RING_BYTES;
@@ -325,77 +336,123 @@ __global__ void __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams
   const kv_kan_desc_t& d = p.d;
   const Geom gm = p.gm;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m_tile = blockIdx.x, n_tile = blockIdx.y, g = blockIdx.z;
+  const uint32_t rank = ptx::cluster_ctarank();  // 0 = leader of the CTA pair
+  const int n_tile = blockIdx.y % gm.n_tiles;
+  const int m_tile = (blockIdx.y / gm.n_tiles) * 2 + (int)rank;
+  const int g = blockIdx.z;
   const int M = d.M;
   const int n_units = gm.n_units;
   const int BN = gm.BN, NB = gm.NB, NCH = gm.NCH;
-  const uint32_t b_unit_bytes = (uint32_t)BN * KU * 2;
+  const uint32_t b_unit_bytes = (uint32_t)BN * KU;  // this CTA's half of the B unit: BN/2 rows x 16 x 2 B
   const int t0 = m_tile * BM;
 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < NCH_MAX; ++s) {
-      ptx::mbar_init(fullA(s), N_PRODUCER_WARPS);
+      ptx::mbar_init(fullA(s), 2 * N_PRODUCER_WARPS);  // (leader) local + peer producer warps
       ptx::mbar_init(emptyA(s), 1);
     }
     for (int s = 0; s < NB_MAX; ++s) {
-      ptx::mbar_init(fullB(s), 1);
+      ptx::mbar_init(fullB(s), rank == 0 ? 2 : 1);  // leader: own bulk copy + the peer's "my half landed"
       ptx::mbar_init(emptyB(s), 1);
     }
     ptx::mbar_init(tmem_full, 1);
     ptx::fence_mbar_init();
   }
   if (warp == 0) {
-    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), TMEM_COLS);
-    ptx::tmem_relinquish();
+    ptx::tmem_alloc2(ptx::smem_u32(tmem_slot), TMEM_COLS);
+    ptx::tmem_relinquish2();
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  ptx::cluster_sync_all();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // timing experiments only (d.reserved & 32): first tile stamps clock64 into the head of Y
+  const bool dbg = (d.reserved & 32) && blockIdx.y == 0 && blockIdx.z == 0;
+  uint32_t* dbuf = reinterpret_cast<uint32_t*>(smem + A_RING_BYTES + B_RING_BYTES + BAR_BYTES);
+  auto stamp = [&](int role, int u, int k) {
+    if (dbg && u < 256) dbuf[(role * 256 + u) * 4 + k] = (uint32_t)clock64();
+  };
 
+  const int S = gm.S;
+  const int n_stages = (n_units + S - 1) / S;
   if (warp == 0) {
-    // ================= B loader: one bulk copy per unit =================
+    // ================= B loader: this CTA's half of S units per bulk copy =================
     if (lane == 0) {
       const uint8_t* src = reinterpret_cast<const uint8_t*>(p.wt) +
-                           ((size_t)g * gm.n_tiles + n_tile) * gm.tile_elems() * 2;
-      for (int u = 0; u < n_units; ++u) {
-        const int s = u % NB;
-        const uint32_t it = u / NB;
-        ptx::mbar_wait(emptyB(s), (it & 1) ^ 1);
-        ptx::mbar_arrive_expect_tx(fullB(s), b_unit_bytes);
-        ptx::bulk_g2s(ptx::smem_u32(sB) + s * b_unit_bytes, src + (size_t)u * b_unit_bytes, b_unit_bytes,
-                      fullB(s));
+                           (((size_t)g * gm.n_tiles + n_tile) * 2 + rank) * (size_t)n_units * b_unit_bytes;
+      int s = 0;
+      uint32_t ph = 1;  // a fresh barrier passes a wait on parity 1
+      for (int st = 0; st < n_stages; ++st) {
+        const int nu = min(S, n_units - st * S);
+        ptx::mbar_wait(emptyB(s), ph);
+        stamp(1, st, 0);
+        ptx::mbar_arrive_expect_tx(fullB(s), nu * b_unit_bytes);
+        ptx::bulk_g2s(ptx::smem_u32(sB) + s * S * b_unit_bytes, src + (size_t)st * S * b_unit_bytes,
+                      nu * b_unit_bytes, fullB(s));
+        stamp(1, st, 1);
+        if (++s == NB) { s = 0; ph ^= 1; }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
+    if (rank == 0) {
+      // ================= MMA issuer (leader CTA): the whole warp walks the loop, one elected lane issues ===
       const int n1 = BN > 256 ? 256 : BN;
       const int n2 = BN - n1;
-      const uint32_t idesc1 = ptx::make_idesc_bf16(BM, n1);
-      const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(BM, n2) : 0u;
-      const uint32_t a_lbo = (BM / 8) * 128, b_lbo = (uint32_t)(BN / 8) * 128, sbo = 128;
-      int u = 0;
+      const uint32_t idesc1 = ptx::make_idesc_bf16(2 * BM, n1);
+      const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(2 * BM, n2) : 0u;
+      const uint32_t sbo = 128;
+      // descriptors differ only in the 14-bit start-address field: add (bytes >> 4) per step
+      const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), (BM / 8) * 128, sbo);
+      const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)n1 * 8, sbo);
+      const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 16, (uint32_t)n2 * 8, sbo);
+      const uint32_t a_chunk_step = (uint32_t)(M * A_UNIT_BYTES) >> 4, b_unit_step = b_unit_bytes >> 4;
+      int sc = 0, sb = 0, ub = 0, u = 0;
+      uint32_t phA = 0, phB = 0;
       for (int ch = 0; ch < gm.n_chunks; ++ch) {
-        const int sc = ch % NCH;
-        ptx::mbar_wait(fullA(sc), (ch / NCH) & 1);
-        const uint32_t a_chunk = ptx::smem_u32(sA) + sc * M * A_UNIT_BYTES;
+        if (!(d.reserved & 2)) ptx::mbar_wait(fullA(sc), phA);
+        uint64_t da = da0 + (uint64_t)(sc * a_chunk_step);
         for (int q = 0; q < M; ++q, ++u) {
-          const int sb = u % NB;
-          ptx::mbar_wait(fullB(sb), (u / NB) & 1);
+          if (ub == 0) {
+            stamp(0, u, 0);
+            if (!(d.reserved & 64)) ptx::mbar_wait(fullB(sb), phB);
+            stamp(0, u, 1);
+          }
           ptx::tc_fence_after();
-          const uint64_t da = ptx::make_smem_desc(a_chunk + q * A_UNIT_BYTES, a_lbo, sbo);
-          const uint32_t b_addr = ptx::smem_u32(sB) + sb * b_unit_bytes;
-          ptx::mma_bf16_ss(tmem_base, da, ptx::make_smem_desc(b_addr, b_lbo, sbo), idesc1, u > 0);
-          if (n2)
-            ptx::mma_bf16_ss(tmem_base + 256, da, ptx::make_smem_desc(b_addr + 256 * 16, b_lbo, sbo), idesc2,
-                             u > 0);
-          ptx::tc_commit(emptyB(sb));
+          const uint32_t boff = (uint32_t)(sb * S + ub) * b_unit_step;
+          const bool last_of_stage = (ub + 1 == S) || (u + 1 == n_units);
+          if (ptx::elect_one()) {
+            if (!(d.reserved & 4)) {
+              ptx::mma2_bf16_ss(tmem_base, da, db1_0 + boff, idesc1, u > 0);
+              if (n2 && !(d.reserved & 128)) ptx::mma2_bf16_ss(tmem_base + 256, da, db2_0 + boff, idesc2, u > 0);
+            }
+            if (last_of_stage) ptx::tc_commit2(emptyB(sb));
+            if (q == M - 1) ptx::tc_commit2(emptyA(sc));
+            if (u + 1 == n_units) ptx::tc_commit2(tmem_full);
+          }
+          __syncwarp();
+          stamp(0, u, 3);
+          da += A_UNIT_BYTES >> 4;
+          if (last_of_stage) {
+            ub = 0;
+            if (++sb == NB) { sb = 0; phB ^= 1; }
+          } else {
+            ++ub;
+          }
         }
-        ptx::tc_commit(emptyA(sc));
+        if (++sc == NCH) { sc = 0; phA ^= 1; }
       }
-      ptx::tc_commit(tmem_full);
+    } else if (lane == 0) {
+      // ================= peer CTA: tell the leader when our half of each B stage has landed ===========
+      int s = 0;
+      uint32_t ph = 0;
+      for (int st = 0; st < n_stages; ++st) {
+        ptx::mbar_wait(fullB(s), ph);
+        stamp(3, st, 0);
+        ptx::mbar_arrive_cluster(ptx::mapa(fullB(s), 0));
+        stamp(3, st, 1);
+        if (++s == NB) { s = 0; ph ^= 1; }
+      }
     }
     __syncwarp();
   } else {
@@ -436,6 +493,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams
       }
       const int sc = ch % NCH;
       ptx::mbar_wait(emptyA(sc), ((ch / NCH) & 1) ^ 1);
+      if (ptid == 0) stamp(2, ch, 0);
       uint8_t* base = sA + sc * M * A_UNIT_BYTES + row_off;
       const int i0 = ch * KU + wg * 8;
       if (F == KV_EFFKAN) {
@@ -457,52 +515,102 @@ __global__ void __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams
       }
       ptx::fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(fullA(sc));
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(sc), 0));  // the leader's barrier
+      if (ptid == 0) stamp(2, ch, 1);
 #pragma unroll
       for (int q = 0; q < 8; ++q) cur[q] = nxt[q];
     }
-    // ================= epilogue =================
+    // ================= epilogue: TMEM -> registers -> smem transpose -> coalesced global stores =========
     ptx::mbar_wait(tmem_full, 0);
     ptx::tc_fence_after();
     const int pw = warp - 2;
     const int q4 = warp & 3;            // TMEM lane quadrant this warp may read
     const int half = pw >> 2;           // two warps per quadrant split the column blocks
-    const int row = q4 * 32 + lane;
-    const int te = t0 + row;
     const int out = d.out_features;
     const int ncols_total = d.n_groups * out;
-    const int prow = map_row(te < d.T ? te : 0, d.rows_in, d.rows_out, d.row_shift);
-    const int posrow = d.rows_in ? (d.row_shift + (te < d.T ? te : 0) % d.rows_in) : te;
+    constexpr int LDT = 36;             // staging row stride in floats (conflict-free float4 access)
+    float* stg = reinterpret_cast<float*>(sA) + pw * (32 * LDT);  // the operand rings are idle by now
+    const int c4 = (lane & 7) * 4, rsub = lane >> 3;
+    // the 8 rows this lane stores in the row-wise phase
+    long long yoff[8];
+    int posrow[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int te = t0 + q4 * 32 + it * 4 + rsub;
+      if (te < d.T) {
+        yoff[it] = (long long)map_row(te, d.rows_in, d.rows_out, d.row_shift) * d.ldy;
+        posrow[it] = d.rows_in ? (d.row_shift + te % d.rows_in) : te;
+      } else {
+        yoff[it] = -1;
+        posrow[it] = 0;
+      }
+    }
+    const int colbase = g * out + n_tile * BN;
+    const bool vec_y = ((d.ldy & 3) == 0) && ((colbase & 3) == 0) && ((ncols_total & 3) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(p.Y) & 15) == 0) &&
+                       (!p.residual || (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0) &&
+                       (!p.pos || (reinterpret_cast<uintptr_t>(p.pos) & 15) == 0) &&
+                       (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
     for (int cb = half; cb * 32 < BN; cb += 2) {
       uint32_t rr[32];
       ptx::tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + cb * 32, rr);
       ptx::tmem_ld_wait();
-      if (te < d.T) {
-        const int o0 = n_tile * BN + cb * 32;
-        const int col0 = g * out + o0;
-        float* yrow = p.Y + (size_t)prow * d.ldy + col0;
-        const float* rrow = p.residual ? p.residual + (size_t)prow * d.ldy + col0 : nullptr;
-        const float* prow_p = p.pos ? p.pos + (size_t)posrow * ncols_total + col0 : nullptr;
-        const float* brow = p.bias ? p.bias + col0 : nullptr;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          if (cb * 32 + j < BN && o0 + j < out) {
-            float v = __uint_as_float(rr[j]);
-            if (brow) v += brow[j];
-            if (prow_p) v += prow_p[j];
-            if (d.flags & KV_FLAG_RELU) v = fmaxf(v, 0.0f);
-            if (rrow) v += rrow[j];
-            yrow[j] = v;
+      for (int k = 0; k < 8; ++k)
+        *reinterpret_cast<uint4*>(stg + lane * LDT + 4 * k) = make_uint4(rr[4 * k], rr[4 * k + 1], rr[4 * k + 2], rr[4 * k + 3]);
+      __syncwarp();
+      const int cl = cb * 32 + c4;           // column inside the tile
+      const int o = n_tile * BN + cl;        // output feature of the group
+      const int col = colbase + cl;          // column of Y
+      float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+      const bool full4 = vec_y && (cl + 3 < BN) && (o + 3 < out);
+      if (p.bias && full4) bv = *reinterpret_cast<const float4*>(p.bias + col);
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const float4 a = *reinterpret_cast<const float4*>(stg + (it * 4 + rsub) * LDT + c4);
+        if (yoff[it] < 0) continue;
+        float v[4] = {a.x, a.y, a.z, a.w};
+        if (full4) {
+          v[0] += bv.x; v[1] += bv.y; v[2] += bv.z; v[3] += bv.w;
+          if (p.pos) {
+            const float4 pv = *reinterpret_cast<const float4*>(p.pos + (size_t)posrow[it] * ncols_total + col);
+            v[0] += pv.x; v[1] += pv.y; v[2] += pv.z; v[3] += pv.w;
+          }
+          if (d.flags & KV_FLAG_RELU) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) v[e] = fmaxf(v[e], 0.0f);
+          }
+          if (p.residual) {
+            const float4 rv = *reinterpret_cast<const float4*>(p.residual + yoff[it] + col);
+            v[0] += rv.x; v[1] += rv.y; v[2] += rv.z; v[3] += rv.w;
+          }
+          *reinterpret_cast<float4*>(p.Y + yoff[it] + col) = make_float4(v[0], v[1], v[2], v[3]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            if (cl + e < BN && o + e < out) {
+              float w = v[e];
+              if (p.bias) w += p.bias[col + e];
+              if (p.pos) w += p.pos[(size_t)posrow[it] * ncols_total + col + e];
+              if (d.flags & KV_FLAG_RELU) w = fmaxf(w, 0.0f);
+              if (p.residual) w += p.residual[yoff[it] + col + e];
+              p.Y[yoff[it] + col + e] = w;
+            }
           }
         }
       }
+      __syncwarp();
     }
     ptx::tc_fence_before();
   }
-  __syncthreads();
+  ptx::cluster_sync_all();  // the peer's smem / TMEM stay alive until every MMA and epilogue is done
+  if (dbg) {
+    for (int i = threadIdx.x; i < 4096; i += NTHREADS)
+      reinterpret_cast<uint32_t*>(p.Y)[(size_t)(rank * 128 + i / 512) * d.ldy + (i % 512)] = dbuf[i];
+  }
   if (warp == 0) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+    ptx::tmem_dealloc2(tmem_base, TMEM_COLS);
   }
 }
 
@@ -514,7 +622,9 @@ static int launch_fwd(const FwdParams& p, cudaStream_t st) {
             "tc_fwd smem attribute");
     attr_set = true;
   }
-  dim3 grid(ceil_div(p.d.T, BM), p.gm.n_tiles, p.d.n_groups);
+  const int n_pairs = ceil_div(p.d.T, 2 * BM);
+  if ((long long)n_pairs * p.gm.n_tiles > 65535 || p.d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
+  dim3 grid(2, n_pairs * p.gm.n_tiles, p.d.n_groups);  // x = CTA pair; output tiles of one row pair adjacent
   kan_tc_fwd_kernel<F><<<grid, NTHREADS, SMEM_BYTES, st>>>(p);
   KV_CHECK_LAUNCH("kan_tc_fwd_kernel");
   return KV_OK;

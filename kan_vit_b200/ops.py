@@ -43,6 +43,7 @@ PROFILE_ONLY = None  # None = every call, else a set of names
 # tensor-core kernels with bf16 operands and fp32 accumulation in TMEM (parity 2e-2).  Activations
 # stay fp32 in HBM in both modes.
 _PRECISION = "fp32"
+_DEBUG_BITS = int(__import__("os").environ.get("KV_DEBUG_BITS", "0"))  # kernel timing experiments only
 
 
 def set_precision(mode: str):
@@ -136,7 +137,7 @@ class KanSpec:
         return L.KanDesc(self.family, T, self.in_features, self.out_features, self.n_groups,
                          self.x_share, self.M, self.grid_size, self.spline_order, ldx, ldy,
                          rows_in, rows_out, row_shift, self.flags | extra_flags, self.rbf_denom,
-                         getattr(self, "fparam_stride", 1 << 30), 0)
+                         getattr(self, "fparam_stride", 1 << 30), _DEBUG_BITS)
 
     # -- parameter pointer table (device, cached while the parameter storages stay put)
     def ptr_table(self, flat: Sequence[Optional[torch.Tensor]], device) -> torch.Tensor:

@@ -1,0 +1,22 @@
+import os, sys
+os.environ["KV_DEBUG_BITS"] = sys.argv[1] if len(sys.argv) > 1 else "32"
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import kan_vit_b200 as K
+from kan_vit_b200 import ops
+from kan_vit_b200._dispatch import make_spec, slots_of
+dev = torch.device("cuda:0")
+m = K.KANLinear(768, 3072).to(dev)
+x = torch.randn(25216, 768, device=dev)
+spec = make_spec([m]); K.set_precision("bf16")
+for _ in range(2):
+    y = ops.kan_apply(x, spec, [slots_of(m)])
+torch.cuda.synchronize()
+for rank in range(2):
+    d = y[rank * 128: rank * 128 + 8, :512].contiguous().view(torch.int32).cpu().view(4, 256, 4).long() & 0xffffffff
+    t0 = int(d[1, 0, 0])
+    f = lambda v: (int(v) - t0) & 0xffffffff
+    print("CTA rank", rank, "roles: 0=mma(u: start,fullB,peerB,commit) 1=loader(u: emptyB ok, issued) 2=producer(chunk: emptyA ok, arrived) 3=relay(u: fullB, arrived)")
+    for u in list(range(0, 40)) + list(range(200, 212)):
+        print(u, "mma", [f(d[0, u, k]) for k in range(4)], "load", [f(d[1, u, k]) for k in range(2)],
+              "prod", [f(d[2, u, k]) for k in range(2)], "relay", [f(d[3, u, k]) for k in range(2)])
