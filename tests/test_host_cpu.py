@@ -33,7 +33,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_bad_arguments_return_codes_without_a_gpu():
     L, lib = _lib()
-    d = L.KanDesc(L.KV_EFFKAN, 4, 8, 8, 1, 1, 9, 5, 3, 8, 8, 0, 0, 0, 0, 1.0, 8 * 12, 0)
+    d = L.KanDesc(L.KV_EFFKAN, 4, 8, 8, 1, 1, 9, 5, 3, 8, 8, 0, 0, 0, 0, 1.0, 8 * 12 + 4, 0)
     assert lib.kv_kan_fparam_count(C.byref(d)) == 8 * 12 + 4  # knots + the 4-float grid probe
     assert lib.kv_kan_fwd(C.byref(d), None, None, None, None, None, None, None, None, None, None, None) == -1
     d.M = 7  # inconsistent with grid_size + spline_order + 1
