@@ -56,6 +56,9 @@ typedef enum {
 #define KV_FLAG_NO_LAYERNORM  2u  /* fastkan time_benchmark=True (models/fastkan.py:69-70)            */
 #define KV_FLAG_NO_BASE       4u  /* fastkan use_base_update=False (models/fastkan.py:60-63)          */
 #define KV_FLAG_BF16_TC       8u  /* tcgen05 bf16 tensor-core path (fp32 accumulate) instead of fp32 SIMT */
+#define KV_FLAG_UNIFORM_GRID 16u  /* effkan: the caller has checked that every feature shares one uniform knot
+                                     vector (true until KANLinear.update_grid, models/effkan.py:189-242, is used);
+                                     enables the closed-form B-spline prologue and the tensor-core gradient kernels */
 
 /* One KAN (or Linear) layer, or a batch of `n_groups` independent layers of equal
  * shape applied to column slices of the same activation matrix (the per-head Q/K/V
@@ -119,8 +122,15 @@ int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32
 
 /* Bytes of the tensor-core operand images of kv_kan_pack (KV_FLAG_BF16_TC path).  Returns
  * KV_ERR_UNSUPPORTED when the layer cannot run on the tensor-core kernels (M > 24);
- * *wtiles_t_bytes == 0 means the input gradient runs on the fp32 kernels for this layer. */
-int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles_t_bytes);
+ * *wtiles_t_bytes == 0 / *dy_image_bytes == 0 mean the gradients run on the fp32 kernels for this layer. */
+int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles_t_bytes,
+                    size_t* dy_image_bytes);
+
+/* Tensor-core gradient path: bf16 copy of dY (times the ReLU mask when KV_FLAG_RELU is set) in the
+ * operand tiling both gradient kernels read; made once per backward pass of a layer.
+ * dy_image: *dy_image_bytes of kv_kan_tc_bytes (0 = this layer's gradients run on the fp32 kernels). */
+int kv_kan_dy_image(const kv_kan_desc_t* d, const float* dY, const float* act_mask, void* dy_image,
+                    void* stream);
 
 /* Per-(row, slice) mean and 1/sqrt(var+eps) over `width` consecutive columns:
  * the LayerNorm statistics of FastKANLayer.layernorm (models/fastkan.py:57,68).
@@ -146,15 +156,15 @@ int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, cons
  * by kv_fastkan_ln_bwd.  dfparams [g][fparam_stride] (sine: d freq accumulated with
  * atomics, must be zeroed by the caller; others untouched).  dX is OVERWRITTEN. */
 int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
-                     const float* wp_f32, const void* wtiles_t_bf16, const float* fparams,
-                     const float* mean, const float* rstd, float* dX, float* dXn,
+                     const float* wp_f32, const void* wtiles_t_bf16, const void* dy_image,
+                     const float* fparams, const float* mean, const float* rstd, float* dX, float* dXn,
                      float* dfparams, void* stream);
 
 /* Weight gradient in packed layout: dWp[g][o][i*M+m] = sum_t dY[t,o] * Phi_m(x[t,i]),
  * dbias[g][o] = sum_t dY[t,o] (nullable).  dWp and dbias must be ZEROED by the caller
  * (split over row ranges, accumulated with fp32 atomics). */
 int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
-                      const float* fparams, const float* mean, const float* rstd,
+                      const void* dy_image, const float* fparams, const float* mean, const float* rstd,
                       float* dWp, float* dbias, void* stream);
 
 /* FastKAN: LayerNorm backward of the RBF branch (models/fastkan.py:57,68):

@@ -49,4 +49,8 @@ def make_spec(modules, x_share=1):
     for m in modules[1:]:
         if spec_args(m) != (fam, i, o, kw):
             raise L.KanVitError("grouped layers must share family, sizes and grid")
-    return KanSpec(fam, i, o, n_groups=len(modules), x_share=x_share, **kw)
+    spec = KanSpec(fam, i, o, n_groups=len(modules), x_share=x_share, **kw)
+    if fam == L.KV_EFFKAN:
+        mods = list(modules)
+        spec.dyn_flags = lambda: L.KV_FLAG_UNIFORM_GRID if all(m.grid_is_uniform() for m in mods) else 0
+    return spec

@@ -19,6 +19,7 @@ KV_FLAG_RELU = 1
 KV_FLAG_NO_LAYERNORM = 2
 KV_FLAG_NO_BASE = 4
 KV_FLAG_BF16_TC = 8
+KV_FLAG_UNIFORM_GRID = 16
 
 
 class KanDesc(C.Structure):
@@ -42,11 +43,12 @@ _DP = C.POINTER(KanDesc)
 _SIGNATURES = {
     "kv_kan_fparam_count": [_DP],
     "kv_kan_pack": [_DP, _P, _P, _P, _P, _P, _P, _P],
-    "kv_kan_tc_bytes": [_DP, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],
+    "kv_kan_tc_bytes": [_DP, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)],
+    "kv_kan_dy_image": [_DP, _P, _P, _P, _P],
     "kv_row_stats": [_P, _I, _I, _I, _I, C.c_float, _P, _P, _P],
     "kv_kan_fwd": [_DP] + [_P] * 11,
-    "kv_kan_bwd_input": [_DP] + [_P] * 12,
-    "kv_kan_bwd_weight": [_DP] + [_P] * 9,
+    "kv_kan_bwd_input": [_DP] + [_P] * 13,
+    "kv_kan_bwd_weight": [_DP] + [_P] * 10,
     "kv_fastkan_ln_bwd": [_DP] + [_P] * 8,
     "kv_kan_unpack_grads": [_DP] + [_P] * 6,
     "kv_attn_fwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],

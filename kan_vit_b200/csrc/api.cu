@@ -368,14 +368,24 @@ int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32
   return KV_OK;
 }
 
-int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles_t_bytes) {
+int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles_t_bytes, size_t* dy_image_bytes) {
   int rc = check_desc(d);
   if (rc != KV_OK) return rc;
   rc = tc_supported(*d);
   if (rc != KV_OK) return rc;
   if (wtiles_bytes) *wtiles_bytes = tc_wtiles_bytes(*d);
   if (wtiles_t_bytes) *wtiles_t_bytes = tc_wtiles_t_bytes(*d);
+  if (dy_image_bytes) *dy_image_bytes = tc_dy_image_bytes(*d);
   return KV_OK;
+}
+
+int kv_kan_dy_image(const kv_kan_desc_t* d, const float* dY, const float* act_mask, void* dy_image, void* stream) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  if (d->T == 0) return KV_OK;
+  if (dY == nullptr || dy_image == nullptr) return KV_ERR_BAD_ARG;
+  if ((d->flags & KV_FLAG_RELU) && act_mask == nullptr) return KV_ERR_BAD_ARG;
+  return tc_dy_image(*d, dY, act_mask, dy_image, (cudaStream_t)stream);
 }
 
 int kv_row_stats(const float* X, int T, int ldx, int n_slices, int width, float eps, float* mean,
@@ -413,9 +423,9 @@ int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, cons
 }
 
 int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
-                     const float* wp_f32, const void* wtiles_t_bf16, const float* fparams,
-                     const float* mean, const float* rstd, float* dX, float* dXn, float* dfparams,
-                     void* stream) {
+                     const float* wp_f32, const void* wtiles_t_bf16, const void* dy_image,
+                     const float* fparams, const float* mean, const float* rstd, float* dX, float* dXn,
+                     float* dfparams, void* stream) {
   int rc = check_desc(d);
   if (rc != KV_OK) return rc;
   if (d->T == 0) return KV_OK;
@@ -426,19 +436,15 @@ int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, co
       (mean == nullptr || rstd == nullptr || dXn == nullptr))
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
-  if ((d->flags & KV_FLAG_BF16_TC) && wtiles_t_bf16 != nullptr) {
-    rc = tc_supported(*d);
-    if (rc != KV_OK) return rc;
-    return tc_bwd_input(*d, X, dY, act_mask, wtiles_t_bf16, fparams, mean, rstd, dX, dXn, dfparams,
-                        (cudaStream_t)stream);
-  }
+  if ((d->flags & KV_FLAG_BF16_TC) && wtiles_t_bf16 != nullptr && dy_image != nullptr)
+    return tc_bwd_input(*d, X, dy_image, wtiles_t_bf16, fparams, dX, (cudaStream_t)stream);
   if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;
   return simt_bwd_input(*d, X, dY, act_mask, wp_f32, fparams, mean, rstd, dX, dXn, dfparams,
                         (cudaStream_t)stream);
 }
 
 int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
-                      const float* fparams, const float* mean, const float* rstd, float* dWp,
+                      const void* dy_image, const float* fparams, const float* mean, const float* rstd, float* dWp,
                       float* dbias, void* stream) {
   int rc = check_desc(d);
   if (rc != KV_OK) return rc;
@@ -449,10 +455,11 @@ int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, c
   if (d->family == KV_FASTKAN && !(d->flags & KV_FLAG_NO_LAYERNORM) && (mean == nullptr || rstd == nullptr))
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
-  if ((d->flags & KV_FLAG_BF16_TC) && tc_bwd_weight_available(*d)) {
-    rc = tc_supported(*d);
+  if ((d->flags & KV_FLAG_BF16_TC) && dy_image != nullptr && tc_bwd_weight_available(*d)) {
+    rc = tc_bwd_weight(*d, X, dy_image, fparams, dWp, (cudaStream_t)stream);
     if (rc != KV_OK) return rc;
-    return tc_bwd_weight(*d, X, dY, act_mask, fparams, mean, rstd, dWp, dbias, (cudaStream_t)stream);
+    if (dbias == nullptr) return KV_OK;
+    return simt_col_sums(*d, dY, act_mask, dbias, (cudaStream_t)stream);
   }
   return simt_bwd_weight(*d, X, dY, act_mask, fparams, mean, rstd, dWp, dbias, (cudaStream_t)stream);
 }

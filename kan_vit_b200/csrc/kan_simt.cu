@@ -469,6 +469,44 @@ int simt_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, cons
   KV_DISPATCH_FAMILY(d.family, CALL)
 #undef CALL
 }
+// dbias[g][o] += sum_t dY[t, g*out + o] (x ReLU mask): companion of the tensor-core weight gradient
+__global__ void col_sums_kernel(const kv_kan_desc_t d, int rows_per_block, const float* __restrict__ dY,
+                                const float* __restrict__ act_mask, float* __restrict__ dbias) {
+  __shared__ float part[8][33];
+  const int ncols = d.n_groups * d.out_features;
+  const int col = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int sub = threadIdx.x >> 5;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(d.T, r0 + rows_per_block);
+  float acc = 0.0f;
+  if (col < ncols) {
+    for (int t = r0 + sub; t < r1; t += 8) {
+      const size_t idx = (size_t)map_row(t, d.rows_in, d.rows_out, d.row_shift) * d.ldy + col;
+      float v = dY[idx];
+      if ((d.flags & KV_FLAG_RELU) && !(act_mask[idx] > 0.0f)) v = 0.0f;
+      acc += v;
+    }
+  }
+  part[sub][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (sub == 0 && col < ncols) {
+    float s = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += part[k][threadIdx.x];
+    atomicAdd(&dbias[col], s);
+  }
+}
+
+int simt_col_sums(const kv_kan_desc_t& d, const float* dY, const float* mask, float* dbias, cudaStream_t st) {
+  const int ncols = d.n_groups * d.out_features;
+  int ysplit = ceil_div(d.T, 2048);
+  if (ysplit > 64) ysplit = 64;
+  const int rows_per_block = ceil_div(d.T, ysplit);
+  col_sums_kernel<<<dim3(ceil_div(ncols, 32), ysplit), 256, 0, st>>>(d, rows_per_block, dY, mask, dbias);
+  KV_CHECK_LAUNCH("col_sums_kernel");
+  return KV_OK;
+}
+
 int simt_bwd_weight(const kv_kan_desc_t& d, const float* X, const float* dY, const float* mask,
                     const float* fparams, const float* mean, const float* rstd, float* dWp,
                     float* dbias, cudaStream_t st) {

@@ -67,7 +67,8 @@ __host__ __device__ inline Geom make_geom(const kv_kan_desc_t& d) {
   int nb = B_RING_BYTES / (g.S * half_unit);
   g.NB = nb > NB_MAX ? NB_MAX : nb;
   g.NCH = A_UNITS / d.M;
-  g.effkan8 = (d.family == KV_EFFKAN && d.spline_order == 3 && d.grid_size == 5) ? 1 : 0;
+  g.effkan8 = (d.family == KV_EFFKAN && d.spline_order == 3 && d.grid_size == 5 &&
+               (d.flags & KV_FLAG_UNIFORM_GRID)) ? 1 : 0;
   return g;
 }
 
@@ -630,6 +631,297 @@ static int launch_fwd(const FwdParams& p, cudaStream_t st) {
   return KV_OK;
 }
 
+
+// =========================================================================================
+// Input gradient on the tensor cores (default effkan on a uniform grid, LAYOUT_EFFKAN8, x_share == 1):
+//   S[T, K'] = dY[T, out] . Wp[out, K']   (tcgen05, contraction over out)
+//   dX[t, i] = sum_m Phi'_m(x[t,i]) * S[t, (i,m)]   (epilogue, basis derivative recomputed)
+// Both MMA operands arrive by bulk copies: A = dY from a bf16 core-matrix-tiled copy made once per
+// backward pass (dy_image_kernel, shared with the weight-gradient kernel), B = the transposed weight
+// image of tc_pack.  One CTA pair = 256 rows x (n_sub chunks of 16 features = n_sub x 144 columns).
+// =========================================================================================
+constexpr int BI_KS = 4;                       // K=16 steps per stage (64 outputs)
+constexpr int BI_A_STAGE = BM * BI_KS * KU * 2;  // 16 KB
+constexpr int BI_B_STAGE = 32 * 1024;          // >= n_sub * SW * 64 bytes
+constexpr int BI_STAGES = 4;
+constexpr int BI_SMEM = BI_STAGES * (BI_A_STAGE + BI_B_STAGE) + BAR_BYTES;
+
+struct BwdGeom {
+  int SW;        // columns (= B rows) per sub-MMA: one chunk = 16 * M
+  int n_sub;     // chunks per tile
+  int n_tiles;   // column tiles
+  int n_stages;  // contraction stages of 64 outputs
+  int T8, O8;    // dY image extents in core matrices (T padded to 256, out padded to 64)
+  int n_chunks;
+};
+
+__host__ __device__ inline BwdGeom make_bwd_geom(const kv_kan_desc_t& d) {
+  BwdGeom b;
+  b.n_chunks = (d.in_features + KU - 1) / KU;
+  b.SW = KU * d.M;
+  b.n_sub = 512 / b.SW;
+  if (b.n_sub > b.n_chunks) b.n_sub = b.n_chunks;
+  if (b.n_sub * b.SW * 64 > BI_B_STAGE) b.n_sub = BI_B_STAGE / (b.SW * 64);
+  b.n_tiles = (b.n_chunks + b.n_sub - 1) / b.n_sub;
+  b.n_stages = (d.out_features + 63) / 64;
+  b.O8 = b.n_stages * 8;
+  b.T8 = (d.T + 255) / 256 * 32;
+  return b;
+}
+
+// dY fp32 [rows][ldy] (x ReLU mask) -> bf16 image [g][T8][O8][8 rows][8 outputs], zero padded
+__global__ void dy_image_kernel(const kv_kan_desc_t d, const float* __restrict__ dY,
+                                const float* __restrict__ act_mask, __nv_bfloat16* __restrict__ img, BwdGeom b) {
+  const size_t total = (size_t)d.n_groups * b.T8 * b.O8 * 8;
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (size_t)gridDim.x * blockDim.x) {
+    size_t r = idx;
+    const int tr = r % 8; r /= 8;
+    const int o8 = r % b.O8; r /= b.O8;
+    const int t8 = r % b.T8; r /= b.T8;
+    const int g = (int)r;
+    const int t = t8 * 8 + tr;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = 0.0f;
+    if (t < d.T) {
+      const size_t row = (size_t)map_row(t, d.rows_in, d.rows_out, d.row_shift) * d.ldy + (size_t)g * d.out_features;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int o = o8 * 8 + e;
+        if (o < d.out_features) {
+          float w = dY[row + o];
+          if ((d.flags & KV_FLAG_RELU) && !(act_mask[row + o] > 0.0f)) w = 0.0f;
+          v[e] = w;
+        }
+      }
+    }
+    *reinterpret_cast<uint4*>(img + idx * 8) =
+        make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+  }
+}
+
+// transposed weight image for the input gradient:
+//   [g][tile][stage][CTA rank][sub j][o8 (8)][n8 (SW/16)][8 columns][8 outputs]
+__global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const float* __restrict__ wp,
+                                 __nv_bfloat16* __restrict__ wtt, BwdGeom b) {
+  const int M = d.M, in = d.in_features, out = d.out_features, K = in * M;
+  const int half = b.SW / 2;
+  const size_t per_stage_rank = (size_t)b.n_sub * half * 64;
+  const size_t total = (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * per_stage_rank;
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (size_t)gridDim.x * blockDim.x) {
+    size_t r = idx;
+    const int oe = r % 8; r /= 8;
+    const int r8 = r % 8; r /= 8;
+    const int n8 = r % (half / 8); r /= (half / 8);
+    const int o8 = r % 8; r /= 8;
+    const int j = r % b.n_sub; r /= b.n_sub;
+    const int rank = r % 2; r /= 2;
+    const int st = r % b.n_stages; r /= b.n_stages;
+    const int tile = r % b.n_tiles; r /= b.n_tiles;
+    const int g = (int)r;
+    const int c = tile * b.n_sub + j;
+    const int cc = rank * half + n8 * 8 + r8;  // column inside the chunk
+    int i, m;
+    unit_to_im(LAYOUT_EFFKAN8, M, c, cc / 16, (cc / 8) & 1, cc & 7, i, m);
+    const int o = st * 64 + o8 * 8 + oe;
+    float v = 0.0f;
+    if (o < out && i < in && c < b.n_chunks) v = wp[((size_t)g * out + o) * K + (size_t)i * M + m];
+    wtt[idx] = __float2bfloat16_rn(v);
+  }
+}
+
+struct BwdInParams {
+  kv_kan_desc_t d;
+  const float* X;
+  const __nv_bfloat16* dyimg;
+  const __nv_bfloat16* wtt;
+  const float* fparams;
+  float* dX;
+  BwdGeom b;
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8_bwd_input_kernel(const BwdInParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + BI_STAGES * BI_A_STAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BI_STAGES * (BI_A_STAGE + BI_B_STAGE));
+  const uint32_t bar0 = ptx::smem_u32(bars);
+  auto full = [&](int s) { return bar0 + 8u * s; };
+  auto empty = [&](int s) { return bar0 + 8u * (BI_STAGES + s); };
+  const uint32_t tmem_full = bar0 + 8u * (2 * BI_STAGES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * BI_STAGES + 1);
+
+  const kv_kan_desc_t& d = p.d;
+  const BwdGeom b = p.b;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const int tile = blockIdx.y % b.n_tiles;
+  const int m_tile = (blockIdx.y / b.n_tiles) * 2 + (int)rank;
+  const int g = blockIdx.z;
+  const int t0 = m_tile * BM;
+  const int SW = b.SW, n_sub = b.n_sub;
+  const uint32_t b_stage_bytes = (uint32_t)n_sub * SW * 64;  // this CTA's half: n_sub * SW/2 rows * 64 * 2 B
+
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < BI_STAGES; ++s) {
+      ptx::mbar_init(full(s), rank == 0 ? 2 : 1);
+      ptx::mbar_init(empty(s), 1);
+    }
+    ptx::mbar_init(tmem_full, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) {
+    ptx::tmem_alloc2(ptx::smem_u32(tmem_slot), TMEM_COLS);
+    ptx::tmem_relinquish2();
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync_all();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---- loader: per stage 16 x 1 KB of the dY image (this CTA's 128 rows) + one copy of the weight image
+      const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.dyimg) +
+                            ((size_t)g * b.T8 + (size_t)m_tile * 16) * b.O8 * 128;
+      const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.wtt) +
+                            (((size_t)g * b.n_tiles + tile) * b.n_stages * 2 + rank) * (size_t)b_stage_bytes;
+      int s = 0;
+      uint32_t ph = 1;
+      for (int st = 0; st < b.n_stages; ++st) {
+        ptx::mbar_wait(empty(s), ph);
+        ptx::mbar_arrive_expect_tx(full(s), BI_A_STAGE + b_stage_bytes);
+        const uint32_t adst = ptx::smem_u32(sA) + s * BI_A_STAGE;
+#pragma unroll 4
+        for (int t8 = 0; t8 < 16; ++t8)
+          ptx::bulk_g2s(adst + t8 * 1024, asrc + ((size_t)t8 * b.O8 + (size_t)st * 8) * 128, 1024, full(s));
+        ptx::bulk_g2s(ptx::smem_u32(sB) + s * BI_B_STAGE, bsrc + (size_t)st * 2 * b_stage_bytes, b_stage_bytes,
+                      full(s));
+        if (++s == BI_STAGES) { s = 0; ph ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (rank == 0) {
+      // ---- MMA issuer: S[256 rows, n_sub x SW] += dY[256, 16] . Wt[SW, 16]^T
+      const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, SW);
+      const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), 128, 1024);
+      const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)SW * 8, 128);
+      const uint32_t b_sub_step = (uint32_t)(SW * 64) >> 4;    // next sub-MMA's rows
+      const uint32_t b_k_step = (uint32_t)(2 * SW * 8) >> 4;   // next K=16 step: two 8-wide core columns
+      int s = 0;
+      uint32_t ph = 0;
+      for (int st = 0; st < b.n_stages; ++st) {
+        ptx::mbar_wait(full(s), ph);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          const uint64_t da = da0 + (uint64_t)((s * BI_A_STAGE) >> 4);
+          const uint64_t db = db0 + (uint64_t)((s * BI_B_STAGE) >> 4);
+#pragma unroll
+          for (int ks = 0; ks < BI_KS; ++ks) {
+            for (int j = 0; j < n_sub; ++j)
+              ptx::mma2_bf16_ss(tmem_base + j * SW, da + (uint64_t)(ks * 16), db + (uint64_t)(j * b_sub_step + ks * b_k_step),
+                                idesc, (st | ks) > 0);
+          }
+          ptx::tc_commit2(empty(s));
+          if (st + 1 == b.n_stages) ptx::tc_commit2(tmem_full);
+        }
+        __syncwarp();
+        if (++s == BI_STAGES) { s = 0; ph ^= 1; }
+      }
+    } else if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int st = 0; st < b.n_stages; ++st) {
+        ptx::mbar_wait(full(s), ph);
+        ptx::mbar_arrive_cluster(ptx::mapa(full(s), 0));
+        if (++s == BI_STAGES) { s = 0; ph ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---- epilogue: dX[t, i] = sum_e S[.., e] * B'_e(x) + S_base * silu'(x)
+    const int pw = warp - 2;
+    const int q4 = warp & 3, half = pw >> 2;
+    const int te = t0 + q4 * 32 + lane;
+    const bool row_ok = te < d.T;
+    const int in = d.in_features;
+    const float* probe = p.fparams + (size_t)g * d.fparam_stride + (size_t)in * (d.grid_size + 2 * d.spline_order + 1);
+    const float gt0 = probe[1], ginv_h = probe[2];
+    const int xoff = g * in;  // x_share == 1: group g reads its own slice
+    const float* xrow = p.X + (size_t)(row_ok ? te : 0) * d.ldx + xoff;
+    float* dxrow = p.dX + (size_t)(row_ok ? te : 0) * d.ldx + xoff;
+    const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(p.dX) & 15) == 0);
+    // prefetch the inputs of every chunk of this tile while the MMAs run
+    float xs[3][8];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int c = tile * n_sub + j;
+      if (j < n_sub && c < b.n_chunks) load_x8(xrow, c * KU + half * 8, in, row_ok, vec, xs[j]);
+    }
+    ptx::mbar_wait(tmem_full, 0);
+    ptx::tc_fence_after();
+    const uint32_t trow = tmem_base + ((uint32_t)(q4 * 32) << 16);
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int c = tile * n_sub + j;
+      if (j >= n_sub || c >= b.n_chunks) continue;   // warp-uniform
+      uint32_t sa[32], sb2[32], sbase[8];
+      ptx::tmem_ld32(trow + j * SW + half * 64, sa);        // units 4*half, 4*half+1
+      ptx::tmem_ld32(trow + j * SW + half * 64 + 32, sb2);  // units 4*half+2, 4*half+3
+      ptx::tmem_ld8(trow + j * SW + 128 + half * 8, sbase);
+      ptx::tmem_ld_wait();
+      float dx[8];
+#pragma unroll
+      for (int f = 0; f < 8; ++f) {
+        const float xv = xs[j][f];
+        const float u = (xv - gt0) * ginv_h;
+        const float jf = floorf(u);
+        const float s = u - jf;
+        const int j3 = (int)jf - 3;
+        const bool ok = (u >= 0.0f) && (u < 11.0f);
+        const float om = 1.0f - s, s2 = s * s;
+        // d/dx of the four cubic pieces (times 1/h)
+        const float w0 = ok ? -0.5f * om * om * ginv_h : 0.0f;
+        const float w1 = ok ? (1.5f * s2 - 2.0f * s) * ginv_h : 0.0f;
+        const float w2 = ok ? (-1.5f * s2 + s + 0.5f) * ginv_h : 0.0f;
+        const float w3 = ok ? 0.5f * s2 * ginv_h : 0.0f;
+        float acc = 0.0f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int dd = e - j3;
+          const float coef = dd == 0 ? w0 : (dd == 1 ? w1 : (dd == 2 ? w2 : (dd == 3 ? w3 : 0.0f)));
+          const uint32_t sv = (f < 4) ? sa[f * 8 + e] : sb2[(f - 4) * 8 + e];
+          acc = fmaf(coef, __uint_as_float(sv), acc);
+        }
+        const float sg = __fdividef(1.0f, 1.0f + __expf(-xv));
+        acc = fmaf(sg * (1.0f + xv * (1.0f - sg)), __uint_as_float(sbase[f]), acc);
+        dx[f] = acc;
+      }
+      if (row_ok) {
+        const int i0 = c * KU + half * 8;
+        if (vec && i0 + 8 <= in) {
+          *reinterpret_cast<float4*>(dxrow + i0) = make_float4(dx[0], dx[1], dx[2], dx[3]);
+          *reinterpret_cast<float4*>(dxrow + i0 + 4) = make_float4(dx[4], dx[5], dx[6], dx[7]);
+        } else {
+#pragma unroll
+          for (int f = 0; f < 8; ++f)
+            if (i0 + f < in) dxrow[i0 + f] = dx[f];
+        }
+      }
+    }
+    ptx::tc_fence_before();
+  }
+  ptx::cluster_sync_all();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc2(tmem_base, TMEM_COLS);
+  }
+}
+
 }  // namespace tc
 
 int tc_supported(const kv_kan_desc_t& d) {
@@ -642,19 +934,52 @@ size_t tc_wtiles_bytes(const kv_kan_desc_t& d) {
   return (size_t)d.n_groups * gm.n_tiles * gm.tile_elems() * 2;
 }
 
-size_t tc_wtiles_t_bytes(const kv_kan_desc_t&) { return 0; }
+// the tensor-core gradient kernels exist for the default effkan on a uniform grid, one group per slice
+static bool tc_bwd_ok(const kv_kan_desc_t& d) {
+  return tc::make_geom(d).effkan8 && d.x_share == 1 && d.M == 9;
+}
+size_t tc_wtiles_t_bytes(const kv_kan_desc_t& d) {
+  if (!tc_bwd_ok(d)) return 0;
+  const tc::BwdGeom b = tc::make_bwd_geom(d);
+  return (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * b.n_sub * b.SW * 64;
+}
+size_t tc_dy_image_bytes(const kv_kan_desc_t& d) {
+  if (!tc_bwd_ok(d)) return 0;
+  const tc::BwdGeom b = tc::make_bwd_geom(d);
+  return (size_t)d.n_groups * b.T8 * b.O8 * 128;
+}
 bool tc_bwd_weight_available(const kv_kan_desc_t&) { return false; }
+
+static int grid_for(size_t total, int threads) {
+  const size_t blocks = (total + threads - 1) / threads;
+  return (int)(blocks > 148 * 32 ? 148 * 32 : (blocks ? blocks : 1));
+}
 
 int tc_pack(const kv_kan_desc_t& d, const float* wp_f32, const float* fparams, void* wtiles, void* wtiles_t,
             cudaStream_t st) {
-  (void)wtiles_t;
-  if (wtiles == nullptr) return KV_OK;
   const tc::Geom gm = tc::make_geom(d);
-  const size_t total = (size_t)d.n_groups * gm.n_tiles * gm.tile_elems();
-  const int threads = 256;
-  const int blocks = (int)((total + threads - 1) / threads > 148 * 16 ? 148 * 16 : (total + threads - 1) / threads);
-  tc::tc_pack_kernel<<<blocks, threads, 0, st>>>(d, wp_f32, fparams, reinterpret_cast<__nv_bfloat16*>(wtiles), gm);
-  KV_CHECK_LAUNCH("tc_pack_kernel");
+  if (wtiles != nullptr) {
+    const size_t total = (size_t)d.n_groups * gm.n_tiles * gm.tile_elems();
+    tc::tc_pack_kernel<<<grid_for(total, 256), 256, 0, st>>>(d, wp_f32, fparams,
+                                                             reinterpret_cast<__nv_bfloat16*>(wtiles), gm);
+    KV_CHECK_LAUNCH("tc_pack_kernel");
+  }
+  if (wtiles_t != nullptr) {
+    if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
+    const tc::BwdGeom b = tc::make_bwd_geom(d);
+    const size_t total = tc_wtiles_t_bytes(d) / 2;
+    tc::tc_pack_t_kernel<<<grid_for(total, 256), 256, 0, st>>>(d, wp_f32, reinterpret_cast<__nv_bfloat16*>(wtiles_t), b);
+    KV_CHECK_LAUNCH("tc_pack_t_kernel");
+  }
+  return KV_OK;
+}
+
+int tc_dy_image(const kv_kan_desc_t& d, const float* dY, const float* act_mask, void* image, cudaStream_t st) {
+  if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
+  const tc::BwdGeom b = tc::make_bwd_geom(d);
+  const size_t total = (size_t)d.n_groups * b.T8 * b.O8 * 8;
+  tc::dy_image_kernel<<<grid_for(total, 256), 256, 0, st>>>(d, dY, act_mask, reinterpret_cast<__nv_bfloat16*>(image), b);
+  KV_CHECK_LAUNCH("dy_image_kernel");
   return KV_OK;
 }
 
@@ -685,10 +1010,34 @@ int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const flo
   return KV_ERR_BAD_FAMILY;
 }
 
-// backward tensor-core kernels: not built yet -- the bf16 path uses the fp32 SIMT gradients
-int tc_bwd_input(const kv_kan_desc_t&, const float*, const float*, const float*, const void*, const float*,
-                 const float*, const float*, float*, float*, float*, cudaStream_t) { return KV_ERR_UNSUPPORTED; }
-int tc_bwd_weight(const kv_kan_desc_t&, const float*, const float*, const float*, const float*, const float*,
-                  const float*, float*, float*, cudaStream_t) { return KV_ERR_UNSUPPORTED; }
+int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const void* dy_image, const void* wtiles_t,
+                 const float* fparams, float* dX, cudaStream_t st) {
+  if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
+  static bool attr_set = false;
+  if (!attr_set) {
+    KV_CUDA(cudaFuncSetAttribute(tc::effkan8_bwd_input_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 tc::BI_SMEM), "tc_bwd_input smem attribute");
+    attr_set = true;
+  }
+  tc::BwdInParams p;
+  p.d = d;
+  p.X = X;
+  p.dyimg = reinterpret_cast<const __nv_bfloat16*>(dy_image);
+  p.wtt = reinterpret_cast<const __nv_bfloat16*>(wtiles_t);
+  p.fparams = fparams;
+  p.dX = dX;
+  p.b = tc::make_bwd_geom(d);
+  const int n_pairs = ceil_div(d.T, 2 * tc::BM);
+  if ((long long)n_pairs * p.b.n_tiles > 65535 || d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
+  dim3 grid(2, n_pairs * p.b.n_tiles, d.n_groups);
+  tc::effkan8_bwd_input_kernel<<<grid, tc::NTHREADS, tc::BI_SMEM, st>>>(p);
+  KV_CHECK_LAUNCH("effkan8_bwd_input_kernel");
+  return KV_OK;
+}
+
+// weight gradient on the tensor cores: not built yet -- the bf16 path uses the fp32 SIMT kernel
+int tc_bwd_weight(const kv_kan_desc_t&, const float*, const void*, const float*, float*, cudaStream_t) {
+  return KV_ERR_UNSUPPORTED;
+}
 
 }  // namespace kv

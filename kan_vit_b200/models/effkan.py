@@ -118,6 +118,20 @@ class KANLinear(torch.nn.Module):
         return regularize_activation * total + regularize_entropy * entropy
 
     # ------------------------------------------------------------------ hot path
+    def grid_is_uniform(self) -> bool:
+        """True when every feature still shares one uniform knot vector (the constructor's grid; it
+        only changes through update_grid / load_state_dict).  The check reads the buffer once per
+        version of ``grid`` (one device sync), so the kernels may use their closed-form prologue."""
+        g = self.grid
+        key = (g.data_ptr(), g._version, g.device)
+        if getattr(self, "_uniform_key", None) != key:
+            n = g.shape[1]
+            t0, span = g[0, 0], g[0, -1] - g[0, 0]
+            ideal = t0 + torch.arange(n, device=g.device, dtype=g.dtype) * (span / (n - 1))
+            ok = bool(((g - ideal).abs().max() <= 1e-5 * span) & (span > 0))
+            self._uniform_key, self._uniform = key, ok
+        return self._uniform
+
     def _slots(self):
         return [self.base_weight, self.spline_weight,
                 self.spline_scaler if self.enable_standalone_scale_spline else None, self.grid]

@@ -123,15 +123,19 @@ class KanSpec:
         d = self.desc(0, 0, 0)
         self.fparam_stride = max(L.load().kv_kan_fparam_count(C.byref(d)), 0)
         self._tbl_cache = None     # (ptrs, device tensor)
-        a, b = C.c_size_t(0), C.c_size_t(0)
-        rc = L.load().kv_kan_tc_bytes(C.byref(self.desc(0, self.n_slices * in_features, n_groups * out_features)),
-                                      C.byref(a), C.byref(b))
-        self.tc_bytes = (a.value, b.value) if rc == 0 else None   # None: no tensor-core kernel for this shape
+        self.dyn_flags = None      # callable -> per-call flags (effkan: KV_FLAG_UNIFORM_GRID when the grid is)
         self._goff_cache = None    # (shapes key, offsets tensor, mask, total, views meta)
 
     @property
     def n_slices(self):
         return self.n_groups // self.x_share
+
+    def tc_sizes(self, d):
+        """(forward image, input-gradient image, dY image) bytes of the tensor-core path for this call,
+        or None when the layer has no tensor-core kernel (it then runs on the fp32 kernels)."""
+        a, b, c = C.c_size_t(0), C.c_size_t(0), C.c_size_t(0)
+        rc = L.load().kv_kan_tc_bytes(C.byref(d), C.byref(a), C.byref(b), C.byref(c))
+        return (a.value, b.value, c.value) if rc == 0 else None
 
     def desc(self, T, ldx, ldy, rows_in=0, rows_out=0, row_shift=0, extra_flags=0) -> L.KanDesc:
         return L.KanDesc(self.family, T, self.in_features, self.out_features, self.n_groups,
@@ -148,7 +152,7 @@ class KanSpec:
         return self._tbl_cache[1]
 
     # -- packed weights / prologue parameters (cached until a parameter is modified)
-    def packed(self, flat, device, want_tc: bool):
+    def packed(self, flat, device, tc_sizes, flags=0):
         # No cache across calls: fused optimizers (torch.optim.Adam(fused=True)) update parameters
         # without bumping Tensor._version, so a (data_ptr, version) key would serve stale weights.
         # The pack is one small memory-bound launch per layer; forward hands it to backward via ctx.
@@ -160,12 +164,12 @@ class KanSpec:
         has_bias = self.family in _FAMILY_BIAS_SLOT and any(
             flat[q * L.KV_PTRS_PER_GROUP + _FAMILY_BIAS_SLOT[self.family]] is not None for q in range(g))
         bias = torch.empty((g, o), dtype=torch.float32, device=device) if has_bias else None
-        d = self.desc(0, self.n_slices * self.in_features, g * o)
+        d = self.desc(0, self.n_slices * self.in_features, g * o, extra_flags=flags)
         wt = wtt = None
-        if want_tc:
-            wt = torch.empty((self.tc_bytes[0],), dtype=torch.uint8, device=device)
-            if self.tc_bytes[1]:
-                wtt = torch.empty((self.tc_bytes[1],), dtype=torch.uint8, device=device)
+        if tc_sizes is not None:
+            wt = torch.empty((tc_sizes[0],), dtype=torch.uint8, device=device)
+            if tc_sizes[1]:
+                wtt = torch.empty((tc_sizes[1],), dtype=torch.uint8, device=device)
         _call("kv_kan_pack", lib.kv_kan_pack, C.byref(d), tbl.data_ptr(), wp.data_ptr(), L.ptr(wt), L.ptr(wtt),
                                 fp.data_ptr() if self.fparam_stride else None, L.ptr(bias), _stream())
         pk = {"wp": wp, "fp": fp if self.fparam_stride else None, "bias": bias, "tbl": tbl, "wt": wt, "wtt": wtt}
@@ -207,11 +211,16 @@ class _KanFn(torch.autograd.Function):
         rows_in, rows_out, row_shift = cfg.get("rows_in", 0), cfg.get("rows_out", 0), cfg.get("row_shift", 0)
         rows = T if rows_in == 0 else (T // rows_in) * rows_out
         extra = L.KV_FLAG_RELU if cfg.get("relu") else 0
-        use_tc = _PRECISION == "bf16" and spec.tc_bytes is not None
-        if use_tc:
-            extra |= L.KV_FLAG_BF16_TC
-        d = spec.desc(T, n_in, n_out, rows_in, rows_out, row_shift, extra)
-        pk = spec.packed(flat, x.device, use_tc)
+        if spec.dyn_flags is not None:
+            extra |= spec.dyn_flags()
+        tc_sizes = None
+        if _PRECISION == "bf16":
+            d = spec.desc(T, n_in, n_out, rows_in, rows_out, row_shift, extra | L.KV_FLAG_BF16_TC)
+            tc_sizes = spec.tc_sizes(d)
+        if tc_sizes is None:
+            d = spec.desc(T, n_in, n_out, rows_in, rows_out, row_shift, extra)
+        pk = spec.packed(flat, x.device, tc_sizes, d.flags & (L.KV_FLAG_UNIFORM_GRID | L.KV_FLAG_BF16_TC))
+        pk["tc_sizes"] = tc_sizes
         mean = rstd = None
         if spec.family == L.KV_FASTKAN and not (spec.flags & L.KV_FLAG_NO_LAYERNORM):
             mean = torch.empty((T, spec.n_slices), dtype=torch.float32, device=x.device)
@@ -251,6 +260,11 @@ class _KanFn(torch.autograd.Function):
         dfp = None
         if spec.family in (L.KV_SINE, L.KV_FASTKAN):
             dfp = torch.zeros((g, spec.fparam_stride), dtype=torch.float32, device=dev)
+        dyimg = None
+        if pk["tc_sizes"] is not None and pk["tc_sizes"][2]:
+            dyimg = torch.empty((pk["tc_sizes"][2],), dtype=torch.uint8, device=dev)
+            _call("kv_kan_dy_image", lib.kv_kan_dy_image, C.byref(d), dy.data_ptr(), L.ptr(ymask), dyimg.data_ptr(), st,
+                  work=6.0 * T * g * o)
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x)
@@ -258,7 +272,7 @@ class _KanFn(torch.autograd.Function):
             if mean is not None:
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
-                                         pk["wp"].data_ptr(), L.ptr(pk["wtt"]), L.ptr(pk["fp"]), L.ptr(mean),
+                                         pk["wp"].data_ptr(), L.ptr(pk["wtt"]), L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean),
                                          L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
@@ -271,7 +285,7 @@ class _KanFn(torch.autograd.Function):
             if mean is not None:
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
-                                         pk["wp"].data_ptr(), L.ptr(pk["wtt"]), L.ptr(pk["fp"]), L.ptr(mean),
+                                         pk["wp"].data_ptr(), L.ptr(pk["wtt"]), L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean),
                                          L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
@@ -281,7 +295,7 @@ class _KanFn(torch.autograd.Function):
             dwp = torch.zeros((g, o, K), dtype=torch.float32, device=dev)
             dbias = torch.zeros((g, o), dtype=torch.float32, device=dev) if pk["bias"] is not None else None
             _call("kv_kan_bwd_weight", lib.kv_kan_bwd_weight, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
-                                          L.ptr(pk["fp"]), L.ptr(mean), L.ptr(rstd), dwp.data_ptr(),
+                                          L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean), L.ptr(rstd), dwp.data_ptr(),
                                           L.ptr(dbias), st, work=_kan_flops(spec, T))
             off_t, meta, total = spec.grad_layout(flat, dev)
             gflat = torch.empty((total,), dtype=torch.float32, device=dev)

@@ -100,3 +100,31 @@ def test_bf16_layer_vs_own_fp32(family, T, i, o):
     assert relerr(y16, y32) < TOL_BF16
     # the tensor-core kernel must actually have run: results differ from the exact path
     assert not torch.equal(y16, y32)
+
+
+@pytest.mark.parametrize("T,i,o", [(300, 80, 528), (129, 24, 40), (700, 768, 200), (260, 48, 3072)])
+def test_bf16_effkan_gradients_vs_own_fp32(T, i, o):
+    """Tensor-core gradient kernels (input gradient S = dY.W with the B-spline derivative contracted in
+    the epilogue; weight gradient Phi^T.dY) against the exact fp32 kernels of this library."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(1)
+    m = K.KANLinear(i, o).to(_dev())
+    spec = make_spec([m])
+    x0 = torch.randn(T, i, device=_dev())
+    dy = torch.randn(T, o, device=_dev())
+
+    def run(mode):
+        K.set_precision(mode)
+        m.zero_grad(set_to_none=True)
+        x = x0.clone().requires_grad_(True)
+        ops.kan_apply(x, spec, [slots_of(m)]).backward(dy)
+        return x.grad, {k: p.grad.clone() for k, p in m.named_parameters()}
+
+    gx16, gp16 = run("bf16")
+    gx32, gp32 = run("fp32")
+    K.set_precision("bf16")
+    assert relerr(gx16, gx32) < TOL_BF16
+    for k in gp32:
+        assert relerr(gp16[k], gp32[k]) < TOL_BF16, k
