@@ -664,7 +664,11 @@ __host__ __device__ inline BwdGeom make_bwd_geom(const kv_kan_desc_t& d) {
   if (b.n_sub * b.SW * 64 > BI_B_STAGE) b.n_sub = BI_B_STAGE / (b.SW * 64);
   b.n_tiles = (b.n_chunks + b.n_sub - 1) / b.n_sub;
   b.n_stages = (d.out_features + 63) / 64;
-  b.O8 = b.n_stages * 8;
+  {
+    const Geom gm = make_geom(d);
+    const int cover = gm.n_tiles * gm.BN;  // the weight-gradient kernel reads whole output tiles
+    b.O8 = (cover > b.n_stages * 64 ? (cover + 7) / 8 : b.n_stages * 8);
+  }
   b.T8 = (d.T + 255) / 256 * 32;
   return b;
 }
@@ -922,6 +926,276 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
   }
 }
 
+
+// =========================================================================================
+// Weight gradient on the tensor cores:  dWp^T[K', out] = Phi^T[K', T] . dY[T, out]  (contraction over T)
+// The expensive, recomputed operand (the basis) is the M side: one CTA owns 128 basis columns K'
+// (default effkan: the 8 B-splines of one 16-feature chunk, or the SiLU column of 128 features; Linear:
+// 128 features), the pair 256, and reuses every value against up to 512 outputs.  Both operands are
+// "MN-major" (the contraction index t is the strided one): A = the same 16-byte basis vectors the forward
+// producers build, B = the bf16 dY image.  T is split over CTAs; partial sums are added with fp32 RED.
+// =========================================================================================
+constexpr int BW_A_STAGE = 16 * 1024;   // 64 t x 128 K' x 2 B
+constexpr int BW_B_STAGE = 32 * 1024;   // 64 t x BN/2 x 2 B
+constexpr int BW_NA = 3, BW_NB = 4;
+constexpr int BW_SMEM = BW_NA * BW_A_STAGE + BW_NB * BW_B_STAGE + BAR_BYTES;
+
+struct BwdWParams {
+  kv_kan_desc_t d;
+  const float* X;
+  const __nv_bfloat16* dyimg;
+  const float* fparams;
+  float* dWp;
+  BwdGeom b;
+  Geom gm;       // BN / n_tiles of the output dimension
+  int KT;        // number of 128-wide K' tiles
+  int n_kpairs;  // ceil(KT / 2)
+  int tsplits, rows_per_split;
+};
+
+template <int F>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_bwd_weight_kernel(const BwdWParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + BW_NA * BW_A_STAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BW_NA * BW_A_STAGE + BW_NB * BW_B_STAGE);
+  const uint32_t bar0 = ptx::smem_u32(bars);
+  auto fullA = [&](int s) { return bar0 + 8u * s; };
+  auto emptyA = [&](int s) { return bar0 + 8u * (BW_NA + s); };
+  auto fullB = [&](int s) { return bar0 + 8u * (2 * BW_NA + s); };
+  auto emptyB = [&](int s) { return bar0 + 8u * (2 * BW_NA + BW_NB + s); };
+  const uint32_t tmem_full = bar0 + 8u * (2 * BW_NA + 2 * BW_NB);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * BW_NA + 2 * BW_NB + 1);
+
+  const kv_kan_desc_t& d = p.d;
+  const BwdGeom b = p.b;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const int n_tile = blockIdx.y % p.gm.n_tiles;
+  const int kt = (blockIdx.y / p.gm.n_tiles) * 2 + (int)rank;   // this CTA's K' tile
+  const int g = blockIdx.z / p.tsplits, ts = blockIdx.z % p.tsplits;
+  const int BN = p.gm.BN;
+  const int n1 = BN > 256 ? 256 : BN, n2 = BN - n1;
+  const int row0 = ts * p.rows_per_split;
+  const int row1 = min(d.T, row0 + p.rows_per_split);
+  const int n_stages = (row1 - row0 + 63) / 64;
+  const uint32_t b_stage_bytes = (uint32_t)BN * 64;
+  const int in = d.in_features;
+  const bool tile_live = kt < p.KT;
+  // tile kind: effkan spline tile (chunk kt) | effkan SiLU tile | linear feature tile
+  const bool spline_tile = (F == KV_EFFKAN) && kt < b.n_chunks;
+  const int feat0 = spline_tile ? kt * KU : ((F == KV_EFFKAN) ? (kt - b.n_chunks) * 128 : kt * 128);
+
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < BW_NA; ++s) {
+      ptx::mbar_init(fullA(s), 2 * N_PRODUCER_WARPS);
+      ptx::mbar_init(emptyA(s), 1);
+    }
+    for (int s = 0; s < BW_NB; ++s) {
+      ptx::mbar_init(fullB(s), rank == 0 ? 2 : 1);
+      ptx::mbar_init(emptyB(s), 1);
+    }
+    ptx::mbar_init(tmem_full, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) {
+    ptx::tmem_alloc2(ptx::smem_u32(tmem_slot), TMEM_COLS);
+    ptx::tmem_relinquish2();
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync_all();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---- loader: this CTA's half of the dY rows of each sub-MMA, 8 row blocks per stage
+      const uint8_t* img = reinterpret_cast<const uint8_t*>(p.dyimg) + (size_t)g * b.T8 * b.O8 * 128;
+      const int o8_1 = (n_tile * BN + (int)rank * (n1 / 2)) / 8;
+      const int o8_2 = (n_tile * BN + n1 + (int)rank * (n2 / 2)) / 8;
+      int s = 0;
+      uint32_t ph = 1;
+      for (int st = 0; st < n_stages; ++st) {
+        ptx::mbar_wait(emptyB(s), ph);
+        ptx::mbar_arrive_expect_tx(fullB(s), b_stage_bytes);
+        const uint32_t dst = ptx::smem_u32(sB) + s * BW_B_STAGE;
+        const int t8g = (row0 + st * 64) / 8;
+        for (int t8 = 0; t8 < 8; ++t8) {
+          const uint8_t* rowp = img + (size_t)(t8g + t8) * b.O8 * 128;
+          ptx::bulk_g2s(dst + t8 * (n1 * 8), rowp + (size_t)o8_1 * 128, n1 * 8, fullB(s));
+          if (n2) ptx::bulk_g2s(dst + n1 * 64 + t8 * (n2 * 8), rowp + (size_t)o8_2 * 128, n2 * 8, fullB(s));
+        }
+        if (++s == BW_NB) { s = 0; ph ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (rank == 0) {
+      // ---- MMA issuer: D[256 K', BN] += Phi^T[256, 16 t] . dY^T[BN, 16 t]^T, both operands MN-major
+      const uint32_t idesc1 = ptx::make_idesc_bf16(2 * BM, n1, 1, 1);
+      const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(2 * BM, n2, 1, 1) : 0u;
+      // A step: [t8 (2)][K' block (16)][t%8][16 B]: K-block stride (LBO) 2048, MN-block stride (SBO) 128
+      const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), 2048, 128);
+      // B sub-tile: [t8 (8)][o8 (nj/16)][t%8][16 B]: LBO = nj*8, SBO = 128
+      const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)n1 * 8, 128);
+      const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 64, (uint32_t)n2 * 8, 128);
+      int sa = 0, sb = 0;
+      uint32_t pha = 0, phb = 0;
+      for (int st = 0; st < n_stages; ++st) {
+        ptx::mbar_wait(fullA(sa), pha);
+        ptx::mbar_wait(fullB(sb), phb);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          const uint64_t da = da0 + (uint64_t)((sa * BW_A_STAGE) >> 4);
+          const uint64_t db1 = db1_0 + (uint64_t)((sb * BW_B_STAGE) >> 4);
+          const uint64_t db2 = db2_0 + (uint64_t)((sb * BW_B_STAGE) >> 4);
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            ptx::mma2_bf16_ss(tmem_base, da + (uint64_t)(ks * 256), db1 + (uint64_t)((ks * 2 * n1 * 8) >> 4), idesc1,
+                              (st | ks) > 0);
+            if (n2)
+              ptx::mma2_bf16_ss(tmem_base + 256, da + (uint64_t)(ks * 256), db2 + (uint64_t)((ks * 2 * n2 * 8) >> 4),
+                                idesc2, (st | ks) > 0);
+          }
+          ptx::tc_commit2(emptyA(sa));
+          ptx::tc_commit2(emptyB(sb));
+          if (st + 1 == n_stages) ptx::tc_commit2(tmem_full);
+        }
+        __syncwarp();
+        if (++sa == BW_NA) { sa = 0; pha ^= 1; }
+        if (++sb == BW_NB) { sb = 0; phb ^= 1; }
+      }
+    } else if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int st = 0; st < n_stages; ++st) {
+        ptx::mbar_wait(fullB(s), ph);
+        ptx::mbar_arrive_cluster(ptx::mapa(fullB(s), 0));
+        if (++s == BW_NB) { s = 0; ph ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---- A producers: basis values of 64 rows x this tile's features per stage
+    const int ptid = threadIdx.x - 64;
+    const int tl = ptid & 63, fb = ptid >> 6;          // row inside the stage, feature block (0..3)
+    const int xoff = (g / d.x_share) * in;
+    const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0);
+    float gt0 = 0.f, ginv_h = 0.f;
+    if (F == KV_EFFKAN) {
+      const float* probe = p.fparams + (size_t)g * d.fparam_stride + (size_t)in * (d.grid_size + 2 * d.spline_order + 1);
+      gt0 = probe[1];
+      ginv_h = probe[2];
+    }
+    // byte offset of this row inside a K=16 step image: [t8 (2)][block (16)][t%8][16 B]
+    const int row_off = (tl >> 4) * 4096 + ((tl >> 3) & 1) * 2048 + (tl & 7) * 16;
+    int s = 0;
+    uint32_t ph = 1;
+    for (int st = 0; st < n_stages; ++st) {
+      const int t = row0 + st * 64 + tl;
+      const bool row_ok = t < row1;
+      const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
+      float xv[32];
+      if (tile_live) {
+        if (spline_tile) {
+          // 4 features per thread: features feat0 + 4*fb .. +3
+          const int i0 = feat0 + 4 * fb;
+          if (row_ok && vec && i0 + 4 <= in) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(xrow + i0));
+            xv[0] = a.x; xv[1] = a.y; xv[2] = a.z; xv[3] = a.w;
+          } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) xv[q] = (row_ok && i0 + q < in) ? __ldg(xrow + i0 + q) : 0.0f;
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            float t8v[8];
+            load_x8(xrow, feat0 + 32 * fb + 8 * k, in, row_ok, vec, t8v);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) xv[8 * k + q] = t8v[q];
+          }
+        }
+      }
+      ptx::mbar_wait(emptyA(s), ph);
+      uint8_t* base = sA + s * BW_A_STAGE + row_off;
+      if (tile_live) {
+        if (spline_tile) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float u = (xv[q] - gt0) * ginv_h;
+            const float jf = floorf(u);
+            const float sfr = u - jf;
+            const int j = (int)jf;
+            const bool ok = (u >= 0.0f) && (u < 11.0f);
+            const float s2 = sfr * sfr, s3 = s2 * sfr, om = 1.0f - sfr;
+            const float w0 = om * om * om * (1.0f / 6.0f);
+            const float w1 = fmaf(0.5f, s3, fmaf(-1.0f, s2, 2.0f / 3.0f));
+            const float w2 = fmaf(-0.5f, s3, fmaf(0.5f, s2, fmaf(0.5f, sfr, 1.0f / 6.0f)));
+            const float w3 = s3 * (1.0f / 6.0f);
+            uint64_t W = (uint64_t)pack_bf16(w0, w1) | ((uint64_t)pack_bf16(w2, w3) << 32);
+            if (!ok) W = 0;
+            const int sh = (j - 3) * 16;
+            const uint64_t lo = shl64(W, sh) | shr64(W, -sh);
+            const uint64_t hi = shl64(W, sh - 64) | shr64(W, 64 - sh);
+            // feature f = 4*fb + q of the chunk owns K' block f (8 splines)
+            sts128(base + (4 * fb + q) * 128, (uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            float v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v[q] = (F == KV_EFFKAN) ? fast_silu(xv[8 * k + q]) : xv[8 * k + q];
+            sts128(base + (4 * fb + k) * 128, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                   pack_bf16(v[6], v[7]));
+          }
+        }
+      }
+      ptx::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(s), 0));
+      if (++s == BW_NA) { s = 0; ph ^= 1; }
+    }
+    // ---- epilogue: TMEM lane = basis column K', column = output; fp32 RED into dWp[g][o][i*M+m]
+    ptx::mbar_wait(tmem_full, 0);
+    ptx::tc_fence_after();
+    if (tile_live) {
+      const int pw = warp - 2;
+      const int q4 = warp & 3, half = pw >> 2;
+      const int l = q4 * 32 + lane;  // K' index inside the tile
+      int i, m;
+      if (spline_tile) {
+        i = feat0 + (l >> 3);  // K' block f of the tile = feature f of the chunk, 8 splines each
+        m = l & 7;
+      } else {
+        i = feat0 + l;
+        m = (F == KV_EFFKAN) ? 8 : 0;
+      }
+      const int M = d.M, K = in * M, out = d.out_features;
+      float* dst = p.dWp + (size_t)g * out * K + (size_t)i * M + m;
+      for (int cb = half; cb * 32 < BN; cb += 2) {
+        uint32_t rr[32];
+        ptx::tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + cb * 32, rr);
+        ptx::tmem_ld_wait();
+        if (i < in) {
+#pragma unroll
+          for (int jn = 0; jn < 32; ++jn) {
+            const int o = n_tile * BN + cb * 32 + jn;
+            if (cb * 32 + jn < BN && o < out) atomicAdd(dst + (size_t)o * K, __uint_as_float(rr[jn]));
+          }
+        }
+      }
+    }
+    ptx::tc_fence_before();
+  }
+  ptx::cluster_sync_all();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc2(tmem_base, TMEM_COLS);
+  }
+}
+
 }  // namespace tc
 
 int tc_supported(const kv_kan_desc_t& d) {
@@ -948,7 +1222,7 @@ size_t tc_dy_image_bytes(const kv_kan_desc_t& d) {
   const tc::BwdGeom b = tc::make_bwd_geom(d);
   return (size_t)d.n_groups * b.T8 * b.O8 * 128;
 }
-bool tc_bwd_weight_available(const kv_kan_desc_t&) { return false; }
+bool tc_bwd_weight_available(const kv_kan_desc_t& d) { return tc_bwd_ok(d); }
 
 static int grid_for(size_t total, int threads) {
   const size_t blocks = (total + threads - 1) / threads;
@@ -1035,9 +1309,42 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const void* dy_image, c
   return KV_OK;
 }
 
-// weight gradient on the tensor cores: not built yet -- the bf16 path uses the fp32 SIMT kernel
-int tc_bwd_weight(const kv_kan_desc_t&, const float*, const void*, const float*, float*, cudaStream_t) {
-  return KV_ERR_UNSUPPORTED;
+int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, const float* fparams, float* dWp,
+                  cudaStream_t st) {
+  if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
+  static bool attr_set = false;
+  if (!attr_set) {
+    KV_CUDA(cudaFuncSetAttribute(tc::kan_tc_bwd_weight_kernel<KV_EFFKAN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 tc::BW_SMEM), "tc_bwd_weight smem attribute");
+    attr_set = true;
+  }
+  tc::BwdWParams p;
+  p.d = d;
+  p.X = X;
+  p.dyimg = reinterpret_cast<const __nv_bfloat16*>(dy_image);
+  p.fparams = fparams;
+  p.dWp = dWp;
+  p.b = tc::make_bwd_geom(d);
+  p.gm = tc::make_geom(d);
+  p.KT = p.b.n_chunks + (p.b.n_chunks + 7) / 8;
+  p.n_kpairs = (p.KT + 1) / 2;
+  // split T so that the grid fills the 74 CTA-pair slots evenly; every split keeps >= 512 rows
+  const int P = p.n_kpairs * p.gm.n_tiles * d.n_groups;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int s = 1; s <= 32; ++s) {
+    if (s > 1 && d.T / s < 512) break;
+    const double waves = (double)P * s / 74.0;
+    const double eff = waves / (double)(long long)(waves + 0.999999);
+    if (eff > best_eff + 0.03) { best_eff = eff; best = s; }
+  }
+  p.tsplits = best;
+  p.rows_per_split = (ceil_div(d.T, best) + 63) / 64 * 64;
+  if ((long long)p.n_kpairs * p.gm.n_tiles > 65535 || (long long)d.n_groups * best > 65535) return KV_ERR_BAD_SHAPE;
+  dim3 grid(2, p.n_kpairs * p.gm.n_tiles, d.n_groups * best);
+  tc::kan_tc_bwd_weight_kernel<KV_EFFKAN><<<grid, tc::NTHREADS, tc::BW_SMEM, st>>>(p);
+  KV_CHECK_LAUNCH("kan_tc_bwd_weight_kernel");
+  return KV_OK;
 }
 
 }  // namespace kv
