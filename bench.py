@@ -215,6 +215,7 @@ def run_gpu_arm(args):
     chw, npatch, nb, d, h, out_d, kind, kan_mlp, batch, cpu_batch = CONFIGS[name]
     if args.batch:
         batch = args.batch
+    K.set_precision("bf16" if args.bf16 else "fp32")
     torch.manual_seed(0)  # identical replicas on every rank
     model = K.VisionTransformer(chw, npatch, nb, d, h, out_d, kind, kan_mlp=kan_mlp).to(dev)
     if world > 1:

@@ -52,5 +52,14 @@ def make_spec(modules, x_share=1):
     spec = KanSpec(fam, i, o, n_groups=len(modules), x_share=x_share, **kw)
     if fam == L.KV_EFFKAN:
         mods = list(modules)
-        spec.dyn_flags = lambda: L.KV_FLAG_UNIFORM_GRID if all(m.grid_is_uniform() for m in mods) else 0
+
+
+        def uniform_flag():
+            # one uniform knot vector shared by every feature of every grouped module
+            if not all(m.grid_is_uniform() for m in mods):
+                return 0
+            ends = {m.grid_ends() for m in mods}
+            return L.KV_FLAG_UNIFORM_GRID if len(ends) == 1 else 0
+
+        spec.dyn_flags = uniform_flag
     return spec

@@ -330,6 +330,24 @@ const char* kv_last_cuda_error(void) { return g_cuda_err; }
 
 unsigned long long kv_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
+// Tensor-core view of a descriptor.  Groups that share an input slice (x_share > 1: the q/k/v maps of one
+// head, attention.py:196-197) and one uniform knot vector are ONE layer with x_share*out outputs: the
+// packed weights [g][out][K], bias [g][out], dY/Y columns g*out+o and dWp are the same memory either way,
+// so the merge is a reinterpretation.  The basis is then evaluated once per slice instead of once per
+// group, and the gradient kernels (one group per slice) apply.  Prologue parameters are read from the
+// first group of each slice (fparam_stride scaled), which the uniform-grid flag makes equal to the others.
+static kv_kan_desc_t tc_view(const kv_kan_desc_t& d) {
+  kv_kan_desc_t v = d;
+  if ((d.flags & KV_FLAG_BF16_TC) && d.family == KV_EFFKAN && (d.flags & KV_FLAG_UNIFORM_GRID) && d.x_share > 1 &&
+      d.n_groups % d.x_share == 0 && d.out_features * d.x_share <= 512) {
+    v.n_groups = d.n_groups / d.x_share;
+    v.out_features = d.out_features * d.x_share;
+    v.fparam_stride = d.fparam_stride * d.x_share;
+    v.x_share = 1;
+  }
+  return v;
+}
+
 int kv_kan_fparam_count(const kv_kan_desc_t* d) {
   if (d == nullptr) return KV_ERR_BAD_ARG;
   if (d->family < KV_LINEAR || d->family > KV_FOURIER) return KV_ERR_BAD_FAMILY;
@@ -362,7 +380,7 @@ int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32
     rc = tc_supported(*d);
     if (rc != KV_OK) return rc;
     if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;  // layout choice reads the grid probe
-    rc = tc_pack(*d, wp_f32, fparams, wtiles_bf16, wtiles_t_bf16, st);
+    rc = tc_pack(tc_view(*d), wp_f32, fparams, wtiles_bf16, wtiles_t_bf16, st);
     if (rc != KV_OK) return rc;
   }
   return KV_OK;
@@ -373,9 +391,10 @@ int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles
   if (rc != KV_OK) return rc;
   rc = tc_supported(*d);
   if (rc != KV_OK) return rc;
-  if (wtiles_bytes) *wtiles_bytes = tc_wtiles_bytes(*d);
-  if (wtiles_t_bytes) *wtiles_t_bytes = tc_wtiles_t_bytes(*d);
-  if (dy_image_bytes) *dy_image_bytes = tc_dy_image_bytes(*d);
+  const kv_kan_desc_t v = tc_view(*d);
+  if (wtiles_bytes) *wtiles_bytes = tc_wtiles_bytes(v);
+  if (wtiles_t_bytes) *wtiles_t_bytes = tc_wtiles_t_bytes(v);
+  if (dy_image_bytes) *dy_image_bytes = tc_dy_image_bytes(v);
   return KV_OK;
 }
 
@@ -385,7 +404,7 @@ int kv_kan_dy_image(const kv_kan_desc_t* d, const float* dY, const float* act_ma
   if (d->T == 0) return KV_OK;
   if (dY == nullptr || dy_image == nullptr) return KV_ERR_BAD_ARG;
   if ((d->flags & KV_FLAG_RELU) && act_mask == nullptr) return KV_ERR_BAD_ARG;
-  return tc_dy_image(*d, dY, act_mask, dy_image, (cudaStream_t)stream);
+  return tc_dy_image(tc_view(*d), dY, act_mask, dy_image, (cudaStream_t)stream);
 }
 
 int kv_row_stats(const float* X, int T, int ldx, int n_slices, int width, float eps, float* mean,
@@ -416,7 +435,7 @@ int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, cons
     if (wtiles_bf16 == nullptr) return KV_ERR_BAD_ARG;
     rc = tc_supported(*d);
     if (rc != KV_OK) return rc;
-    return tc_fwd(*d, X, wtiles_bf16, fparams, bias, mean, rstd, residual, pos, Y, (cudaStream_t)stream);
+    return tc_fwd(tc_view(*d), X, wtiles_bf16, fparams, bias, mean, rstd, residual, pos, Y, (cudaStream_t)stream);
   }
   if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;
   return simt_fwd(*d, X, wp_f32, fparams, bias, mean, rstd, residual, pos, Y, (cudaStream_t)stream);
@@ -437,7 +456,7 @@ int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, co
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
   if ((d->flags & KV_FLAG_BF16_TC) && wtiles_t_bf16 != nullptr && dy_image != nullptr)
-    return tc_bwd_input(*d, X, dy_image, wtiles_t_bf16, fparams, dX, (cudaStream_t)stream);
+    return tc_bwd_input(tc_view(*d), X, dy_image, wtiles_t_bf16, fparams, dX, (cudaStream_t)stream);
   if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;
   return simt_bwd_input(*d, X, dY, act_mask, wp_f32, fparams, mean, rstd, dX, dXn, dfparams,
                         (cudaStream_t)stream);
@@ -455,8 +474,8 @@ int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, c
   if (d->family == KV_FASTKAN && !(d->flags & KV_FLAG_NO_LAYERNORM) && (mean == nullptr || rstd == nullptr))
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
-  if ((d->flags & KV_FLAG_BF16_TC) && dy_image != nullptr && tc_bwd_weight_available(*d)) {
-    rc = tc_bwd_weight(*d, X, dy_image, fparams, dWp, (cudaStream_t)stream);
+  if ((d->flags & KV_FLAG_BF16_TC) && dy_image != nullptr && tc_bwd_weight_available(tc_view(*d))) {
+    rc = tc_bwd_weight(tc_view(*d), X, dy_image, fparams, dWp, (cudaStream_t)stream);
     if (rc != KV_OK) return rc;
     if (dbias == nullptr) return KV_OK;
     return simt_col_sums(*d, dY, act_mask, dbias, (cudaStream_t)stream);

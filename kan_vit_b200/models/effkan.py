@@ -130,7 +130,13 @@ class KANLinear(torch.nn.Module):
             ideal = t0 + torch.arange(n, device=g.device, dtype=g.dtype) * (span / (n - 1))
             ok = bool(((g - ideal).abs().max() <= 1e-5 * span) & (span > 0))
             self._uniform_key, self._uniform = key, ok
+            self._ends = (float(t0), float(g[0, -1]))
         return self._uniform
+
+    def grid_ends(self):
+        """(first, last) knot of feature 0, cached with grid_is_uniform()."""
+        self.grid_is_uniform()
+        return self._ends
 
     def _slots(self):
         return [self.base_weight, self.spline_weight,

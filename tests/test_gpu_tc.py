@@ -128,3 +128,35 @@ def test_bf16_effkan_gradients_vs_own_fp32(T, i, o):
     assert relerr(gx16, gx32) < TOL_BF16
     for k in gp32:
         assert relerr(gp16[k], gp32[k]) < TOL_BF16, k
+
+
+@pytest.mark.parametrize("T,H,dh", [(394, 12, 64), (150, 2, 32), (300, 3, 48)])
+def test_bf16_grouped_qkv_effkan_vs_own_fp32(T, H, dh):
+    """The per-head q/k/v maps (3H groups, three per input slice) on the tensor-core path, where the three
+    maps of a head run as one layer with 3*d_head outputs (api.cu tc_view), against the exact fp32 kernels."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(2)
+    mods = [K.KANLinear(dh, dh).to(_dev()) for _ in range(3 * H)]
+    spec = make_spec(mods, x_share=3)
+    x0 = torch.randn(T, H * dh, device=_dev())
+    dy = torch.randn(T, 3 * H * dh, device=_dev())
+
+    def run(mode):
+        K.set_precision(mode)
+        for m in mods:
+            m.zero_grad(set_to_none=True)
+        x = x0.clone().requires_grad_(True)
+        y = ops.kan_apply(x, spec, [slots_of(m) for m in mods])
+        y.backward(dy)
+        return y.detach(), x.grad, [{k: p.grad.clone() for k, p in m.named_parameters()} for m in mods]
+
+    y16, gx16, gp16 = run("bf16")
+    y32, gx32, gp32 = run("fp32")
+    K.set_precision("bf16")
+    assert relerr(y16, y32) < TOL_BF16 and not torch.equal(y16, y32)
+    assert relerr(gx16, gx32) < TOL_BF16
+    for a, b in zip(gp16, gp32):
+        for k in b:
+            assert relerr(a[k], b[k]) < TOL_BF16, k
