@@ -115,7 +115,7 @@ int kv_kan_fparam_count(const kv_kan_desc_t* d);
  * Outputs (any may be NULL to skip): wp_f32 [g][out][in*M] (K index i*M+m, effkan's
  * spline_scaler folded in -- models/effkan.py:166-172,180-183); wtiles_bf16 / wtiles_t_bf16:
  * the bf16 tcgen05 operand images of the same weights for the forward / input-gradient
- * tensor-core kernels (opaque pre-tiled layouts, sizes from kv_kan_tc_bytes; need wp_f32);
+ * tensor-core kernels (opaque pre-tiled layouts, sizes from kv_kan_tc_bytes; cut straight from the module tensors);
  * fparams [g][fparam_stride], bias [g][out] (zeros where the module has none). */
 int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32,
                 void* wtiles_bf16, void* wtiles_t_bf16, float* fparams, float* bias, void* stream);
@@ -195,6 +195,16 @@ int kv_attn_fwd(const float* qkv, const float* residual, float* out, float* lse,
  * overwritten.  dout: [B*N][H*d_h]. */
 int kv_attn_bwd(const float* qkv, const float* dout, const float* lse, float* dqkv,
                 int B, int N, int H, int d_head, void* stream);
+
+/* Tensor-core variants of the two calls above (bf16 operands, fp32 softmax and accumulation; same
+ * arguments, layouts and saved lse, tolerance 2e-2): flash-style online softmax over key chunks in
+ * the forward, two-pass recompute in the backward.  Return KV_ERR_UNSUPPORTED (nothing launched) when
+ * d_head > 64, d_head % 4 != 0 or a head does not fit in shared memory; the caller then uses the
+ * fp32 entry points. */
+int kv_attn_fwd_bf16(const float* qkv, const float* residual, float* out, float* lse,
+                     int B, int N, int H, int d_head, void* stream);
+int kv_attn_bwd_bf16(const float* qkv, const float* dout, const float* lse, float* dqkv,
+                     int B, int N, int H, int d_head, void* stream);
 
 /* nn.LayerNorm(d), eps 1e-5, affine (model.py:22,24,107).  mean/rstd [T] saved. */
 int kv_layernorm_fwd(const float* X, const float* gamma, const float* beta, float* Y,

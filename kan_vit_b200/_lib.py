@@ -20,6 +20,7 @@ KV_FLAG_NO_LAYERNORM = 2
 KV_FLAG_NO_BASE = 4
 KV_FLAG_BF16_TC = 8
 KV_FLAG_UNIFORM_GRID = 16
+KV_ERR_UNSUPPORTED = -5
 
 
 class KanDesc(C.Structure):
@@ -53,6 +54,8 @@ _SIGNATURES = {
     "kv_kan_unpack_grads": [_DP] + [_P] * 6,
     "kv_attn_fwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "kv_attn_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
+    "kv_attn_fwd_bf16": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
+    "kv_attn_bwd_bf16": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "kv_layernorm_fwd": [_P, _P, _P, _P, _P, _P, _I, _I, _I, C.c_float, _P],
     "kv_layernorm_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, C.c_float, _P],
     "kv_patchify": [_P, _P, _I, _I, _I, _I, _I, _P],

@@ -58,43 +58,6 @@ int check_desc(const kv_kan_desc_t* d) {
 // ------------------------------------------------------------------------------
 // pack: reference parameter layouts -> [g][out][in*M] (K index i*M+m)
 // ------------------------------------------------------------------------------
-__device__ __forceinline__ const float* slot(const uint64_t* tbl, int g, int s) {
-  return reinterpret_cast<const float*>(tbl[(size_t)g * KV_PTRS_PER_GROUP + s]);
-}
-__device__ __forceinline__ float* slot_out(const uint64_t* tbl, int g, int s) {
-  return reinterpret_cast<float*>(tbl[(size_t)g * KV_PTRS_PER_GROUP + s]);
-}
-
-// packed weight element (g, o, i, m) read from the module's own tensors
-__device__ __forceinline__ float load_packed_weight(const kv_kan_desc_t& d, const uint64_t* tbl, int g,
-                                                    int o, int i, int m) {
-  const int in = d.in_features, out = d.out_features, G = d.grid_size;
-  switch (d.family) {
-    case KV_LINEAR:
-      return slot(tbl, g, 0)[(size_t)o * in + i];
-    case KV_EFFKAN: {
-      const int nb = G + d.spline_order;
-      if (m == nb) return slot(tbl, g, 0)[(size_t)o * in + i];
-      float w = slot(tbl, g, 1)[((size_t)o * in + i) * nb + m];
-      const float* sc = slot(tbl, g, 2);
-      if (sc) w *= sc[(size_t)o * in + i];  // scaled_spline_weight, models/effkan.py:166-172
-      return w;
-    }
-    case KV_CHEBY:
-      return slot(tbl, g, 0)[((size_t)i * out + o) * (G + 1) + m];
-    case KV_FASTKAN:
-      if (m < G) return slot(tbl, g, 3)[(size_t)o * in * G + (size_t)i * G + m];
-      return slot(tbl, g, 4)[(size_t)o * in + i];
-    case KV_SINE:
-      return slot(tbl, g, 0)[((size_t)o * in + i) * G + m];
-    case KV_FOURIER: {
-      const int part = m / G, k = m % G;
-      return slot(tbl, g, 0)[(((size_t)part * out + o) * in + i) * G + k];
-    }
-  }
-  return 0.0f;
-}
-
 __global__ void pack_weights_kernel(const kv_kan_desc_t d, const uint64_t* __restrict__ tbl,
                                     float* __restrict__ wp_f32) {
   const int g = blockIdx.y;
@@ -376,11 +339,10 @@ int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32
     }
   }
   if (wtiles_bf16 != nullptr || wtiles_t_bf16 != nullptr) {
-    if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;  // the operand images are cut from the fp32 pack
     rc = tc_supported(*d);
     if (rc != KV_OK) return rc;
     if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;  // layout choice reads the grid probe
-    rc = tc_pack(tc_view(*d), wp_f32, fparams, wtiles_bf16, wtiles_t_bf16, st);
+    rc = tc_pack(tc_view(*d), *d, ptr_table, fparams, wtiles_bf16, wtiles_t_bf16, st);
     if (rc != KV_OK) return rc;
   }
   return KV_OK;

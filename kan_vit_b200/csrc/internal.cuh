@@ -22,8 +22,10 @@ int tc_supported(const kv_kan_desc_t& d);
 size_t tc_wtiles_bytes(const kv_kan_desc_t& d);    // forward operand image
 size_t tc_wtiles_t_bytes(const kv_kan_desc_t& d);  // input-gradient operand image (0 = kernel not available)
 bool tc_bwd_weight_available(const kv_kan_desc_t& d);
-int tc_pack(const kv_kan_desc_t& d, const float* wp_f32, const float* fparams, void* wtiles, void* wtiles_t,
-            cudaStream_t st);
+// operand images straight from the module tensors (ptr_table of kv_kan_pack): d = the tensor-core view of the
+// layer (api.cu tc_view), d0 = the caller's descriptor that indexes the pointer table
+int tc_pack(const kv_kan_desc_t& d, const kv_kan_desc_t& d0, const uint64_t* ptr_table, const float* fparams,
+            void* wtiles, void* wtiles_t, cudaStream_t st);
 int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const float* fparams,
            const float* bias, const float* mean, const float* rstd, const float* residual,
            const float* pos, float* Y, cudaStream_t st);
@@ -33,6 +35,44 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const void* dy_image, c
                  const float* fparams, float* dX, cudaStream_t st);
 int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, const float* fparams, float* dWp,
                   cudaStream_t st);
+
+// parameter pointer table of kv_kan_pack
+__device__ __forceinline__ const float* slot(const uint64_t* tbl, int g, int s) {
+  return reinterpret_cast<const float*>(tbl[(size_t)g * KV_PTRS_PER_GROUP + s]);
+}
+__device__ __forceinline__ float* slot_out(const uint64_t* tbl, int g, int s) {
+  return reinterpret_cast<float*>(tbl[(size_t)g * KV_PTRS_PER_GROUP + s]);
+}
+
+// packed weight element (g, o, i, m) read from the module's own tensors
+__device__ __forceinline__ float load_packed_weight(const kv_kan_desc_t& d, const uint64_t* tbl, int g,
+                                                    int o, int i, int m) {
+  const int in = d.in_features, out = d.out_features, G = d.grid_size;
+  switch (d.family) {
+    case KV_LINEAR:
+      return slot(tbl, g, 0)[(size_t)o * in + i];
+    case KV_EFFKAN: {
+      const int nb = G + d.spline_order;
+      if (m == nb) return slot(tbl, g, 0)[(size_t)o * in + i];
+      float w = slot(tbl, g, 1)[((size_t)o * in + i) * nb + m];
+      const float* sc = slot(tbl, g, 2);
+      if (sc) w *= sc[(size_t)o * in + i];  // scaled_spline_weight, models/effkan.py:166-172
+      return w;
+    }
+    case KV_CHEBY:
+      return slot(tbl, g, 0)[((size_t)i * out + o) * (G + 1) + m];
+    case KV_FASTKAN:
+      if (m < G) return slot(tbl, g, 3)[(size_t)o * in * G + (size_t)i * G + m];
+      return slot(tbl, g, 4)[(size_t)o * in + i];
+    case KV_SINE:
+      return slot(tbl, g, 0)[((size_t)o * in + i) * G + m];
+    case KV_FOURIER: {
+      const int part = m / G, k = m % G;
+      return slot(tbl, g, 0)[(((size_t)part * out + o) * in + i) * G + k];
+    }
+  }
+  return 0.0f;
+}
 
 // validation shared by every kan entry point
 int check_desc(const kv_kan_desc_t* d);

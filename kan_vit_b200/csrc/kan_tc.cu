@@ -93,22 +93,70 @@ __device__ __forceinline__ void unit_to_im(int layout, int M, int c, int q, int 
 }
 
 // ----------------------------------------------------------------------------------------
-// weight pre-tiling: wp_f32 [g][out][in*M] (K index i*M+m)  ->  wtiles bf16
+// weight pre-tiling: module tensors (pointer table of kv_kan_pack)  ->  wtiles bf16
 //   [g][n_tile][CTA rank][unit][sub-MMA j][k-half h][row group][8 rows][8 elements]
 // = for every unit and each CTA of the pair the no-swizzle K-major operand image of its half of the
-//   rows of each N<=256 sub-MMA (core matrix = 8 rows x 16 B).
+//   rows of each N<=256 sub-MMA (core matrix = 8 rows x 16 B).  One thread = one core-matrix row (16 B).
+// d is the tensor-core view of the layer, d0 the caller's descriptor: view group g / output o is
+// group g * xs + o / d0.out, output o % d0.out of the pointer table (xs = merged q/k/v maps, api.cu tc_view).
 // ----------------------------------------------------------------------------------------
-__global__ void tc_pack_kernel(const kv_kan_desc_t d, const float* __restrict__ wp,
+__device__ __forceinline__ uint32_t pack_bf16_pair(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// the 8 K elements e = 0..7 of (chunk c, unit q, k-half h) for output o0 of group g0 of the pointer table
+__device__ __forceinline__ void load_w8(const kv_kan_desc_t& d0, const uint64_t* __restrict__ tbl, int g0, int o0,
+                                        int layout, int c, int q, int h, float (&v)[8]) {
+  const int in = d0.in_features;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) v[e] = 0.0f;
+  if (o0 >= d0.out_features) return;
+  if (layout == LAYOUT_EFFKAN8) {
+    if (q < 8) {  // the 8 B-spline coefficients of one feature: 32 contiguous bytes of spline_weight
+      const int i = c * KU + 2 * q + h;
+      if (i >= in) return;
+      const float* w = slot(tbl, g0, 1) + ((size_t)o0 * in + i) * 8;
+      const float* sc = slot(tbl, g0, 2);
+      const float sv = sc ? sc[(size_t)o0 * in + i] : 1.0f;  // scaled_spline_weight, models/effkan.py:166-172
+      if ((reinterpret_cast<uintptr_t>(w) & 15) == 0) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(w)), b = __ldg(reinterpret_cast<const float4*>(w) + 1);
+        v[0] = a.x * sv; v[1] = a.y * sv; v[2] = a.z * sv; v[3] = a.w * sv;
+        v[4] = b.x * sv; v[5] = b.y * sv; v[6] = b.z * sv; v[7] = b.w * sv;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = w[e] * sv;
+      }
+    } else {      // SiLU branch: 8 consecutive features of base_weight
+      const int i0 = c * KU + h * 8;
+      const float* w = slot(tbl, g0, 0) + (size_t)o0 * in + i0;
+      if (i0 + 8 <= in && (reinterpret_cast<uintptr_t>(w) & 15) == 0) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(w)), b = __ldg(reinterpret_cast<const float4*>(w) + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (i0 + e < in) v[e] = w[e];
+      }
+    }
+    return;
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    int i, m;
+    unit_to_im(layout, d0.M, c, q, h, e, i, m);
+    if (i < in) v[e] = load_packed_weight(d0, tbl, g0, o0, i, m);
+  }
+}
+
+__global__ void tc_pack_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, const uint64_t* __restrict__ tbl,
                                const float* __restrict__ fparams, __nv_bfloat16* __restrict__ wt, Geom gm) {
-  const size_t per_tile = gm.tile_elems();
-  const size_t total = (size_t)d.n_groups * gm.n_tiles * per_tile;
-  const int in = d.in_features, out = d.out_features, M = d.M;
-  const int K = in * M;
-  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+  const size_t total8 = (size_t)d.n_groups * gm.n_tiles * gm.tile_elems() / 8;
+  const int M = d.M, xs = d.n_groups == d0.n_groups ? 1 : d0.x_share;
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total8;
        idx += (size_t)gridDim.x * blockDim.x) {
-    // [g][n_tile][CTA rank][unit][sub-MMA j][k-half h][row group][8 rows][8 elements]
+    // [g][n_tile][CTA rank][unit][sub-MMA j][k-half h][row group][8 rows]  (x 8 elements)
     size_t r = idx;
-    const int e = r % 8; r /= 8;
     const int r8 = r % 8; r /= 8;
     int pr = r % (gm.BN / 8); r /= (gm.BN / 8);   // core-matrix position inside this rank's half unit
     const int u = r % gm.n_units; r /= gm.n_units;
@@ -121,11 +169,15 @@ __global__ void tc_pack_kernel(const kv_kan_desc_t d, const float* __restrict__ 
     const int h = pr / (nj / 16), rgl = pr % (nj / 16);
     const int o = nt * gm.BN + (j ? n1 : 0) + rank * (nj / 2) + rgl * 8 + r8;
     const int c = u / M, q = u - c * M;
-    int i, m;
-    unit_to_im(group_layout(d, gm, fparams, g), M, c, q, h, e, i, m);
-    float v = 0.0f;
-    if (o < out && i < in) v = wp[((size_t)g * out + o) * K + (size_t)i * M + m];
-    wt[idx] = __float2bfloat16_rn(v);
+    float v[8];
+    if (o < d.out_features) {
+      load_w8(d0, tbl, g * xs + o / d0.out_features, o % d0.out_features, group_layout(d, gm, fparams, g), c, q, h, v);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = 0.0f;
+    }
+    *reinterpret_cast<uint4*>(wt + idx * 8) = make_uint4(pack_bf16_pair(v[0], v[1]), pack_bf16_pair(v[2], v[3]),
+                                                         pack_bf16_pair(v[4], v[5]), pack_bf16_pair(v[6], v[7]));
   }
 }
 
@@ -705,19 +757,18 @@ __global__ void dy_image_kernel(const kv_kan_desc_t d, const float* __restrict__
   }
 }
 
-// transposed weight image for the input gradient:
+// transposed weight image for the input gradient (default effkan on a uniform grid only):
 //   [g][tile][stage][CTA rank][sub j][o8 (8)][n8 (SW/16)][8 columns][8 outputs]
-__global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const float* __restrict__ wp,
+// One thread = one core matrix: 8 columns (the 8 B-spline coefficients of one feature, or 8 features of the
+// SiLU branch) x 8 outputs, read as 8 x 32 contiguous bytes and written as 128 contiguous bytes.
+__global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, const uint64_t* __restrict__ tbl,
                                  __nv_bfloat16* __restrict__ wtt, BwdGeom b) {
-  const int M = d.M, in = d.in_features, out = d.out_features, K = in * M;
   const int half = b.SW / 2;
-  const size_t per_stage_rank = (size_t)b.n_sub * half * 64;
-  const size_t total = (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * per_stage_rank;
-  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+  const int xs = d.n_groups == d0.n_groups ? 1 : d0.x_share;
+  const size_t total64 = (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * b.n_sub * half;  // core matrices
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total64;
        idx += (size_t)gridDim.x * blockDim.x) {
     size_t r = idx;
-    const int oe = r % 8; r /= 8;
-    const int r8 = r % 8; r /= 8;
     const int n8 = r % (half / 8); r /= (half / 8);
     const int o8 = r % 8; r /= 8;
     const int j = r % b.n_sub; r /= b.n_sub;
@@ -726,13 +777,27 @@ __global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const float* __restrict_
     const int tile = r % b.n_tiles; r /= b.n_tiles;
     const int g = (int)r;
     const int c = tile * b.n_sub + j;
-    const int cc = rank * half + n8 * 8 + r8;  // column inside the chunk
-    int i, m;
-    unit_to_im(LAYOUT_EFFKAN8, M, c, cc / 16, (cc / 8) & 1, cc & 7, i, m);
-    const int o = st * 64 + o8 * 8 + oe;
-    float v = 0.0f;
-    if (o < out && i < in && c < b.n_chunks) v = wp[((size_t)g * out + o) * K + (size_t)i * M + m];
-    wtt[idx] = __float2bfloat16_rn(v);
+    const int cc = rank * half + n8 * 8;  // first column of this core matrix inside the chunk
+    const int q = cc / 16, h = (cc / 8) & 1;
+    uint32_t w[8][4];  // [column r8][4 output pairs]
+    float v[8][8];     // [output oe][column r8]
+#pragma unroll
+    for (int oe = 0; oe < 8; ++oe) {
+      const int o = st * 64 + o8 * 8 + oe;
+      if (o < d.out_features && c < b.n_chunks) {
+        load_w8(d0, tbl, g * xs + o / d0.out_features, o % d0.out_features, LAYOUT_EFFKAN8, c, q, h, v[oe]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[oe][e] = 0.0f;
+      }
+    }
+#pragma unroll
+    for (int r8 = 0; r8 < 8; ++r8)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) w[r8][k] = pack_bf16_pair(v[2 * k][r8], v[2 * k + 1][r8]);
+    uint4* dst = reinterpret_cast<uint4*>(wtt + idx * 64);
+#pragma unroll
+    for (int r8 = 0; r8 < 8; ++r8) dst[r8] = make_uint4(w[r8][0], w[r8][1], w[r8][2], w[r8][3]);
   }
 }
 
@@ -1229,20 +1294,20 @@ static int grid_for(size_t total, int threads) {
   return (int)(blocks > 148 * 32 ? 148 * 32 : (blocks ? blocks : 1));
 }
 
-int tc_pack(const kv_kan_desc_t& d, const float* wp_f32, const float* fparams, void* wtiles, void* wtiles_t,
-            cudaStream_t st) {
+int tc_pack(const kv_kan_desc_t& d, const kv_kan_desc_t& d0, const uint64_t* ptr_table, const float* fparams,
+            void* wtiles, void* wtiles_t, cudaStream_t st) {
   const tc::Geom gm = tc::make_geom(d);
   if (wtiles != nullptr) {
-    const size_t total = (size_t)d.n_groups * gm.n_tiles * gm.tile_elems();
-    tc::tc_pack_kernel<<<grid_for(total, 256), 256, 0, st>>>(d, wp_f32, fparams,
+    const size_t total = (size_t)d.n_groups * gm.n_tiles * gm.tile_elems() / 8;
+    tc::tc_pack_kernel<<<grid_for(total, 256), 256, 0, st>>>(d, d0, ptr_table, fparams,
                                                              reinterpret_cast<__nv_bfloat16*>(wtiles), gm);
     KV_CHECK_LAUNCH("tc_pack_kernel");
   }
   if (wtiles_t != nullptr) {
     if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
     const tc::BwdGeom b = tc::make_bwd_geom(d);
-    const size_t total = tc_wtiles_t_bytes(d) / 2;
-    tc::tc_pack_t_kernel<<<grid_for(total, 256), 256, 0, st>>>(d, wp_f32, reinterpret_cast<__nv_bfloat16*>(wtiles_t), b);
+    const size_t total = tc_wtiles_t_bytes(d) / 128;
+    tc::tc_pack_t_kernel<<<grid_for(total, 128), 128, 0, st>>>(d, d0, ptr_table, reinterpret_cast<__nv_bfloat16*>(wtiles_t), b);
     KV_CHECK_LAUNCH("tc_pack_t_kernel");
   }
   return KV_OK;

@@ -159,7 +159,10 @@ class KanSpec:
         lib = L.load()
         g, o, K = self.n_groups, self.out_features, self.in_features * self.M
         tbl = self.ptr_table(flat, device)
-        wp = torch.empty((g, o, K), dtype=torch.float32, device=device)
+        # the fp32 pack feeds the exact kernels; a layer whose forward and both gradients run on the
+        # tensor cores only needs the bf16 operand images (cut straight from the module tensors)
+        all_tc = tc_sizes is not None and tc_sizes[1] > 0 and tc_sizes[2] > 0
+        wp = None if all_tc else torch.empty((g, o, K), dtype=torch.float32, device=device)
         fp = torch.empty((g, max(self.fparam_stride, 1)), dtype=torch.float32, device=device)
         has_bias = self.family in _FAMILY_BIAS_SLOT and any(
             flat[q * L.KV_PTRS_PER_GROUP + _FAMILY_BIAS_SLOT[self.family]] is not None for q in range(g))
@@ -170,7 +173,7 @@ class KanSpec:
             wt = torch.empty((tc_sizes[0],), dtype=torch.uint8, device=device)
             if tc_sizes[1]:
                 wtt = torch.empty((tc_sizes[1],), dtype=torch.uint8, device=device)
-        _call("kv_kan_pack", lib.kv_kan_pack, C.byref(d), tbl.data_ptr(), wp.data_ptr(), L.ptr(wt), L.ptr(wtt),
+        _call("kv_kan_pack", lib.kv_kan_pack, C.byref(d), tbl.data_ptr(), L.ptr(wp), L.ptr(wt), L.ptr(wtt),
                                 fp.data_ptr() if self.fparam_stride else None, L.ptr(bias), _stream())
         pk = {"wp": wp, "fp": fp if self.fparam_stride else None, "bias": bias, "tbl": tbl, "wt": wt, "wtt": wtt}
         return pk
@@ -232,7 +235,7 @@ class _KanFn(torch.autograd.Function):
             assert residual.shape == y.shape and residual.is_contiguous()
         if pos is not None:
             assert pos.is_contiguous() and pos.shape[-1] == n_out
-        _call("kv_kan_fwd", lib.kv_kan_fwd, C.byref(d), x.data_ptr(), pk["wp"].data_ptr(), L.ptr(pk["wt"]), L.ptr(pk["fp"]),
+        _call("kv_kan_fwd", lib.kv_kan_fwd, C.byref(d), x.data_ptr(), L.ptr(pk["wp"]), L.ptr(pk["wt"]), L.ptr(pk["fp"]),
                                L.ptr(pk["bias"]), L.ptr(mean), L.ptr(rstd), L.ptr(residual), L.ptr(pos),
                                y.data_ptr(), _stream(), work=_kan_flops(spec, T))
         if v_class is not None:
@@ -272,7 +275,7 @@ class _KanFn(torch.autograd.Function):
             if mean is not None:
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
-                                         pk["wp"].data_ptr(), L.ptr(pk["wtt"]), L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean),
+                                         L.ptr(pk["wp"]), L.ptr(pk["wtt"]), L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean),
                                          L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
@@ -285,7 +288,7 @@ class _KanFn(torch.autograd.Function):
             if mean is not None:
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
-                                         pk["wp"].data_ptr(), L.ptr(pk["wtt"]), L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean),
+                                         L.ptr(pk["wp"]), L.ptr(pk["wtt"]), L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean),
                                          L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
@@ -338,8 +341,15 @@ class _AttnFn(torch.autograd.Function):
         assert qkv.is_contiguous() and qkv.shape == (B * N, 3 * H * dh)
         out = torch.empty((B * N, H * dh), dtype=torch.float32, device=qkv.device)
         lse = torch.empty((B, H, N), dtype=torch.float32, device=qkv.device)
-        _call("kv_attn_fwd", lib.kv_attn_fwd, qkv.data_ptr(), L.ptr(residual), out.data_ptr(), lse.data_ptr(),
-                                B, N, H, dh, _stream(), work=4.0 * B * H * N * N * dh)
+        # bf16 mode: tensor-core kernel where it serves the head shape, else the exact kernel
+        tc = _PRECISION == "bf16" and dh <= 64 and dh % 4 == 0
+        if tc:
+            # shape probe (B = 0 launches nothing); the backward needs the larger shared-memory tile
+            tc = lib.kv_attn_bwd_bf16(None, None, None, None, 0, N, H, dh, None) == 0
+        name, fn = ("kv_attn_fwd_bf16", lib.kv_attn_fwd_bf16) if tc else ("kv_attn_fwd", lib.kv_attn_fwd)
+        _call(name, fn, qkv.data_ptr(), L.ptr(residual), out.data_ptr(), lse.data_ptr(),
+              B, N, H, dh, _stream(), work=4.0 * B * H * N * N * dh)
+        ctx.tc = tc
         ctx.save_for_backward(qkv, lse)
         ctx.dims = (B, N, H, dh)
         ctx.has_res = residual is not None
@@ -352,8 +362,9 @@ class _AttnFn(torch.autograd.Function):
         B, N, H, dh = ctx.dims
         dout = dout.contiguous()
         dqkv = torch.empty_like(qkv)
-        _call("kv_attn_bwd", lib.kv_attn_bwd, qkv.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
-                                B, N, H, dh, _stream(), work=8.0 * B * H * N * N * dh)
+        name, fn = ("kv_attn_bwd_bf16", lib.kv_attn_bwd_bf16) if ctx.tc else ("kv_attn_bwd", lib.kv_attn_bwd)
+        _call(name, fn, qkv.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
+              B, N, H, dh, _stream(), work=8.0 * B * H * N * N * dh)
         return dqkv, (dout if ctx.has_res else None), None, None, None, None
 
 

@@ -50,7 +50,9 @@ def test_bf16_matches_reference_golden(case):
     for k, ref in g.grads().items():
         if ref.abs().max() < 1e-6:
             continue
-        tol = max(gtol, 5e-2) if k.endswith(".freq") else gtol  # cancelling sum, see test_gpu_parity
+        # .freq: a cancelling sum over every row and feature (see test_gpu_parity); inside the composite
+        # models its value is ~1e-5 against O(1) terms, so the bf16 noise of the whole model lands on it
+        tol = (5e-2 if layer else 2.5e-1) if k.endswith(".freq") else gtol
         assert err(params[k].grad, ref) < tol, k
 
 
@@ -160,3 +162,32 @@ def test_bf16_grouped_qkv_effkan_vs_own_fp32(T, H, dh):
     for a, b in zip(gp16, gp32):
         for k in b:
             assert relerr(a[k], b[k]) < TOL_BF16, k
+
+
+@pytest.mark.parametrize("B,N,H,dh", [(3, 197, 12, 64), (5, 50, 2, 32), (4, 17, 8, 24), (2, 33, 3, 48), (1, 200, 2, 64)])
+def test_bf16_attention_vs_own_fp32(B, N, H, dh):
+    """Tensor-core attention (kv_attn_fwd_bf16 / kv_attn_bwd_bf16) against the exact fp32 kernels, with the
+    residual epilogue; torch softmax attention in float64 as a third opinion on the forward."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    torch.manual_seed(3)
+    qkv0 = torch.randn(B * N, 3 * H * dh, device=_dev())
+    res = torch.randn(B * N, H * dh, device=_dev())
+    dout = torch.randn(B * N, H * dh, device=_dev())
+
+    def run(mode):
+        K.set_precision(mode)
+        qkv = qkv0.clone().requires_grad_(True)
+        out = ops.attention(qkv, B, N, H, dh, residual=res)
+        out.backward(dout)
+        return out.detach(), qkv.grad
+
+    o16, g16 = run("bf16")
+    o32, g32 = run("fp32")
+    K.set_precision("bf16")
+    assert relerr(o16, o32) < TOL_BF16 and not torch.equal(o16, o32)
+    assert relerr(g16, g32) < TOL_BF16
+    q, k, v = qkv0.double().view(B, N, H, 3, dh).permute(3, 0, 2, 1, 4)
+    ref = torch.softmax(q @ k.transpose(-1, -2) / dh ** 0.5, -1) @ v
+    ref = ref.permute(0, 2, 1, 3).reshape(B * N, H * dh) + res.double()
+    assert relerr(o16, ref.float()) < TOL_BF16
