@@ -195,6 +195,12 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 __device__ __forceinline__ float fast_silu(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+// (a == b) ? x : y as setp + selp (the ternary chains of the gradient epilogue otherwise compile to branches)
+__device__ __forceinline__ float sel_eq(int a, int b, float x, float y) {
+  float r;
+  asm("{ .reg .pred p; setp.eq.s32 p, %1, %2; selp.f32 %0, %3, %4, p; }" : "=f"(r) : "r"(a), "r"(b), "f"(x), "f"(y));
+  return r;
+}
 __device__ __forceinline__ uint64_t shl64(uint64_t v, int n) {  // PTX shifts clamp: n >= 64 (or "negative") -> 0
   uint64_t r;
   asm("shl.b64 %0, %1, %2;" : "=l"(r) : "l"(v), "r"(n));
@@ -883,14 +889,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
       int s = 0;
       uint32_t ph = 0;
       for (int st = 0; st < b.n_stages; ++st) {
-        ptx::mbar_wait(full(s), ph);
+        if (!(d.reserved & 256)) ptx::mbar_wait(full(s), ph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           const uint64_t da = da0 + (uint64_t)((s * BI_A_STAGE) >> 4);
           const uint64_t db = db0 + (uint64_t)((s * BI_B_STAGE) >> 4);
 #pragma unroll
           for (int ks = 0; ks < BI_KS; ++ks) {
-            for (int j = 0; j < n_sub; ++j)
+            for (int j = 0; j < ((d.reserved & 1024) ? 1 : n_sub); ++j)
               ptx::mma2_bf16_ss(tmem_base + j * SW, da + (uint64_t)(ks * 16), db + (uint64_t)(j * b_sub_step + ks * b_k_step),
                                 idesc, (st | ks) > 0);
           }
@@ -937,7 +943,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
       const int c = tile * n_sub + j;
-      if (j >= n_sub || c >= b.n_chunks) continue;   // warp-uniform
+      if (j >= n_sub || c >= b.n_chunks || (d.reserved & 512)) continue;   // warp-uniform
       uint32_t sa[32], sb2[32], sbase[8];
       ptx::tmem_ld32(trow + j * SW + half * 64, sa);        // units 4*half, 4*half+1
       ptx::tmem_ld32(trow + j * SW + half * 64 + 32, sb2);  // units 4*half+2, 4*half+3
@@ -961,8 +967,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
         float acc = 0.0f;
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const int dd = e - j3;
-          const float coef = dd == 0 ? w0 : (dd == 1 ? w1 : (dd == 2 ? w2 : (dd == 3 ? w3 : 0.0f)));
+          // coefficient of spline e: piece e - j3 of the derivative (branch-free selects)
+          const float coef = sel_eq(j3, e, w0, sel_eq(j3, e - 1, w1, sel_eq(j3, e - 2, w2, sel_eq(j3, e - 3, w3, 0.0f))));
           const uint32_t sv = (f < 4) ? sa[f * 8 + e] : sb2[(f - 4) * 8 + e];
           acc = fmaf(coef, __uint_as_float(sv), acc);
         }
