@@ -10,7 +10,7 @@ zero_grad -> forward -> CrossEntropy -> backward -> (gradient all-reduce) -> Ada
 (the step shape of the reference's train.py:31-40).  Workload at every N: the configuration
 BASELINE.json's metric ("train images/sec at 1/2/4/8 B200") is quoted on, configs[3]: the
 ViT-B/16-shaped KAN-ViT (efficient-kan MLP, 224x224, 197 tokens, dim 768, depth 12), bf16
-tensor-core arithmetic, data-parallel, 64 images per GPU (weak scaling).  It fits one GPU, so it
+tensor-core arithmetic, data-parallel, 256 images per GPU (weak scaling).  It fits one GPU, so it
 is also the N=1 workload.  The other configs (cfg1 .. cfg3, parity-test shapes) are selectable
 with --config for the record; cfg1/cfg2 default to the exact fp32 kernels.
 """
@@ -33,7 +33,7 @@ CONFIGS = {
     "cfg2": ((1, 28, 28), 7, 4, 64, 2, 10, "cheby", False, 1024, 1024),
     "cfg3_fast": ((3, 32, 32), 4, 6, 192, 8, 10, "fast", False, 1024, 32),
     "cfg3_sine": ((3, 32, 32), 4, 6, 192, 8, 10, "sine", False, 1024, 32),
-    "cfg4": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", True, 64, 1),
+    "cfg4": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", True, 256, 1),
     "cfg4_faithful": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", False, 64, 2),
 }
 DEFAULT_PRECISION = {"cfg1": "fp32", "cfg2": "fp32", "cfg3_fast": "bf16", "cfg3_sine": "bf16", "cfg4": "bf16",
@@ -197,11 +197,21 @@ def profile_kernels(step_fn, n_steps):
     torch.cuda.synchronize()
     prof, ops.PROFILE = ops.PROFILE, None
     out = {}
+    by_shape = {}
     for name, evs in prof.items():
-        ms = sum(s.elapsed_time(e) for s, e, _ in evs)
-        work = sum(w for _, _, w in evs)
+        ms = sum(s.elapsed_time(e) for s, e, _, _ in evs)
+        work = sum(w for _, _, w, _ in evs)
         out[name] = {"calls": len(evs) // n_steps, "ms_per_step": ms / n_steps, "work_per_step": work / n_steps,
                      "ms_per_call": ms / len(evs), "work_per_call": work / len(evs)}
+        for s, e, w, tag in evs:
+            if tag is not None:
+                a = by_shape.setdefault(f"{name} {tag}", [0.0, 0.0, 0])
+                a[0] += s.elapsed_time(e)
+                a[1] += w
+                a[2] += 1
+    out["_by_shape"] = {k: {"calls": v[2] // n_steps, "ms_per_call": v[0] / v[2],
+                            "tflops": v[1] / v[2] / (v[0] / v[2] * 1e-3) / 1e12}
+                        for k, v in by_shape.items()}
     return out
 
 
@@ -262,11 +272,23 @@ def run_gpu_arm(args):
     def resident_step(i):
         step(dev_img[i % n_host], dev_lab[i % n_host])
 
+    loss_host = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_evt = [torch.cuda.Event() for _ in range(2)]
+    e2e_losses = []
+
     def e2e_step(i):
-        # the call a user makes: host batch in, loss value out
+        # the call a user makes: host batch in (pinned -> device), loss value out.  The loss of every step
+        # is copied to pinned host memory and read on the host one step later, so the device->host read
+        # does not drain the launch queue (the usual way a training loop logs its loss).
         x = host_img[i % n_host].to(dev, non_blocking=True)
         y = host_lab[i % n_host].to(dev, non_blocking=True)
-        return step(x, y).item()
+        loss = step(x, y)
+        k = i % 2
+        loss_host[k].copy_(loss, non_blocking=True)
+        loss_evt[k].record()
+        if i > 0:
+            loss_evt[1 - k].synchronize()
+            e2e_losses.append(float(loss_host[1 - k]))
 
     # warm-up (also the first packs / allocator growth)
     for i in range(max(args.warmup, 3)):
@@ -284,10 +306,12 @@ def run_gpu_arm(args):
     ms_total = timed(resident_step, args.steps)
     launches = lib.kv_launch_count() - l0
     ms_e2e = timed(e2e_step, args.steps)
+    e2e_losses.append(float(loss_host[(args.steps - 1) % 2]))  # the last step's loss (already on the host)
     clk = clocks.stop()
 
     # per-kernel shares for the roofline (separate pass: the events perturb the step slightly)
     prof = profile_kernels(lambda: resident_step(0), 3)
+    by_shape = prof.pop("_by_shape")
     peaks = load_peaks()
     top = max(prof, key=lambda k: prof[k]["ms_per_step"])
     t = prof[top]
@@ -303,7 +327,11 @@ def run_gpu_arm(args):
                 "kernel_calls_per_step": t["calls"], "kernel_share_of_step": t["ms_per_step"] / kernel_ms,
                 "peak_source": peaks["source"] + " (sustained bf16 dense / copy bandwidth)",
                 "shares": {k: round(v["ms_per_step"] / kernel_ms, 4) for k, v in
-                           sorted(prof.items(), key=lambda kv: -kv[1]["ms_per_step"])}}
+                           sorted(prof.items(), key=lambda kv: -kv[1]["ms_per_step"])},
+                # the GEMM-shaped launches by layer shape (T rows, groups, in->out, M basis functions)
+                "by_shape": {k: {"calls": v["calls"], "ms_per_call": round(v["ms_per_call"], 4),
+                                 "tflops": round(v["tflops"], 1)}
+                             for k, v in sorted(by_shape.items(), key=lambda kv: -kv[1]["ms_per_call"] * kv[1]["calls"])}}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:

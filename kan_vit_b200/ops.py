@@ -72,7 +72,7 @@ class precision:
         set_precision(self.prev)
 
 
-def _call(name, fn, *args, work=0.0):
+def _call(name, fn, *args, work=0.0, tag=None):
     if PROFILE is None or (PROFILE_ONLY is not None and name not in PROFILE_ONLY):
         L.check(fn(*args), name)
         return
@@ -81,7 +81,11 @@ def _call(name, fn, *args, work=0.0):
     s.record()
     L.check(fn(*args), name)
     e.record()
-    PROFILE.setdefault(name, []).append((s, e, work))
+    PROFILE.setdefault(name, []).append((s, e, work, tag))
+
+
+def _kan_tag(spec, T):
+    return f"T{T} g{spec.n_groups} {spec.in_features}->{spec.out_features} M{spec.M}"
 
 
 def _kan_flops(spec, T):
@@ -237,7 +241,7 @@ class _KanFn(torch.autograd.Function):
             assert pos.is_contiguous() and pos.shape[-1] == n_out
         _call("kv_kan_fwd", lib.kv_kan_fwd, C.byref(d), x.data_ptr(), L.ptr(pk["wp"]), L.ptr(pk["wt"]), L.ptr(pk["fp"]),
                                L.ptr(pk["bias"]), L.ptr(mean), L.ptr(rstd), L.ptr(residual), L.ptr(pos),
-                               y.data_ptr(), _stream(), work=_kan_flops(spec, T))
+                               y.data_ptr(), _stream(), work=_kan_flops(spec, T), tag=_kan_tag(spec, T))
         if v_class is not None:
             assert rows_in > 0 and row_shift == 1 and spec.n_groups == 1
             _call("kv_cls_rows_fwd", lib.kv_cls_rows_fwd, v_class.data_ptr(), L.ptr(pos), y.data_ptr(), T // rows_in,
@@ -276,7 +280,7 @@ class _KanFn(torch.autograd.Function):
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
                                          L.ptr(pk["wp"]), L.ptr(pk["wtt"]), L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean),
-                                         L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
+                                         L.ptr(rstd), dx.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T), tag=_kan_tag(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
                                               mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(),
@@ -289,7 +293,7 @@ class _KanFn(torch.autograd.Function):
                 dxn = torch.empty((T, g * spec.in_features), dtype=torch.float32, device=dev)
             _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
                                          L.ptr(pk["wp"]), L.ptr(pk["wtt"]), L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean),
-                                         L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T))
+                                         L.ptr(rstd), dx_tmp.data_ptr(), L.ptr(dxn), L.ptr(dfp), st, work=_kan_flops(spec, T), tag=_kan_tag(spec, T))
             if dxn is not None:
                 _call("kv_fastkan_ln_bwd", lib.kv_fastkan_ln_bwd, C.byref(d), x.data_ptr(), dxn.data_ptr(), pk["fp"].data_ptr(),
                                               mean.data_ptr(), rstd.data_ptr(), dx_tmp.data_ptr(),
@@ -299,7 +303,7 @@ class _KanFn(torch.autograd.Function):
             dbias = torch.zeros((g, o), dtype=torch.float32, device=dev) if pk["bias"] is not None else None
             _call("kv_kan_bwd_weight", lib.kv_kan_bwd_weight, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
                                           L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean), L.ptr(rstd), dwp.data_ptr(),
-                                          L.ptr(dbias), st, work=_kan_flops(spec, T))
+                                          L.ptr(dbias), st, work=_kan_flops(spec, T), tag=_kan_tag(spec, T))
             off_t, meta, total = spec.grad_layout(flat, dev)
             gflat = torch.empty((total,), dtype=torch.float32, device=dev)
             gtbl = torch.where(off_t >= 0, off_t + gflat.data_ptr(), torch.zeros_like(off_t))

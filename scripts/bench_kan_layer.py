@@ -64,7 +64,7 @@ def main():
     prof, ops.PROFILE = ops.PROFILE, None
     out = {"family": a.family, "T": a.T, "in": a.inf, "out": a.outf, "M": spec.M, "precision": a.precision}
     for name, evs in prof.items():
-        ms = sorted(s.elapsed_time(e) for s, e, _ in evs)
+        ms = sorted(s.elapsed_time(e) for s, e, *_ in evs)
         med = ms[len(ms) // 2]
         w = evs[0][2]
         out[name] = {"ms": round(med, 4), "tflops": round(w / (med * 1e-3) / 1e12, 2) if w and name.startswith("kv_kan_") and name != "kv_kan_dy_image" and name != "kv_kan_pack" else None}
