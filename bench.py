@@ -215,6 +215,14 @@ def profile_kernels(step_fn, n_steps):
     return out
 
 
+def _progress(msg):
+    if os.environ.get("KV_VERBOSE") == "1":
+        print(f"[bench +{time.perf_counter() - _T0:7.1f}s] {msg}", file=sys.stderr, flush=True)
+
+
+_T0 = time.perf_counter()
+
+
 def run_gpu_arm(args):
     import torch.distributed as dist
     import kan_vit_b200 as K
@@ -237,8 +245,19 @@ def run_gpu_arm(args):
     if args.batch:
         batch = args.batch
     K.set_precision(args.precision)
+    if os.environ.get("KV_FAST_INIT") == "1":
+        # profiler runs only: skip the least-squares fit of KANLinear.reset_parameters (minutes of host
+        # LAPACK work under ncu); same shapes, same launches, weights of the same scale
+        def _fast_reset(self):
+            with torch.no_grad():
+                torch.nn.init.kaiming_uniform_(self.base_weight, a=5 ** 0.5 * self.scale_base)
+                self.spline_weight.normal_(0.0, 0.02)
+                if self.enable_standalone_scale_spline:
+                    torch.nn.init.kaiming_uniform_(self.spline_scaler, a=5 ** 0.5 * self.scale_spline)
+        K.KANLinear.reset_parameters = _fast_reset
     torch.manual_seed(0)  # identical replicas on every rank
     model = K.VisionTransformer(chw, npatch, nb, d, h, out_d, kind, kan_mlp=kan_mlp).to(dev)
+    _progress("model on device")
     if world > 1:
         for p in model.parameters():
             dist.broadcast(p.data, 0)
@@ -269,8 +288,21 @@ def run_gpu_arm(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    # KV_NCU_RANGE=1: bracket the first timed step with cudaProfilerStart/Stop so that
+    # `ncu --profile-from-start off` captures exactly one step of this command (profiles/README.md)
+    ncu_range = os.environ.get("KV_NCU_RANGE") == "1"
+    state = {"timed": False, "done": False}
+
     def resident_step(i):
+        mark = ncu_range and state["timed"] and not state["done"]
+        if mark:
+            torch.cuda.synchronize()
+            torch.cuda.profiler.start()
         step(dev_img[i % n_host], dev_lab[i % n_host])
+        if mark:
+            torch.cuda.synchronize()
+            torch.cuda.profiler.stop()
+            state["done"] = True
 
     loss_host = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
     loss_evt = [torch.cuda.Event() for _ in range(2)]
@@ -291,8 +323,12 @@ def run_gpu_arm(args):
             e2e_losses.append(float(loss_host[1 - k]))
 
     # warm-up (also the first packs / allocator growth)
+    _progress("host batches pinned and copied")
     for i in range(max(args.warmup, 3)):
         resident_step(i)
+        if os.environ.get("KV_VERBOSE") == "1":
+            torch.cuda.synchronize()
+            _progress(f"warm-up step {i}")
     torch.cuda.synchronize()
     torch.cuda.reset_peak_memory_stats(dev)
     base_mem = torch.cuda.memory_allocated(dev)
@@ -303,9 +339,12 @@ def run_gpu_arm(args):
     clocks = ClockSampler(local)
     clocks.start()
     l0 = lib.kv_launch_count()
+    state["timed"] = True
     ms_total = timed(resident_step, args.steps)
     launches = lib.kv_launch_count() - l0
+    _progress("resident steps timed")
     ms_e2e = timed(e2e_step, args.steps)
+    _progress("e2e steps timed")
     e2e_losses.append(float(loss_host[(args.steps - 1) % 2]))  # the last step's loss (already on the host)
     clk = clocks.stop()
 
