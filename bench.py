@@ -261,7 +261,7 @@ def run_gpu_arm(args):
     if world > 1:
         for p in model.parameters():
             dist.broadcast(p.data, 0)
-    step = TrainStep(model, lr=1e-3)
+    step = TrainStep(model, lr=1e-3, cuda_graph=args.cuda_graph)
     g = torch.Generator().manual_seed(1000 + rank)  # every rank its own shard of synthetic data
     n_host = 4  # rotating pinned host batches for the end-to-end leg
     host_img = [torch.randn((batch,) + tuple(chw), generator=g).pin_memory() for _ in range(n_host)]
@@ -349,7 +349,12 @@ def run_gpu_arm(args):
     clk = clocks.stop()
 
     # per-kernel shares for the roofline (separate pass: the events perturb the step slightly)
-    prof = profile_kernels(lambda: resident_step(0), 3)
+    l1 = lib.kv_launch_count()
+    if args.cuda_graph:
+        prof = profile_kernels(lambda: step._eager(dev_img[0], dev_lab[0]), 3)
+        launches = (lib.kv_launch_count() - l1) // 3 * args.steps  # a replayed graph launches what it captured
+    else:
+        prof = profile_kernels(lambda: resident_step(0), 3)
     by_shape = prof.pop("_by_shape")
     peaks = load_peaks()
     top = max(prof, key=lambda k: prof[k]["ms_per_step"])
@@ -389,7 +394,7 @@ def run_gpu_arm(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if args.precision == "fp32" else "bf16", "data": "synthetic",
             "config": {"workload": workload_name(name, batch), "global_batch": world * batch,
-                       "parallelism": f"dp{world}",
+                       "parallelism": f"dp{world}", "cuda_graph": bool(args.cuda_graph),
                        "l2": f"no flush: one step touches {step_ws_mb:.0f} MB of activations > 126 MB L2"},
             "e2e": {"value": world * batch / (ms_e2e / args.steps * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": img_b, "d2h_bytes_per_step": 4},
@@ -416,6 +421,8 @@ def main():
                          "(default: per config, bf16 for cfg3/cfg4)")
     ap.add_argument("--bf16", action="store_true", help="same as --precision bf16")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cuda-graph", action="store_true",
+                    help="single GPU: capture the whole iteration in a CUDA graph (launch-bound small configs)")
     args = ap.parse_args()
     if args.precision is None:
         args.precision = "bf16" if args.bf16 else DEFAULT_PRECISION[args.config]
