@@ -357,18 +357,36 @@ def run_gpu_arm(args):
         prof = profile_kernels(lambda: resident_step(0), 3)
     by_shape = prof.pop("_by_shape")
     peaks = load_peaks()
+    kernel_ms = sum(v["ms_per_step"] for v in prof.values())
     top = max(prof, key=lambda k: prof[k]["ms_per_step"])
     t = prof[top]
+    # dominant launch kind: entry point x layer shape for the GEMM-shaped kernels (their launches differ in
+    # size by orders of magnitude), the entry point itself otherwise
+    shaped = {k: v for k, v in by_shape.items() if k.startswith(top + " ")}
+    if shaped:
+        top_shape = max(shaped, key=lambda k: shaped[k]["ms_per_call"] * shaped[k]["calls"])
+        ts = shaped[top_shape]
+        top_name, ms_call, calls = top_shape, ts["ms_per_call"], ts["calls"]
+        work_call = ts["tflops"] * 1e12 * ts["ms_per_call"] * 1e-3
+    else:
+        top_name, ms_call, calls, work_call = top, t["ms_per_call"], t["calls"], t["work_per_call"]
     if top in FLOP_KERNELS:
-        achieved = t["work_per_call"] / (t["ms_per_call"] * 1e-3) / 1e12
+        achieved = work_call / (ms_call * 1e-3) / 1e12
         peak, unit, bound = peaks["bf16_tflops_sustained"], "TFLOP/s", "tensor"
     else:
-        achieved = t["work_per_call"] / (t["ms_per_call"] * 1e-3) / 1e9
+        achieved = work_call / (ms_call * 1e-3) / 1e9
         peak, unit, bound = peaks["hbm_gbs"], "GB/s", "hbm"
-    kernel_ms = sum(v["ms_per_step"] for v in prof.values())
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(top_name)  # DRAM bytes of that launch, one ncu --set full capture
     roofline = {"bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
-                "traffic": None, "kernel": top, "kernel_ms_per_call": t["ms_per_call"],
-                "kernel_calls_per_step": t["calls"], "kernel_share_of_step": t["ms_per_step"] / kernel_ms,
+                "traffic": traffic, "kernel": top_name, "kernel_ms_per_call": ms_call,
+                "kernel_calls_per_step": calls, "kernel_share_of_step": ms_call * calls / kernel_ms,
+                "algorithmic_work_per_call": work_call,
+                "entry_point_mean": {"name": top, "achieved": t["work_per_call"] / (t["ms_per_call"] * 1e-3) /
+                                     (1e12 if top in FLOP_KERNELS else 1e9), "share": t["ms_per_step"] / kernel_ms},
                 "peak_source": peaks["source"] + " (sustained bf16 dense / copy bandwidth)",
                 "shares": {k: round(v["ms_per_step"] / kernel_ms, 4) for k, v in
                            sorted(prof.items(), key=lambda kv: -kv[1]["ms_per_step"])},

@@ -60,6 +60,8 @@ typedef enum {
                                      vector (true until KANLinear.update_grid, models/effkan.py:189-242, is used);
                                      enables the closed-form B-spline prologue and the tensor-core gradient kernels */
 
+#define KV_FLAG_ACCUM_GRADS  32u  /* kv_kan_unpack_grads adds into the gradient tensors instead of overwriting them */
+
 /* One KAN (or Linear) layer, or a batch of `n_groups` independent layers of equal
  * shape applied to column slices of the same activation matrix (the per-head Q/K/V
  * maps of MSA, attention.py:136-170,196-197).
@@ -176,7 +178,9 @@ int kv_fastkan_ln_bwd(const kv_kan_desc_t* d, const float* X, const float* dXn, 
 /* Scatter packed gradients back to the reference parameter layouts.  grad_table:
  * device array [n_groups][KV_PTRS_PER_GROUP] of OUTPUT pointers with the same slot
  * meaning as kv_kan_pack (0 = skip); ptr_table = the forward parameters (effkan
- * needs spline_weight and spline_scaler for the product rule, models/effkan.py:166-172). */
+ * needs spline_weight and spline_scaler for the product rule, models/effkan.py:166-172).
+ * With KV_FLAG_ACCUM_GRADS the values are added to what the gradient tensors hold (the caller's
+ * p.grad buffers), which is how autograd accumulates. */
 int kv_kan_unpack_grads(const kv_kan_desc_t* d, const float* dWp, const float* dfparams,
                         const float* dbias, const uint64_t* ptr_table, const uint64_t* grad_table,
                         void* stream);

@@ -20,6 +20,7 @@ KV_FLAG_NO_LAYERNORM = 2
 KV_FLAG_NO_BASE = 4
 KV_FLAG_BF16_TC = 8
 KV_FLAG_UNIFORM_GRID = 16
+KV_FLAG_ACCUM_GRADS = 32
 KV_ERR_UNSUPPORTED = -5
 
 

@@ -145,6 +145,8 @@ __global__ void unpack_grads_kernel(const kv_kan_desc_t d, const float* __restri
                                     const uint64_t* __restrict__ tbl, const uint64_t* __restrict__ gtbl) {
   const int g = blockIdx.y;
   const int M = d.M, in = d.in_features, out = d.out_features, G = d.grid_size;
+  const bool accum = (d.flags & KV_FLAG_ACCUM_GRADS) != 0;  // += into the caller's gradient buffers
+  auto put = [accum](float* dst, float v) { *dst = accum ? *dst + v : v; };
   const size_t n_oi = (size_t)out * in;
   const float* dW = dWp ? dWp + (size_t)g * n_oi * M : nullptr;
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -156,7 +158,7 @@ __global__ void unpack_grads_kernel(const kv_kan_desc_t d, const float* __restri
       switch (d.family) {
         case KV_LINEAR: {
           float* gw = slot_out(gtbl, g, 0);
-          if (gw) gw[p] = src[0];
+          if (gw) put(gw + p, src[0]);
           break;
         }
         case KV_EFFKAN: {
@@ -166,35 +168,35 @@ __global__ void unpack_grads_kernel(const kv_kan_desc_t d, const float* __restri
           float* gsc = slot_out(gtbl, g, 2);
           const float* sw = slot(tbl, g, 1);
           const float* sc = slot(tbl, g, 2);
-          if (gb) gb[p] = src[nb];
+          if (gb) put(gb + p, src[nb]);
           const float scale = sc ? sc[p] : 1.0f;
           float acc = 0.0f;
           for (int m = 0; m < nb; ++m) {
             const float gv = src[m];
-            if (gs) gs[p * nb + m] = gv * scale;
+            if (gs) put(gs + p * nb + m, gv * scale);
             acc += gv * sw[p * nb + m];
           }
-          if (gsc) gsc[p] = acc;
+          if (gsc) put(gsc + p, acc);
           break;
         }
         case KV_CHEBY: {
           float* gc = slot_out(gtbl, g, 0);
           if (gc)
-            for (int m = 0; m < M; ++m) gc[((size_t)i * out + o) * M + m] = src[m];
+            for (int m = 0; m < M; ++m) put(gc + ((size_t)i * out + o) * M + m, src[m]);
           break;
         }
         case KV_FASTKAN: {
           float* gs = slot_out(gtbl, g, 3);
           float* gb = slot_out(gtbl, g, 4);
           if (gs)
-            for (int m = 0; m < G; ++m) gs[(size_t)o * in * G + (size_t)i * G + m] = src[m];
-          if (gb && M > G) gb[p] = src[G];
+            for (int m = 0; m < G; ++m) put(gs + (size_t)o * in * G + (size_t)i * G + m, src[m]);
+          if (gb && M > G) put(gb + p, src[G]);
           break;
         }
         case KV_SINE: {
           float* ga = slot_out(gtbl, g, 0);
           if (ga)
-            for (int m = 0; m < G; ++m) ga[p * G + m] = src[m];
+            for (int m = 0; m < G; ++m) put(ga + p * G + m, src[m]);
           break;
         }
         case KV_FOURIER: {
@@ -202,7 +204,7 @@ __global__ void unpack_grads_kernel(const kv_kan_desc_t d, const float* __restri
           if (gf)
             for (int m = 0; m < M; ++m) {
               const int part = m / G, k = m % G;
-              gf[(((size_t)part * out + o) * in + i) * G + k] = src[m];
+              put(gf + (((size_t)part * out + o) * in + i) * G + k, src[m]);
             }
           break;
         }
@@ -217,7 +219,7 @@ __global__ void unpack_grads_kernel(const kv_kan_desc_t d, const float* __restri
     else if (d.family == KV_FOURIER) s = 1;
     float* gb = s >= 0 ? slot_out(gtbl, g, s) : nullptr;
     if (gb)
-      for (size_t p = tid; p < (size_t)out; p += nth) gb[p] = dbias[(size_t)g * out + p];
+      for (size_t p = tid; p < (size_t)out; p += nth) put(gb + p, dbias[(size_t)g * out + p]);
   }
   if (dfparams != nullptr) {
     const float* dfp = dfparams + (size_t)g * d.fparam_stride;
@@ -225,13 +227,13 @@ __global__ void unpack_grads_kernel(const kv_kan_desc_t d, const float* __restri
       float* gw = slot_out(gtbl, g, 0);
       float* gbb = slot_out(gtbl, g, 1);
       for (size_t p = tid; p < (size_t)in; p += nth) {
-        if (gw) gw[p] = dfp[p];
-        if (gbb) gbb[p] = dfp[in + p];
+        if (gw) put(gw + p, dfp[p]);
+        if (gbb) put(gbb + p, dfp[in + p]);
       }
     } else if (d.family == KV_SINE) {
       float* gf = slot_out(gtbl, g, 1);
       if (gf)
-        for (size_t p = tid; p < (size_t)G; p += nth) gf[p] = dfp[p];
+        for (size_t p = tid; p < (size_t)G; p += nth) put(gf + p, dfp[p]);
     }
   }
 }

@@ -251,7 +251,7 @@ attn_tc_fwd_kernel(const float* __restrict__ qkv, const float* __restrict__ resi
 // backward: row pass (warp = 16 queries: D_i, dQ_i) then column pass (warp = 16 keys: dK_j, dV_j)
 // ------------------------------------------------------------------------------------------
 template <int DHP>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(448)
 attn_tc_bwd_kernel(const float* __restrict__ qkv, const float* __restrict__ dout, const float* __restrict__ lse,
                    float* __restrict__ dqkv, int N, int H, int dh) {
   constexpr int LD = DHP + 8;
@@ -411,10 +411,10 @@ static size_t bwd_smem(int N, int dhp) {
   const size_t np = (N + KC - 1) / KC * KC;
   return (size_t)4 * np * (dhp + 8) * 2 + 2 * np * sizeof(float);
 }
-// warps per CTA: the 16-row blocks spread evenly over at most 8 warps
-static int warps_for(int N) {
+// warps per CTA: the 16-row blocks spread evenly over at most `max_warps` warps
+static int warps_for(int N, int max_warps = 8) {
   const int nrb = (N + 15) / 16;
-  const int rounds = (nrb + 7) / 8;
+  const int rounds = (nrb + max_warps - 1) / max_warps;
   return (nrb + rounds - 1) / rounds;
 }
 static int dhp_for(int dh) { return dh <= 32 ? 32 : 64; }
@@ -462,7 +462,7 @@ extern "C" int kv_attn_bwd_bf16(const float* qkv, const float* dout, const float
   if (B == 0) return KV_OK;
   if (qkv == nullptr || dout == nullptr || lse == nullptr || dqkv == nullptr) return KV_ERR_BAD_ARG;
   if (B == 0) return KV_OK;
-  const int threads = 32 * atc::warps_for(N);
+  const int threads = 32 * atc::warps_for(N, 14);  // one CTA per SM (four staged tiles): more warps, one round
   if (dhp == 32) {
     KV_CUDA(cudaFuncSetAttribute(atc::attn_tc_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
             "attn_tc_bwd smem");

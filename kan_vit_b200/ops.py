@@ -39,6 +39,14 @@ def _require_cuda(*tensors):
 PROFILE = None
 PROFILE_ONLY = None  # None = every call, else a set of names
 
+# Optional gradient sink (set by trainer.TrainStep around backward): an object with
+#   target(param) -> the tensor the gradient of `param` must be ADDED to (its .grad view in the flat bucket
+#                    buffer), or None when the parameter is not managed;
+#   done(param)   -> called once that gradient has been written (bucket bookkeeping / all-reduce trigger).
+# With a sink, kv_kan_unpack_grads accumulates straight into those buffers and autograd gets no parameter
+# gradients back, which removes one small `add` launch per parameter tensor per step.
+GRAD_SINK = None
+
 # Arithmetic of the KAN / Linear GEMMs: "fp32" = exact SIMT kernels (parity 1e-5), "bf16" = tcgen05
 # tensor-core kernels with bf16 operands and fp32 accumulation in TMEM (parity 2e-2).  Activations
 # stay fp32 in HBM in both modes.
@@ -129,6 +137,7 @@ class KanSpec:
         self._tbl_cache = None     # (ptrs, device tensor)
         self.dyn_flags = None      # callable -> per-call flags (effkan: KV_FLAG_UNIFORM_GRID when the grid is)
         self._goff_cache = None    # (shapes key, offsets tensor, mask, total, views meta)
+        self._sink_tbl = None      # (gradient target pointers, device table) when ops.GRAD_SINK is in use
 
     @property
     def n_slices(self):
@@ -305,13 +314,27 @@ class _KanFn(torch.autograd.Function):
                                           L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean), L.ptr(rstd), dwp.data_ptr(),
                                           L.ptr(dbias), st, work=_kan_flops(spec, T), tag=_kan_tag(spec, T))
             off_t, meta, total = spec.grad_layout(flat, dev)
-            gflat = torch.empty((total,), dtype=torch.float32, device=dev)
-            gtbl = torch.where(off_t >= 0, off_t + gflat.data_ptr(), torch.zeros_like(off_t))
-            _call("kv_kan_unpack_grads", lib.kv_kan_unpack_grads, C.byref(d), dwp.data_ptr(), L.ptr(dfp), L.ptr(dbias),
-                                            pk["tbl"].data_ptr(), gtbl.data_ptr(), st)
-            for idx, m in enumerate(meta):
-                if m is not None and flat[idx].requires_grad:
-                    grads[idx] = gflat[m[0]:m[0] + m[1]].view(m[2])
+            sink = GRAD_SINK
+            wanted = [idx for idx, m in enumerate(meta) if m is not None and flat[idx].requires_grad]
+            targets = {idx: sink.target(flat[idx]) for idx in wanted} if sink is not None else {}
+            if sink is not None and all(t is not None and t.is_contiguous() for t in targets.values()):
+                ptrs = tuple(targets[idx].data_ptr() if idx in targets else 0 for idx in range(len(flat)))
+                if spec._sink_tbl is None or spec._sink_tbl[0] != ptrs:
+                    spec._sink_tbl = (ptrs, torch.tensor(ptrs, dtype=torch.int64).to(dev))
+                d2 = L.KanDesc.from_buffer_copy(d)
+                d2.flags |= L.KV_FLAG_ACCUM_GRADS
+                _call("kv_kan_unpack_grads", lib.kv_kan_unpack_grads, C.byref(d2), dwp.data_ptr(), L.ptr(dfp),
+                      L.ptr(dbias), pk["tbl"].data_ptr(), spec._sink_tbl[1].data_ptr(), st)
+                for idx in wanted:
+                    sink.done(flat[idx])
+            else:
+                gflat = torch.empty((total,), dtype=torch.float32, device=dev)
+                gtbl = torch.where(off_t >= 0, off_t + gflat.data_ptr(), torch.zeros_like(off_t))
+                _call("kv_kan_unpack_grads", lib.kv_kan_unpack_grads, C.byref(d), dwp.data_ptr(), L.ptr(dfp),
+                      L.ptr(dbias), pk["tbl"].data_ptr(), gtbl.data_ptr(), st)
+                for idx, m in enumerate(meta):
+                    if m is not None and flat[idx].requires_grad:
+                        grads[idx] = gflat[m[0]:m[0] + m[1]].view(m[2])
         dres = dy if ctx.has_res else None
         dcls = None
         if ctx.has_cls:

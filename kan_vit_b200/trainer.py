@@ -67,6 +67,14 @@ class FlatGradBuckets:
             self._handles.append(dist.all_reduce(self.flat[s:e], op=dist.ReduceOp.SUM, group=self.group,
                                                  async_op=True))
 
+    # -- ops.GRAD_SINK protocol: the KAN layers add their parameter gradients straight into the flat buffer
+    def target(self, p):
+        return p.grad if id(p) in self._bucket_of else None
+
+    def done(self, p):
+        if self.world > 1:
+            self._on_grad(p)
+
     def finish(self):
         """Wait for the collectives, reduce buckets whose hooks never fired (unused parameters),
         and turn the sums into means."""
@@ -109,7 +117,14 @@ class TrainStep:
         self.grads.zero()
         logits = self.model(images)
         loss = F.cross_entropy(logits, labels)
-        loss.backward()
+        if images.is_cuda:
+            from . import ops
+            ops.GRAD_SINK = self.grads
+        try:
+            loss.backward()
+        finally:
+            if images.is_cuda:
+                ops.GRAD_SINK = None
         self.grads.finish()
         self.opt.step()
         return loss.detach()
