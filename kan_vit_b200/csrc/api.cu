@@ -303,7 +303,8 @@ unsigned long long kv_launch_count(void) { return __atomic_load_n(&g_launches, _
 // first group of each slice (fparam_stride scaled), which the uniform-grid flag makes equal to the others.
 static kv_kan_desc_t tc_view(const kv_kan_desc_t& d) {
   kv_kan_desc_t v = d;
-  if ((d.flags & KV_FLAG_BF16_TC) && d.family == KV_EFFKAN && (d.flags & KV_FLAG_UNIFORM_GRID) && d.x_share > 1 &&
+  const bool mergeable = (d.family == KV_EFFKAN && (d.flags & KV_FLAG_UNIFORM_GRID)) || d.family == KV_LINEAR;
+  if ((d.flags & KV_FLAG_BF16_TC) && mergeable && d.x_share > 1 &&
       d.n_groups % d.x_share == 0 && d.out_features * d.x_share <= 512) {
     v.n_groups = d.n_groups / d.x_share;
     v.out_features = d.out_features * d.x_share;
@@ -420,7 +421,7 @@ int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, co
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
   if ((d->flags & KV_FLAG_BF16_TC) && wtiles_t_bf16 != nullptr && dy_image != nullptr)
-    return tc_bwd_input(tc_view(*d), X, dy_image, wtiles_t_bf16, fparams, dX, (cudaStream_t)stream);
+    return tc_bwd_input(tc_view(*d), X, dY, act_mask, dy_image, wtiles_t_bf16, fparams, dX, (cudaStream_t)stream);
   if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;
   return simt_bwd_input(*d, X, dY, act_mask, wp_f32, fparams, mean, rstd, dX, dXn, dfparams,
                         (cudaStream_t)stream);

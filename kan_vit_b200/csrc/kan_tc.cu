@@ -181,6 +181,40 @@ __global__ void tc_pack_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, co
   }
 }
 
+// Linear input gradient: dX = dY . W is the forward of the TRANSPOSED layer (in' = out, out' = in), so its
+// operand image is the forward image of W^T.  dt = descriptor of that transposed layer (geometry gmt), d / d0 as
+// above.  Element (output row o' = input feature of the layer, K element i' = output of the layer).
+__global__ void tc_pack_linear_t_kernel(const kv_kan_desc_t dt, const kv_kan_desc_t d, const kv_kan_desc_t d0,
+                                        const uint64_t* __restrict__ tbl, __nv_bfloat16* __restrict__ wt, Geom gmt) {
+  const size_t total8 = (size_t)dt.n_groups * gmt.n_tiles * gmt.tile_elems() / 8;
+  const int xs = d.n_groups == d0.n_groups ? 1 : d0.x_share;
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total8;
+       idx += (size_t)gridDim.x * blockDim.x) {
+    size_t r = idx;
+    const int r8 = r % 8; r /= 8;
+    int pr = r % (gmt.BN / 8); r /= (gmt.BN / 8);
+    const int u = r % gmt.n_units; r /= gmt.n_units;
+    const int rank = r % 2; r /= 2;
+    const int nt = r % gmt.n_tiles; r /= gmt.n_tiles;
+    const int g = (int)r;
+    const int n1 = gmt.BN > 256 ? 256 : gmt.BN, n2 = gmt.BN - n1;
+    int j = 0, nj = n1;
+    if (pr >= n1 / 8) { pr -= n1 / 8; j = 1; nj = n2; }
+    const int h = pr / (nj / 16), rgl = pr % (nj / 16);
+    const int op = nt * gmt.BN + (j ? n1 : 0) + rank * (nj / 2) + rgl * 8 + r8;  // o' : input feature of the layer
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int ip = u * KU + h * 8 + e;  // i' : output of the (merged) layer
+      v[e] = 0.0f;
+      if (op < d.in_features && ip < d.out_features)
+        v[e] = load_packed_weight(d0, tbl, g * xs + ip / d0.out_features, ip % d0.out_features, op, 0);
+    }
+    *reinterpret_cast<uint4*>(wt + idx * 8) = make_uint4(pack_bf16_pair(v[0], v[1]), pack_bf16_pair(v[2], v[3]),
+                                                         pack_bf16_pair(v[4], v[5]), pack_bf16_pair(v[6], v[7]));
+  }
+}
+
 // scattered bf16 stores of Phi_m(x) into a chunk slot (basis-major layout): unit m at m * A_UNIT_BYTES
 struct UnitSink {
   static constexpr bool kDense = true;
@@ -227,6 +261,7 @@ struct FwdParams {
   const float* pos;
   float* Y;
   Geom gm;
+  const float* in_mask;  // Linear only, nullable: the input is X * (in_mask > 0), same addressing as X
 };
 
 // 8 consecutive features of one row (zero beyond `in` / beyond T)
@@ -540,12 +575,26 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       rs = p.rstd[(size_t)t * n_slices + slice];
     }
     const int row_off = (r >> 3) * 128 + (r & 7) * 16;
+    // Linear as the input gradient of a ReLU layer: dY is gated by the layer's own forward output
+    const float* mrow = (F == KV_LINEAR && p.in_mask != nullptr)
+                            ? p.in_mask + (size_t)(row_ok ? t : 0) * d.ldx + xoff : nullptr;
+    const bool mvec = vec && ((reinterpret_cast<uintptr_t>(p.in_mask) & 15) == 0);
+    auto gate = [&](int i0g, float (&v)[8]) {
+      if (F == KV_LINEAR && mrow != nullptr) {
+        float mk[8];
+        load_x8(mrow, i0g, in, row_ok, mvec, mk);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = mk[q] > 0.0f ? v[q] : 0.0f;
+      }
+    };
     float cur[8];
     load_x8(xrow, wg * 8, in, row_ok, vec, cur);
+    gate(wg * 8, cur);
     for (int ch = 0; ch < gm.n_chunks; ++ch) {
       float nxt[8];
       if (ch + 1 < gm.n_chunks) {
         load_x8(xrow, (ch + 1) * KU + wg * 8, in, row_ok, vec, nxt);
+        gate((ch + 1) * KU + wg * 8, nxt);
       } else {
 #pragma unroll
         for (int q = 0; q < 8; ++q) nxt[q] = 0.0f;
@@ -1279,12 +1328,29 @@ size_t tc_wtiles_bytes(const kv_kan_desc_t& d) {
   return (size_t)d.n_groups * gm.n_tiles * gm.tile_elems() * 2;
 }
 
-// the tensor-core gradient kernels exist for the default effkan on a uniform grid, one group per slice
+// the tensor-core gradient kernels exist for the default effkan on a uniform grid and for nn.Linear
+// (without the class-token row map), one group per slice
+static bool tc_bwd_linear(const kv_kan_desc_t& d) {
+  return d.family == KV_LINEAR && d.x_share == 1 && d.rows_in == 0 && (d.ldx % 4) == 0 && (d.ldy % 4) == 0 &&
+         d.in_features % 4 == 0 && d.out_features % 4 == 0;
+}
 static bool tc_bwd_ok(const kv_kan_desc_t& d) {
-  return tc::make_geom(d).effkan8 && d.x_share == 1 && d.M == 9;
+  return (tc::make_geom(d).effkan8 && d.x_share == 1 && d.M == 9) || tc_bwd_linear(d);
+}
+// Linear: dX = dY . W runs as the forward kernel of the transposed layer
+static kv_kan_desc_t linear_transposed(const kv_kan_desc_t& d) {
+  kv_kan_desc_t t = d;
+  t.in_features = d.out_features;
+  t.out_features = d.in_features;
+  t.ldx = d.ldy;
+  t.ldy = d.ldx;
+  t.flags = d.flags & ~(uint32_t)KV_FLAG_RELU;
+  t.fparam_stride = 0;
+  return t;
 }
 size_t tc_wtiles_t_bytes(const kv_kan_desc_t& d) {
   if (!tc_bwd_ok(d)) return 0;
+  if (d.family == KV_LINEAR) return tc_wtiles_bytes(linear_transposed(d));
   const tc::BwdGeom b = tc::make_bwd_geom(d);
   return (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * b.n_sub * b.SW * 64;
 }
@@ -1309,7 +1375,15 @@ int tc_pack(const kv_kan_desc_t& d, const kv_kan_desc_t& d0, const uint64_t* ptr
                                                              reinterpret_cast<__nv_bfloat16*>(wtiles), gm);
     KV_CHECK_LAUNCH("tc_pack_kernel");
   }
-  if (wtiles_t != nullptr) {
+  if (wtiles_t != nullptr && d.family == KV_LINEAR) {
+    if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
+    const kv_kan_desc_t dt = linear_transposed(d);
+    const tc::Geom gmt = tc::make_geom(dt);
+    const size_t total = (size_t)dt.n_groups * gmt.n_tiles * gmt.tile_elems() / 8;
+    tc::tc_pack_linear_t_kernel<<<grid_for(total, 256), 256, 0, st>>>(dt, d, d0, ptr_table,
+                                                                      reinterpret_cast<__nv_bfloat16*>(wtiles_t), gmt);
+    KV_CHECK_LAUNCH("tc_pack_linear_t_kernel");
+  } else if (wtiles_t != nullptr) {
     if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
     const tc::BwdGeom b = tc::make_bwd_geom(d);
     const size_t total = tc_wtiles_t_bytes(d) / 128;
@@ -1344,6 +1418,7 @@ int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const flo
   p.pos = pos;
   p.Y = Y;
   p.gm = tc::make_geom(d);
+  p.in_mask = nullptr;
   switch (d.family) {
     case KV_LINEAR: return tc::launch_fwd<KV_LINEAR>(p, st);
     case KV_EFFKAN: return tc::launch_fwd<KV_EFFKAN>(p, st);
@@ -1355,9 +1430,21 @@ int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const flo
   return KV_ERR_BAD_FAMILY;
 }
 
-int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const void* dy_image, const void* wtiles_t,
-                 const float* fparams, float* dX, cudaStream_t st) {
+int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const float* act_mask, const void* dy_image,
+                 const void* wtiles_t, const float* fparams, float* dX, cudaStream_t st) {
   if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
+  if (d.family == KV_LINEAR) {
+    tc::FwdParams q;
+    q.d = linear_transposed(d);
+    q.X = dY;
+    q.wt = reinterpret_cast<const __nv_bfloat16*>(wtiles_t);
+    q.fparams = nullptr;
+    q.bias = q.mean = q.rstd = q.residual = q.pos = nullptr;
+    q.Y = dX;
+    q.gm = tc::make_geom(q.d);
+    q.in_mask = (d.flags & KV_FLAG_RELU) ? act_mask : nullptr;
+    return tc::launch_fwd<KV_LINEAR>(q, st);
+  }
   static bool attr_set = false;
   if (!attr_set) {
     KV_CUDA(cudaFuncSetAttribute(tc::effkan8_bwd_input_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1387,6 +1474,8 @@ int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, 
   if (!attr_set) {
     KV_CUDA(cudaFuncSetAttribute(tc::kan_tc_bwd_weight_kernel<KV_EFFKAN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  tc::BW_SMEM), "tc_bwd_weight smem attribute");
+    KV_CUDA(cudaFuncSetAttribute(tc::kan_tc_bwd_weight_kernel<KV_LINEAR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 tc::BW_SMEM), "tc_bwd_weight smem attribute");
     attr_set = true;
   }
   tc::BwdWParams p;
@@ -1397,7 +1486,9 @@ int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, 
   p.dWp = dWp;
   p.b = tc::make_bwd_geom(d);
   p.gm = tc::make_geom(d);
-  p.KT = p.b.n_chunks + (p.b.n_chunks + 7) / 8;
+  // K' tiles of 128 basis columns: effkan = one per 16-feature chunk (8 splines each) + one per 128 features
+  // (SiLU column); Linear = one per 128 features
+  p.KT = d.family == KV_LINEAR ? (d.in_features + 127) / 128 : p.b.n_chunks + (p.b.n_chunks + 7) / 8;
   p.n_kpairs = (p.KT + 1) / 2;
   // split T so that the grid fills the 74 CTA-pair slots evenly; every split keeps >= 512 rows
   const int P = p.n_kpairs * p.gm.n_tiles * d.n_groups;
@@ -1409,11 +1500,15 @@ int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, 
     const double eff = waves / (double)(long long)(waves + 0.999999);
     if (eff > best_eff + 0.03) { best_eff = eff; best = s; }
   }
-  p.tsplits = best;
   p.rows_per_split = (ceil_div(d.T, best) + 63) / 64 * 64;
+  p.tsplits = ceil_div(d.T, p.rows_per_split);  // rounding to whole 64-row stages may empty the last splits
+  best = p.tsplits;
   if ((long long)p.n_kpairs * p.gm.n_tiles > 65535 || (long long)d.n_groups * best > 65535) return KV_ERR_BAD_SHAPE;
   dim3 grid(2, p.n_kpairs * p.gm.n_tiles, d.n_groups * best);
-  tc::kan_tc_bwd_weight_kernel<KV_EFFKAN><<<grid, tc::NTHREADS, tc::BW_SMEM, st>>>(p);
+  if (d.family == KV_LINEAR)
+    tc::kan_tc_bwd_weight_kernel<KV_LINEAR><<<grid, tc::NTHREADS, tc::BW_SMEM, st>>>(p);
+  else
+    tc::kan_tc_bwd_weight_kernel<KV_EFFKAN><<<grid, tc::NTHREADS, tc::BW_SMEM, st>>>(p);
   KV_CHECK_LAUNCH("kan_tc_bwd_weight_kernel");
   return KV_OK;
 }

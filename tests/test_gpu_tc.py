@@ -191,3 +191,98 @@ def test_bf16_attention_vs_own_fp32(B, N, H, dh):
     ref = torch.softmax(q @ k.transpose(-1, -2) / dh ** 0.5, -1) @ v
     ref = ref.permute(0, 2, 1, 3).reshape(B * N, H * dh) + res.double()
     assert relerr(o16, ref.float()) < TOL_BF16
+
+
+@pytest.mark.parametrize("T,i,o,relu", [(300, 256, 1024, True), (1000, 768, 3072, False), (130, 64, 200, True),
+                                        (257, 100, 36, False)])
+def test_bf16_linear_gradients_vs_own_fp32(T, i, o, relu):
+    """nn.Linear on the tensor cores in both directions: dX = (dY * relu-mask) . W as the forward kernel of the
+    transposed layer, dW through the MN-major weight-gradient kernel; against the exact fp32 kernels."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(4)
+    m = torch.nn.Linear(i, o).to(_dev())
+    spec = make_spec([m])
+    x0 = torch.randn(T, i, device=_dev())
+    if relu:
+        # the ReLU gate must be the same in both modes for the gradients to be comparable (one flipped gate moves a
+        # whole dY element in or out of a row's sum): inputs and weights on a bf16-exact grid and a bias that
+        # keeps every pre-activation at least 1/64 away from zero
+        with torch.no_grad():
+            m.weight.copy_(torch.randint(-8, 9, (o, i), device=_dev()).float() / 8)
+            m.bias.copy_(torch.randint(-8, 9, (o,), device=_dev()).float() / 32 + 1.0 / 64)
+        x0 = torch.randint(-8, 9, (T, i), device=_dev()).float() / 4
+    dy = torch.randn(T, o, device=_dev())
+
+    def run(mode):
+        K.set_precision(mode)
+        m.zero_grad(set_to_none=True)
+        x = x0.clone().requires_grad_(True)
+        y = ops.kan_apply(x, spec, [slots_of(m)], relu=relu)
+        y.backward(dy)
+        return y.detach(), x.grad, {k: p.grad.clone() for k, p in m.named_parameters()}
+
+    y16, gx16, gp16 = run("bf16")
+    y32, gx32, gp32 = run("fp32")
+    K.set_precision("bf16")
+    assert relerr(y16, y32) < TOL_BF16
+    if relu:
+        assert torch.equal(y16 > 0, y32 > 0)
+    assert relerr(gx16, gx32) < TOL_BF16
+    for k in gp32:
+        assert relerr(gp16[k], gp32[k]) < TOL_BF16, k
+
+
+@pytest.mark.parametrize("T,i,o", [(17408, 192, 768), (17408, 768, 192), (1100, 48, 3072)])
+def test_bf16_weight_gradient_row_splits(T, i, o):
+    """Weight gradients whose row range is cut into many splits (few K' tiles): the 64-row rounding of a split must
+    not leave an empty one (a CTA without stages would never signal its accumulator)."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(6)
+    for m in (torch.nn.Linear(i, o).to(_dev()), K.KANLinear(i, o).to(_dev())):
+        spec = make_spec([m])
+        x0 = torch.randn(T, i, device=_dev())
+        dy = torch.randn(T, o, device=_dev())
+        out = {}
+        for mode in ("bf16", "fp32"):
+            K.set_precision(mode)
+            m.zero_grad(set_to_none=True)
+            ops.kan_apply(x0, spec, [slots_of(m)]).backward(dy)
+            out[mode] = {k: p.grad.clone() for k, p in m.named_parameters()}
+        K.set_precision("bf16")
+        for k in out["fp32"]:
+            assert relerr(out["bf16"][k], out["fp32"][k]) < TOL_BF16, k
+
+
+def test_bf16_grouped_qkv_linear_vs_own_fp32():
+    """The vanilla per-head q/k/v maps (nn.Linear, three groups per slice) merged into one layer per head."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(5)
+    T, H, dh = 394, 12, 64
+    mods = [torch.nn.Linear(dh, dh).to(_dev()) for _ in range(3 * H)]
+    spec = make_spec(mods, x_share=3)
+    x0 = torch.randn(T, H * dh, device=_dev())
+    dy = torch.randn(T, 3 * H * dh, device=_dev())
+
+    def run(mode):
+        K.set_precision(mode)
+        for m in mods:
+            m.zero_grad(set_to_none=True)
+        x = x0.clone().requires_grad_(True)
+        y = ops.kan_apply(x, spec, [slots_of(m) for m in mods])
+        y.backward(dy)
+        return y.detach(), x.grad, [{k: p.grad.clone() for k, p in m.named_parameters()} for m in mods]
+
+    y16, gx16, gp16 = run("bf16")
+    y32, gx32, gp32 = run("fp32")
+    K.set_precision("bf16")
+    assert relerr(y16, y32) < TOL_BF16
+    assert relerr(gx16, gx32) < TOL_BF16
+    for a, b in zip(gp16, gp32):
+        for k in b:
+            assert relerr(a[k], b[k]) < TOL_BF16, k
