@@ -303,7 +303,9 @@ unsigned long long kv_launch_count(void) { return __atomic_load_n(&g_launches, _
 // first group of each slice (fparam_stride scaled), which the uniform-grid flag makes equal to the others.
 static kv_kan_desc_t tc_view(const kv_kan_desc_t& d) {
   kv_kan_desc_t v = d;
-  const bool mergeable = (d.family == KV_EFFKAN && (d.flags & KV_FLAG_UNIFORM_GRID)) || d.family == KV_LINEAR;
+  // effkan needs one shared knot vector; Linear / ChebyKAN / Fourier have no per-module prologue parameters
+  const bool mergeable = (d.family == KV_EFFKAN && (d.flags & KV_FLAG_UNIFORM_GRID)) || d.family == KV_LINEAR ||
+                         d.family == KV_CHEBY || d.family == KV_FOURIER;
   if ((d.flags & KV_FLAG_BF16_TC) && mergeable && d.x_share > 1 &&
       d.n_groups % d.x_share == 0 && d.out_features * d.x_share <= 512) {
     v.n_groups = d.n_groups / d.x_share;
@@ -440,7 +442,7 @@ int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, c
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
   if ((d->flags & KV_FLAG_BF16_TC) && dy_image != nullptr && tc_bwd_weight_available(tc_view(*d))) {
-    rc = tc_bwd_weight(tc_view(*d), X, dy_image, fparams, dWp, (cudaStream_t)stream);
+    rc = tc_bwd_weight(tc_view(*d), X, dy_image, fparams, mean, rstd, dWp, (cudaStream_t)stream);
     if (rc != KV_OK) return rc;
     if (dbias == nullptr) return KV_OK;
     return simt_col_sums(*d, dY, act_mask, dbias, (cudaStream_t)stream);

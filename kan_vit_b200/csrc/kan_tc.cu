@@ -313,16 +313,39 @@ __device__ __forceinline__ void effkan8_chunk(uint8_t* base, int wg, const float
 }
 
 // Basis-major layout, basis index outermost: 8 features x one m = one 16-byte store.
+// basis_octet: the values of 8 consecutive features (one 16-byte vector per basis function m) for the bases
+// m0 <= m < m0 + Mt, written at dst + (m - m0) * stride.
+struct StrideSink {  // per-feature scattered bf16 stores (generic Cox-de Boor path)
+  static constexpr bool kDense = true;
+  uint8_t* base;
+  int stride, m0, Mt;
+  __device__ __forceinline__ void put(int m, float v) {
+    if (m >= m0 && m < m0 + Mt) *reinterpret_cast<__nv_bfloat16*>(base + (m - m0) * stride) = __float2bfloat16_rn(v);
+  }
+};
+
 template <int F>
-__device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const float (&x)[8], const BasisCtx& c,
-                                                  int i0, float mu, float rs) {
-  uint8_t* dst = base + wg * 2048;
+__device__ __forceinline__ void basis_octet(uint8_t* dst, int stride, int m0, int Mt, const float (&x)[8],
+                                            const BasisCtx& c, int i0, float mu, float rs) {
   const int M = c.M;
   float v[8];
   auto emit = [&](int m) {
-    sts128(dst + m * A_UNIT_BYTES, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
-           pack_bf16(v[6], v[7]));
+    if (m >= m0 && m < m0 + Mt)
+      sts128(dst + (m - m0) * stride, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+             pack_bf16(v[6], v[7]));
   };
+  if (F == KV_EFFKAN) {
+#pragma unroll 1
+    for (int q = 0; q < 8; ++q) {
+      StrideSink sink{dst + q * 2, stride, m0, Mt};
+      if (i0 + q < c.in) {
+        basis_eval<F>(c, i0 + q, x[q], x[q], sink);
+      } else {
+        for (int m = 0; m < M; ++m) sink.put(m, 0.0f);
+      }
+    }
+    return;
+  }
   if (F == KV_LINEAR) {
 #pragma unroll
     for (int q = 0; q < 8; ++q) v[q] = x[q];
@@ -410,6 +433,12 @@ __device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const f
       emit(m);
     }
   }
+}
+
+template <int F>
+__device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const float (&x)[8], const BasisCtx& c,
+                                                  int i0, float mu, float rs) {
+  basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, 0, c.M, x, c, i0, mu, rs);
 }
 
 template <int F>
@@ -1071,6 +1100,11 @@ struct BwdWParams {
   int KT;        // number of 128-wide K' tiles
   int n_kpairs;  // ceil(KT / 2)
   int tsplits, rows_per_split;
+  // generic tiles (every family but the default effkan / Linear): a tile = `no` feature octets x `Mt` bases,
+  // block b (8 columns) = octet b / Mt, basis m0 + b % Mt;  M > 16 splits the bases over `tpo` tiles per octet
+  int generic, no, tpo;
+  const float* mean;
+  const float* rstd;
 };
 
 template <int F>
@@ -1103,8 +1137,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
   const int in = d.in_features;
   const bool tile_live = kt < p.KT;
   // tile kind: effkan spline tile (chunk kt) | effkan SiLU tile | linear feature tile
-  const bool spline_tile = (F == KV_EFFKAN) && kt < b.n_chunks;
+  const bool generic = p.generic != 0;
+  const bool spline_tile = !generic && (F == KV_EFFKAN) && kt < b.n_chunks;
   const int feat0 = spline_tile ? kt * KU : ((F == KV_EFFKAN) ? (kt - b.n_chunks) * 128 : kt * 128);
+  // generic tile: octets [oc0, oc0 + no), bases [m0, m0 + Mt)
+  const int g_oc0 = generic ? (p.tpo > 1 ? kt / p.tpo : kt * p.no) : 0;
+  const int g_m0 = (generic && p.tpo > 1) ? (kt % p.tpo) * 16 : 0;
+  const int g_Mt = generic ? (p.tpo > 1 ? min(16, d.M - g_m0) : d.M) : 1;
 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < BW_NA; ++s) {
@@ -1211,6 +1250,38 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     const int row_off = (tl >> 4) * 4096 + ((tl >> 3) & 1) * 2048 + (tl & 7) * 16;
     int s = 0;
     uint32_t ph = 1;
+    if (generic) {
+      // ---- generic producers: thread = (row tl, part fb); part fb evaluates octets fb, fb + 4, ... of the tile
+      const BasisCtx c = make_ctx(d, p.fparams, g);
+      const int n_slices = d.n_groups / d.x_share, slice = g / d.x_share;
+      const bool ln = (F == KV_FASTKAN) && !(d.flags & KV_FLAG_NO_LAYERNORM);
+      int s = 0;
+      uint32_t ph = 1;
+      for (int st = 0; st < n_stages; ++st) {
+        const int t = row0 + st * 64 + tl;
+        const bool row_ok = t < row1;
+        const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
+        float mu = 0.f, rs = 1.f;
+        if (ln && row_ok) {
+          mu = p.mean[(size_t)t * n_slices + slice];
+          rs = p.rstd[(size_t)t * n_slices + slice];
+        }
+        ptx::mbar_wait(emptyA(s), ph);
+        uint8_t* base = sA + s * BW_A_STAGE + row_off;
+        if (tile_live) {
+          for (int oq = fb; oq < p.no; oq += 4) {
+            const int i0 = (g_oc0 + oq) * 8;
+            float x8[8];
+            load_x8(xrow, i0, in, row_ok && i0 < in, vec, x8);
+            basis_octet<F>(base + oq * g_Mt * 128, 128, g_m0, g_Mt, x8, c, i0, mu, rs);
+          }
+        }
+        ptx::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(s), 0));
+        if (++s == BW_NA) { s = 0; ph ^= 1; }
+      }
+    } else
     for (int st = 0; st < n_stages; ++st) {
       const int t = row0 + st * 64 + tl;
       const bool row_ok = t < row1;
@@ -1285,7 +1356,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       const int q4 = warp & 3, half = pw >> 2;
       const int l = q4 * 32 + lane;  // K' index inside the tile
       int i, m;
-      if (spline_tile) {
+      if (generic) {
+        const int blk = l >> 3;  // block = (octet, basis)
+        i = (g_oc0 + blk / g_Mt) * 8 + (l & 7);
+        m = g_m0 + blk % g_Mt;
+        if (blk >= p.no * g_Mt) i = in;  // unused block of the tile
+      } else if (spline_tile) {
         i = feat0 + (l >> 3);  // K' block f of the tile = feature f of the chunk, 8 splines each
         m = l & 7;
       } else {
@@ -1334,8 +1410,13 @@ static bool tc_bwd_linear(const kv_kan_desc_t& d) {
   return d.family == KV_LINEAR && d.x_share == 1 && d.rows_in == 0 && (d.ldx % 4) == 0 && (d.ldy % 4) == 0 &&
          d.in_features % 4 == 0 && d.out_features % 4 == 0;
 }
-static bool tc_bwd_ok(const kv_kan_desc_t& d) {
+static bool tc_bwd_ok(const kv_kan_desc_t& d) {  // input-gradient kernel available
   return (tc::make_geom(d).effkan8 && d.x_share == 1 && d.M == 9) || tc_bwd_linear(d);
+}
+// weight-gradient kernel: every family (generic basis tiles), one group per slice
+static bool tc_bwd_w_ok(const kv_kan_desc_t& d) {
+  if (tc_bwd_ok(d)) return true;
+  return d.family != KV_LINEAR && d.x_share == 1 && d.M <= tc::MAX_M_TC;
 }
 // Linear: dX = dY . W runs as the forward kernel of the transposed layer
 static kv_kan_desc_t linear_transposed(const kv_kan_desc_t& d) {
@@ -1355,11 +1436,12 @@ size_t tc_wtiles_t_bytes(const kv_kan_desc_t& d) {
   return (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * b.n_sub * b.SW * 64;
 }
 size_t tc_dy_image_bytes(const kv_kan_desc_t& d) {
-  if (!tc_bwd_ok(d)) return 0;
+  if (!tc_bwd_w_ok(d)) return 0;
   const tc::BwdGeom b = tc::make_bwd_geom(d);
   return (size_t)d.n_groups * b.T8 * b.O8 * 128;
 }
-bool tc_bwd_weight_available(const kv_kan_desc_t& d) { return tc_bwd_ok(d); }
+bool tc_bwd_weight_available(const kv_kan_desc_t& d) { return tc_bwd_w_ok(d); }
+bool tc_bwd_input_available(const kv_kan_desc_t& d) { return tc_bwd_ok(d); }
 
 static int grid_for(size_t total, int threads) {
   const size_t blocks = (total + threads - 1) / threads;
@@ -1394,7 +1476,7 @@ int tc_pack(const kv_kan_desc_t& d, const kv_kan_desc_t& d0, const uint64_t* ptr
 }
 
 int tc_dy_image(const kv_kan_desc_t& d, const float* dY, const float* act_mask, void* image, cudaStream_t st) {
-  if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
+  if (!tc_bwd_w_ok(d)) return KV_ERR_UNSUPPORTED;
   const tc::BwdGeom b = tc::make_bwd_geom(d);
   const size_t total = (size_t)d.n_groups * b.T8 * b.O8 * 8;
   tc::dy_image_kernel<<<grid_for(total, 256), 256, 0, st>>>(d, dY, act_mask, reinterpret_cast<__nv_bfloat16*>(image), b);
@@ -1467,17 +1549,22 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
   return KV_OK;
 }
 
-int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, const float* fparams, float* dWp,
-                  cudaStream_t st) {
-  if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
+template <int F>
+static int launch_bwd_weight(const tc::BwdWParams& p, dim3 grid, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    KV_CUDA(cudaFuncSetAttribute(tc::kan_tc_bwd_weight_kernel<KV_EFFKAN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 tc::BW_SMEM), "tc_bwd_weight smem attribute");
-    KV_CUDA(cudaFuncSetAttribute(tc::kan_tc_bwd_weight_kernel<KV_LINEAR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    KV_CUDA(cudaFuncSetAttribute(tc::kan_tc_bwd_weight_kernel<F>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  tc::BW_SMEM), "tc_bwd_weight smem attribute");
     attr_set = true;
   }
+  tc::kan_tc_bwd_weight_kernel<F><<<grid, tc::NTHREADS, tc::BW_SMEM, st>>>(p);
+  KV_CHECK_LAUNCH("kan_tc_bwd_weight_kernel");
+  return KV_OK;
+}
+
+int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, const float* fparams,
+                  const float* mean, const float* rstd, float* dWp, cudaStream_t st) {
+  if (!tc_bwd_w_ok(d)) return KV_ERR_UNSUPPORTED;
   tc::BwdWParams p;
   p.d = d;
   p.X = X;
@@ -1488,7 +1575,23 @@ int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, 
   p.gm = tc::make_geom(d);
   // K' tiles of 128 basis columns: effkan = one per 16-feature chunk (8 splines each) + one per 128 features
   // (SiLU column); Linear = one per 128 features
-  p.KT = d.family == KV_LINEAR ? (d.in_features + 127) / 128 : p.b.n_chunks + (p.b.n_chunks + 7) / 8;
+  p.mean = mean;
+  p.rstd = rstd;
+  p.generic = tc_bwd_ok(d) ? 0 : 1;
+  p.no = 1;
+  p.tpo = 1;
+  if (p.generic) {
+    const int n_oct = (d.in_features + 7) / 8;
+    if (d.M <= 16) {
+      p.no = 16 / d.M;
+      p.KT = (n_oct + p.no - 1) / p.no;
+    } else {
+      p.tpo = (d.M + 15) / 16;
+      p.KT = n_oct * p.tpo;
+    }
+  } else {
+    p.KT = d.family == KV_LINEAR ? (d.in_features + 127) / 128 : p.b.n_chunks + (p.b.n_chunks + 7) / 8;
+  }
   p.n_kpairs = (p.KT + 1) / 2;
   // split T so that the grid fills the 74 CTA-pair slots evenly; every split keeps >= 512 rows
   const int P = p.n_kpairs * p.gm.n_tiles * d.n_groups;
@@ -1505,12 +1608,15 @@ int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, 
   best = p.tsplits;
   if ((long long)p.n_kpairs * p.gm.n_tiles > 65535 || (long long)d.n_groups * best > 65535) return KV_ERR_BAD_SHAPE;
   dim3 grid(2, p.n_kpairs * p.gm.n_tiles, d.n_groups * best);
-  if (d.family == KV_LINEAR)
-    tc::kan_tc_bwd_weight_kernel<KV_LINEAR><<<grid, tc::NTHREADS, tc::BW_SMEM, st>>>(p);
-  else
-    tc::kan_tc_bwd_weight_kernel<KV_EFFKAN><<<grid, tc::NTHREADS, tc::BW_SMEM, st>>>(p);
-  KV_CHECK_LAUNCH("kan_tc_bwd_weight_kernel");
-  return KV_OK;
+  switch (d.family) {
+    case KV_LINEAR: return launch_bwd_weight<KV_LINEAR>(p, grid, st);
+    case KV_EFFKAN: return launch_bwd_weight<KV_EFFKAN>(p, grid, st);
+    case KV_CHEBY: return launch_bwd_weight<KV_CHEBY>(p, grid, st);
+    case KV_FASTKAN: return launch_bwd_weight<KV_FASTKAN>(p, grid, st);
+    case KV_SINE: return launch_bwd_weight<KV_SINE>(p, grid, st);
+    case KV_FOURIER: return launch_bwd_weight<KV_FOURIER>(p, grid, st);
+  }
+  return KV_ERR_BAD_FAMILY;
 }
 
 }  // namespace kv

@@ -286,3 +286,50 @@ def test_bf16_grouped_qkv_linear_vs_own_fp32():
     for a, b in zip(gp16, gp32):
         for k in b:
             assert relerr(a[k], b[k]) < TOL_BF16, k
+
+
+def _family_layer(name, i, o):
+    import kan_vit_b200 as K
+    return {
+        "cheby": lambda: K.ChebyKANLayer(i, o, 4),
+        "cheby10": lambda: K.ChebyKANLayer(i, o, 10),
+        "fastkan": lambda: K.FastKANLayer(i, o),
+        "fastkan20": lambda: K.FastKANLayer(i, o, num_grids=20),
+        "sine": lambda: K.SineKANLayer(i, o),
+        "sine20": lambda: K.SineKANLayer(i, o, grid_size=20),
+        "fourier": lambda: K.NaiveFourierKANLayer(i, o, 5),
+        "fourier10": lambda: K.NaiveFourierKANLayer(i, o, 10),
+        "effkan10": lambda: K.KANLinear(i, o, grid_size=10),
+        "effkan20": lambda: K.KANLinear(i, o, grid_size=20),
+        "effkan_k2": lambda: K.KANLinear(i, o, grid_size=6, spline_order=2),
+    }[name]()
+
+
+@pytest.mark.parametrize("name", ["cheby", "cheby10", "fastkan", "fastkan20", "sine", "sine20", "fourier", "fourier10",
+                                  "effkan10", "effkan20", "effkan_k2"])
+@pytest.mark.parametrize("T,i,o", [(700, 72, 200), (1300, 192, 528)])
+def test_bf16_family_gradients_vs_own_fp32(name, T, i, o):
+    """Every basis family in bf16 mode (forward and weight gradient on the tensor cores through the generic
+    octet x basis tiles, whatever the family has for the input gradient) against the exact fp32 kernels."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(7)
+    m = _family_layer(name, i, o).to(_dev())
+    spec = make_spec([m])
+    x0 = torch.randn(T, i, device=_dev())
+    dy = torch.randn(T, o, device=_dev())
+    res = {}
+    for mode in ("bf16", "fp32"):
+        K.set_precision(mode)
+        m.zero_grad(set_to_none=True)
+        x = x0.clone().requires_grad_(True)
+        y = ops.kan_apply(x, spec, [slots_of(m)])
+        y.backward(dy)
+        res[mode] = (y.detach(), x.grad, {k: p.grad.clone() for k, p in m.named_parameters() if p.grad is not None})
+    K.set_precision("bf16")
+    assert relerr(res["bf16"][0], res["fp32"][0]) < TOL_BF16
+    assert relerr(res["bf16"][1], res["fp32"][1]) < TOL_BF16
+    for k, ref in res["fp32"][2].items():
+        tol = 5e-2 if k.endswith("freq") else TOL_BF16  # freq: cancelling sum over all rows and features
+        assert relerr(res["bf16"][2][k], ref) < tol, k
