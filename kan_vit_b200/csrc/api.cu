@@ -423,7 +423,8 @@ int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, co
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
   if ((d->flags & KV_FLAG_BF16_TC) && wtiles_t_bf16 != nullptr && dy_image != nullptr)
-    return tc_bwd_input(tc_view(*d), X, dY, act_mask, dy_image, wtiles_t_bf16, fparams, dX, (cudaStream_t)stream);
+    return tc_bwd_input(tc_view(*d), X, dY, act_mask, dy_image, wtiles_t_bf16, fparams, mean, rstd, dX, dXn, dfparams,
+                        (cudaStream_t)stream);
   if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;
   return simt_bwd_input(*d, X, dY, act_mask, wp_f32, fparams, mean, rstd, dX, dXn, dfparams,
                         (cudaStream_t)stream);

@@ -275,8 +275,10 @@ attn_tc_bwd_kernel(const float* __restrict__ qkv, const float* __restrict__ dout
     stage_rows<DHP>(otile, 1, dout + (size_t)b * N * (size_t)(H * dh) + (size_t)h * dh, (size_t)H * dh, N, Np, dh,
                     tid, blockDim.x);
   }
-  for (int i = tid; i < Np; i += blockDim.x)
+  for (int i = tid; i < Np; i += blockDim.x) {
     Ls[i] = (i < N) ? lse[((size_t)b * H + h) * N + i] * LOG2E : INFINITY;
+    Ds[i] = 0.0f;  // rows beyond the last 16-row block are never written by the row pass (0 * garbage must stay 0)
+  }
   __syncthreads();
   const float scale = rsqrtf((float)dh);
   const float sl2 = scale * LOG2E;

@@ -32,7 +32,8 @@ int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const flo
 size_t tc_dy_image_bytes(const kv_kan_desc_t& d);  // bf16 copy of dY shared by the gradient kernels (0 = n/a)
 int tc_dy_image(const kv_kan_desc_t& d, const float* dY, const float* act_mask, void* image, cudaStream_t st);
 int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const float* act_mask, const void* dy_image,
-                 const void* wtiles_t, const float* fparams, float* dX, cudaStream_t st);
+                 const void* wtiles_t, const float* fparams, const float* mean, const float* rstd, float* dX,
+                 float* dXn, float* dfparams, cudaStream_t st);
 int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, const float* fparams,
                   const float* mean, const float* rstd, float* dWp, cudaStream_t st);
 

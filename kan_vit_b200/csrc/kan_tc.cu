@@ -846,7 +846,7 @@ __global__ void dy_image_kernel(const kv_kan_desc_t d, const float* __restrict__
 // One thread = one core matrix: 8 columns (the 8 B-spline coefficients of one feature, or 8 features of the
 // SiLU branch) x 8 outputs, read as 8 x 32 contiguous bytes and written as 128 contiguous bytes.
 __global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, const uint64_t* __restrict__ tbl,
-                                 __nv_bfloat16* __restrict__ wtt, BwdGeom b) {
+                                 __nv_bfloat16* __restrict__ wtt, BwdGeom b, int layout) {
   const int half = b.SW / 2;
   const int xs = d.n_groups == d0.n_groups ? 1 : d0.x_share;
   const size_t total64 = (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * b.n_sub * half;  // core matrices
@@ -869,7 +869,7 @@ __global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, 
     for (int oe = 0; oe < 8; ++oe) {
       const int o = st * 64 + o8 * 8 + oe;
       if (o < d.out_features && c < b.n_chunks) {
-        load_w8(d0, tbl, g * xs + o / d0.out_features, o % d0.out_features, LAYOUT_EFFKAN8, c, q, h, v[oe]);
+        load_w8(d0, tbl, g * xs + o / d0.out_features, o % d0.out_features, layout, c, q, h, v[oe]);
       } else {
 #pragma unroll
         for (int e = 0; e < 8; ++e) v[oe][e] = 0.0f;
@@ -893,6 +893,11 @@ struct BwdInParams {
   const float* fparams;
   float* dX;
   BwdGeom b;
+  // generic kernel only
+  const float* mean;
+  const float* rstd;
+  float* dXn;
+  float* dfparams;
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8_bwd_input_kernel(const BwdInParams p) {
@@ -1074,6 +1079,226 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
     ptx::tmem_dealloc2(tmem_base, TMEM_COLS);
   }
 }
+
+
+// S values staged in shared memory, element m at s[m * stride]
+struct StridedDotSink {
+  static constexpr bool kDense = false;
+  const float* s;
+  int stride;
+  float acc;
+  __device__ __forceinline__ void put(int m, float v) { acc = fmaf(v, s[m * stride], acc); }
+};
+struct StridedFastkanDotSink {  // RBF part (m < G) and SiLU part (m == G) kept apart (LayerNorm backward needs the first)
+  static constexpr bool kDense = false;
+  const float* s;
+  int stride, G;
+  float acc_rbf, acc_base;
+  __device__ __forceinline__ void put(int m, float v) {
+    if (m < G) acc_rbf = fmaf(v, s[m * stride], acc_rbf); else acc_base = fmaf(v, s[m * stride], acc_base);
+  }
+};
+
+template <int F>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_bwd_input_generic_kernel(const BwdInParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + BI_STAGES * BI_A_STAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BI_STAGES * (BI_A_STAGE + BI_B_STAGE));
+  const uint32_t bar0 = ptx::smem_u32(bars);
+  auto full = [&](int s) { return bar0 + 8u * s; };
+  auto empty = [&](int s) { return bar0 + 8u * (BI_STAGES + s); };
+  const uint32_t tmem_full = bar0 + 8u * (2 * BI_STAGES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * BI_STAGES + 1);
+
+  const kv_kan_desc_t& d = p.d;
+  const BwdGeom b = p.b;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const int tile = blockIdx.y % b.n_tiles;
+  const int m_tile = (blockIdx.y / b.n_tiles) * 2 + (int)rank;
+  const int g = blockIdx.z;
+  const int t0 = m_tile * BM;
+  const int SW = b.SW, n_sub = b.n_sub;
+  const uint32_t b_stage_bytes = (uint32_t)n_sub * SW * 64;  // this CTA's half: n_sub * SW/2 rows * 64 * 2 B
+
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < BI_STAGES; ++s) {
+      ptx::mbar_init(full(s), rank == 0 ? 2 : 1);
+      ptx::mbar_init(empty(s), 1);
+    }
+    ptx::mbar_init(tmem_full, 1);
+    ptx::fence_mbar_init();
+  }
+  float* dfreq_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);  // SineKAN: d freq of this CTA
+  if (warp == 2) dfreq_s[lane] = 0.0f;
+  if (warp == 0) {
+    ptx::tmem_alloc2(ptx::smem_u32(tmem_slot), TMEM_COLS);
+    ptx::tmem_relinquish2();
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync_all();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---- loader: per stage 16 x 1 KB of the dY image (this CTA's 128 rows) + one copy of the weight image
+      const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.dyimg) +
+                            ((size_t)g * b.T8 + (size_t)m_tile * 16) * b.O8 * 128;
+      const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.wtt) +
+                            (((size_t)g * b.n_tiles + tile) * b.n_stages * 2 + rank) * (size_t)b_stage_bytes;
+      int s = 0;
+      uint32_t ph = 1;
+      for (int st = 0; st < b.n_stages; ++st) {
+        ptx::mbar_wait(empty(s), ph);
+        ptx::mbar_arrive_expect_tx(full(s), BI_A_STAGE + b_stage_bytes);
+        const uint32_t adst = ptx::smem_u32(sA) + s * BI_A_STAGE;
+#pragma unroll 4
+        for (int t8 = 0; t8 < 16; ++t8)
+          ptx::bulk_g2s(adst + t8 * 1024, asrc + ((size_t)t8 * b.O8 + (size_t)st * 8) * 128, 1024, full(s));
+        ptx::bulk_g2s(ptx::smem_u32(sB) + s * BI_B_STAGE, bsrc + (size_t)st * 2 * b_stage_bytes, b_stage_bytes,
+                      full(s));
+        if (++s == BI_STAGES) { s = 0; ph ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (rank == 0) {
+      // ---- MMA issuer: S[256 rows, n_sub x SW] += dY[256, 16] . Wt[SW, 16]^T
+      const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, SW);
+      const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), 128, 1024);
+      const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)SW * 8, 128);
+      const uint32_t b_sub_step = (uint32_t)(SW * 64) >> 4;    // next sub-MMA's rows
+      const uint32_t b_k_step = (uint32_t)(2 * SW * 8) >> 4;   // next K=16 step: two 8-wide core columns
+      int s = 0;
+      uint32_t ph = 0;
+      for (int st = 0; st < b.n_stages; ++st) {
+        if (!(d.reserved & 256)) ptx::mbar_wait(full(s), ph);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          const uint64_t da = da0 + (uint64_t)((s * BI_A_STAGE) >> 4);
+          const uint64_t db = db0 + (uint64_t)((s * BI_B_STAGE) >> 4);
+#pragma unroll
+          for (int ks = 0; ks < BI_KS; ++ks) {
+            for (int j = 0; j < ((d.reserved & 1024) ? 1 : n_sub); ++j)
+              ptx::mma2_bf16_ss(tmem_base + j * SW, da + (uint64_t)(ks * 16), db + (uint64_t)(j * b_sub_step + ks * b_k_step),
+                                idesc, (st | ks) > 0);
+          }
+          ptx::tc_commit2(empty(s));
+          if (st + 1 == b.n_stages) ptx::tc_commit2(tmem_full);
+        }
+        __syncwarp();
+        if (++s == BI_STAGES) { s = 0; ph ^= 1; }
+      }
+    } else if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int st = 0; st < b.n_stages; ++st) {
+        ptx::mbar_wait(full(s), ph);
+        ptx::mbar_arrive_cluster(ptx::mapa(full(s), 0));
+        if (++s == BI_STAGES) { s = 0; ph ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---- epilogue (any family): dX[t, i] = sum_m Phi'_m(x[t,i]) * S[t, (i, m)], basis-major columns m * 16 + f.
+    // The S values of one chunk go through shared memory (the operand rings are idle by now), laid out
+    // [m][f][thread] so that the family's derivative routine can index them by m.
+    const int pw = warp - 2;
+    const int q4 = warp & 3, half = pw >> 2;
+    const int etid = pw * 32 + lane;
+    const int te = t0 + q4 * 32 + lane;
+    const bool row_ok = te < d.T;
+    const int in = d.in_features, M = d.M;
+    const BasisCtx c = make_ctx(d, p.fparams, g);
+    const int xoff = g * in;  // x_share == 1: group g reads its own slice
+    const float* xrow = p.X + (size_t)(row_ok ? te : 0) * d.ldx + xoff;
+    float* dxrow = p.dX + (size_t)(row_ok ? te : 0) * d.ldx + xoff;
+    const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(p.dX) & 15) == 0);
+    float mu = 0.f, rs = 1.f;
+    const bool ln = (F == KV_FASTKAN) && !(d.flags & KV_FLAG_NO_LAYERNORM);
+    if (ln && row_ok) {
+      mu = p.mean[(size_t)te * d.n_groups + g];
+      rs = p.rstd[(size_t)te * d.n_groups + g];
+    }
+    float* scratch = reinterpret_cast<float*>(smem);
+    constexpr int MS = 8 * 256;  // scratch stride between consecutive m
+    ptx::mbar_wait(tmem_full, 0);
+    ptx::tc_fence_after();
+    const uint32_t trow = tmem_base + ((uint32_t)(q4 * 32) << 16);
+    for (int j = 0; j < n_sub; ++j) {
+      const int cch = tile * n_sub + j;
+      if (cch >= b.n_chunks) break;  // warp-uniform
+      float x8[8];
+      load_x8(xrow, cch * KU + half * 8, in, row_ok, vec, x8);
+      for (int m = 0; m < M; ++m) {
+        uint32_t r8[8];
+        ptx::tmem_ld8(trow + j * SW + m * 16 + half * 8, r8);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int f = 0; f < 8; ++f) scratch[m * MS + f * 256 + etid] = __uint_as_float(r8[f]);
+      }
+      float dx[8];
+#pragma unroll
+      for (int f = 0; f < 8; ++f) {
+        const int i = cch * KU + half * 8 + f;
+        const int ic = min(i, in - 1);
+        const bool live = row_ok && i < in;
+        const float xv = x8[f];
+        const float* srow = scratch + f * 256 + etid;
+        float acc = 0.0f;
+        if (F == KV_SINE) {
+          const float* freq = c.fp;
+          const float* ph = c.fp + c.G + (size_t)ic * c.G;
+          for (int q = 0; q < c.G; ++q) {
+            const float cs = cosf(fmaf(xv, freq[q], ph[q]));
+            const float sv = srow[q * MS];
+            acc = fmaf(freq[q] * cs, sv, acc);
+            float contrib = live ? xv * cs * sv : 0.0f;  // d freq_q (models/sinekan.py:87), reduced over the CTA
+            contrib = warp_sum(contrib);
+            if (lane == 0) atomicAdd(&dfreq_s[q], contrib);
+          }
+        } else if (F == KV_FASTKAN) {
+          const float xn = fastkan_xn(c, ic, xv, mu, rs);
+          StridedFastkanDotSink sk{srow, MS, c.G, 0.0f, 0.0f};
+          basis_deriv<F>(c, ic, xv, xn, sk);
+          acc = sk.acc_base;
+          if (!ln) acc += sk.acc_rbf;
+          else if (live) p.dXn[(size_t)te * ((size_t)d.n_groups * in) + (size_t)g * in + i] = sk.acc_rbf;
+        } else {
+          StridedDotSink sk{srow, MS, 0.0f};
+          basis_deriv<F>(c, ic, xv, xv, sk);
+          acc = sk.acc;
+        }
+        dx[f] = acc;
+      }
+      if (row_ok) {
+        const int i0 = cch * KU + half * 8;
+        if (vec && i0 + 8 <= in) {
+          *reinterpret_cast<float4*>(dxrow + i0) = make_float4(dx[0], dx[1], dx[2], dx[3]);
+          *reinterpret_cast<float4*>(dxrow + i0 + 4) = make_float4(dx[4], dx[5], dx[6], dx[7]);
+        } else {
+#pragma unroll
+          for (int f = 0; f < 8; ++f)
+            if (i0 + f < in) dxrow[i0 + f] = dx[f];
+        }
+      }
+    }
+    if (F == KV_SINE && p.dfparams != nullptr) {
+      asm volatile("bar.sync 1, 256;" ::: "memory");  // the eight epilogue warps
+      if (etid < c.G) atomicAdd(&p.dfparams[(size_t)g * d.fparam_stride + etid], dfreq_s[etid]);
+    }
+    ptx::tc_fence_before();
+  }
+  ptx::cluster_sync_all();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc2(tmem_base, TMEM_COLS);
+  }
+}
+
 
 
 // =========================================================================================
@@ -1410,14 +1635,16 @@ static bool tc_bwd_linear(const kv_kan_desc_t& d) {
   return d.family == KV_LINEAR && d.x_share == 1 && d.rows_in == 0 && (d.ldx % 4) == 0 && (d.ldy % 4) == 0 &&
          d.in_features % 4 == 0 && d.out_features % 4 == 0;
 }
-static bool tc_bwd_ok(const kv_kan_desc_t& d) {  // input-gradient kernel available
-  return (tc::make_geom(d).effkan8 && d.x_share == 1 && d.M == 9) || tc_bwd_linear(d);
+static bool tc_bwd_effkan8(const kv_kan_desc_t& d) { return tc::make_geom(d).effkan8 && d.x_share == 1 && d.M == 9; }
+// any basis family through the generic kernels (basis-major columns / octet x basis tiles), one group per slice
+static bool tc_bwd_generic(const kv_kan_desc_t& d) {
+  return d.family != KV_LINEAR && !tc_bwd_effkan8(d) && d.x_share == 1 && d.M <= tc::MAX_M_TC;
 }
-// weight-gradient kernel: every family (generic basis tiles), one group per slice
-static bool tc_bwd_w_ok(const kv_kan_desc_t& d) {
-  if (tc_bwd_ok(d)) return true;
-  return d.family != KV_LINEAR && d.x_share == 1 && d.M <= tc::MAX_M_TC;
+// input-gradient kernel: one chunk (16 features x M bases) is one MMA of N = 16 M <= 256 columns
+static bool tc_bwd_ok(const kv_kan_desc_t& d) {
+  return tc_bwd_effkan8(d) || tc_bwd_linear(d) || (tc_bwd_generic(d) && d.M <= 16);
 }
+static bool tc_bwd_w_ok(const kv_kan_desc_t& d) { return tc_bwd_effkan8(d) || tc_bwd_linear(d) || tc_bwd_generic(d); }
 // Linear: dX = dY . W runs as the forward kernel of the transposed layer
 static kv_kan_desc_t linear_transposed(const kv_kan_desc_t& d) {
   kv_kan_desc_t t = d;
@@ -1469,7 +1696,8 @@ int tc_pack(const kv_kan_desc_t& d, const kv_kan_desc_t& d0, const uint64_t* ptr
     if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
     const tc::BwdGeom b = tc::make_bwd_geom(d);
     const size_t total = tc_wtiles_t_bytes(d) / 128;
-    tc::tc_pack_t_kernel<<<grid_for(total, 128), 128, 0, st>>>(d, d0, ptr_table, reinterpret_cast<__nv_bfloat16*>(wtiles_t), b);
+    tc::tc_pack_t_kernel<<<grid_for(total, 128), 128, 0, st>>>(d, d0, ptr_table, reinterpret_cast<__nv_bfloat16*>(wtiles_t), b,
+                                                               tc_bwd_effkan8(d) ? tc::LAYOUT_EFFKAN8 : tc::LAYOUT_BASIS_MAJOR);
     KV_CHECK_LAUNCH("tc_pack_t_kernel");
   }
   return KV_OK;
@@ -1512,8 +1740,22 @@ int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const flo
   return KV_ERR_BAD_FAMILY;
 }
 
+template <int F>
+static int launch_bwd_input_generic(const tc::BwdInParams& p, dim3 grid, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    KV_CUDA(cudaFuncSetAttribute(tc::kan_tc_bwd_input_generic_kernel<F>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 tc::BI_SMEM), "tc_bwd_input smem attribute");
+    attr_set = true;
+  }
+  tc::kan_tc_bwd_input_generic_kernel<F><<<grid, tc::NTHREADS, tc::BI_SMEM, st>>>(p);
+  KV_CHECK_LAUNCH("kan_tc_bwd_input_generic_kernel");
+  return KV_OK;
+}
+
 int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const float* act_mask, const void* dy_image,
-                 const void* wtiles_t, const float* fparams, float* dX, cudaStream_t st) {
+                 const void* wtiles_t, const float* fparams, const float* mean, const float* rstd, float* dX,
+                 float* dXn, float* dfparams, cudaStream_t st) {
   if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
   if (d.family == KV_LINEAR) {
     tc::FwdParams q;
@@ -1540,10 +1782,24 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
   p.wtt = reinterpret_cast<const __nv_bfloat16*>(wtiles_t);
   p.fparams = fparams;
   p.dX = dX;
+  p.mean = mean;
+  p.rstd = rstd;
+  p.dXn = dXn;
+  p.dfparams = dfparams;
   p.b = tc::make_bwd_geom(d);
   const int n_pairs = ceil_div(d.T, 2 * tc::BM);
   if ((long long)n_pairs * p.b.n_tiles > 65535 || d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
   dim3 grid(2, n_pairs * p.b.n_tiles, d.n_groups);
+  if (tc_bwd_generic(d)) {
+    switch (d.family) {
+      case KV_EFFKAN: return launch_bwd_input_generic<KV_EFFKAN>(p, grid, st);
+      case KV_CHEBY: return launch_bwd_input_generic<KV_CHEBY>(p, grid, st);
+      case KV_FASTKAN: return launch_bwd_input_generic<KV_FASTKAN>(p, grid, st);
+      case KV_SINE: return launch_bwd_input_generic<KV_SINE>(p, grid, st);
+      case KV_FOURIER: return launch_bwd_input_generic<KV_FOURIER>(p, grid, st);
+    }
+    return KV_ERR_BAD_FAMILY;
+  }
   tc::effkan8_bwd_input_kernel<<<grid, tc::NTHREADS, tc::BI_SMEM, st>>>(p);
   KV_CHECK_LAUNCH("effkan8_bwd_input_kernel");
   return KV_OK;
@@ -1577,7 +1833,7 @@ int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, 
   // (SiLU column); Linear = one per 128 features
   p.mean = mean;
   p.rstd = rstd;
-  p.generic = tc_bwd_ok(d) ? 0 : 1;
+  p.generic = tc_bwd_generic(d) ? 1 : 0;
   p.no = 1;
   p.tpo = 1;
   if (p.generic) {
