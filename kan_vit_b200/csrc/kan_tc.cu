@@ -1212,7 +1212,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     const bool row_ok = te < d.T;
     const int in = d.in_features, M = d.M;
     const BasisCtx c = make_ctx(d, p.fparams, g);
-    const int xoff = g * in;  // x_share == 1: group g reads its own slice
+    const int n_slices = d.n_groups / d.x_share, slice = g / d.x_share;
+    const int xoff = slice * in;
+    const bool shared_slice = d.x_share > 1;  // several groups add into the same dX columns (zeroed by the host)
     const float* xrow = p.X + (size_t)(row_ok ? te : 0) * d.ldx + xoff;
     float* dxrow = p.dX + (size_t)(row_ok ? te : 0) * d.ldx + xoff;
     const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0) &&
@@ -1220,8 +1222,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     float mu = 0.f, rs = 1.f;
     const bool ln = (F == KV_FASTKAN) && !(d.flags & KV_FLAG_NO_LAYERNORM);
     if (ln && row_ok) {
-      mu = p.mean[(size_t)te * d.n_groups + g];
-      rs = p.rstd[(size_t)te * d.n_groups + g];
+      mu = p.mean[(size_t)te * n_slices + slice];
+      rs = p.rstd[(size_t)te * n_slices + slice];
     }
     float* scratch = reinterpret_cast<float*>(smem);
     constexpr int MS = 8 * 256;  // scratch stride between consecutive m
@@ -1274,7 +1276,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         }
         dx[f] = acc;
       }
-      if (row_ok) {
+      if (row_ok && shared_slice) {
+        const int i0 = cch * KU + half * 8;
+#pragma unroll
+        for (int f = 0; f < 8; ++f)
+          if (i0 + f < in) atomicAdd(dxrow + i0 + f, dx[f]);
+      } else if (row_ok) {
         const int i0 = cch * KU + half * 8;
         if (vec && i0 + 8 <= in) {
           *reinterpret_cast<float4*>(dxrow + i0) = make_float4(dx[0], dx[1], dx[2], dx[3]);
@@ -1637,8 +1644,9 @@ static bool tc_bwd_linear(const kv_kan_desc_t& d) {
 }
 static bool tc_bwd_effkan8(const kv_kan_desc_t& d) { return tc::make_geom(d).effkan8 && d.x_share == 1 && d.M == 9; }
 // any basis family through the generic kernels (basis-major columns / octet x basis tiles), one group per slice
+// (groups that share an input slice -- q/k/v maps with per-module prologue parameters -- add their dX with fp32 RED)
 static bool tc_bwd_generic(const kv_kan_desc_t& d) {
-  return d.family != KV_LINEAR && !tc_bwd_effkan8(d) && d.x_share == 1 && d.M <= tc::MAX_M_TC;
+  return d.family != KV_LINEAR && !tc_bwd_effkan8(d) && d.M <= tc::MAX_M_TC;
 }
 // input-gradient kernel: one chunk (16 features x M bases) is one MMA of N = 16 M <= 256 columns
 static bool tc_bwd_ok(const kv_kan_desc_t& d) {
@@ -1791,6 +1799,10 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
   if ((long long)n_pairs * p.b.n_tiles > 65535 || d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
   dim3 grid(2, n_pairs * p.b.n_tiles, d.n_groups);
   if (tc_bwd_generic(d)) {
+    if (d.x_share > 1)
+      KV_CUDA(cudaMemset2DAsync(dX, (size_t)d.ldx * sizeof(float), 0,
+                                (size_t)(d.n_groups / d.x_share) * d.in_features * sizeof(float), (size_t)d.T, st),
+              "tc_bwd_input zero dX");
     switch (d.family) {
       case KV_EFFKAN: return launch_bwd_input_generic<KV_EFFKAN>(p, grid, st);
       case KV_CHEBY: return launch_bwd_input_generic<KV_CHEBY>(p, grid, st);

@@ -333,3 +333,38 @@ def test_bf16_family_gradients_vs_own_fp32(name, T, i, o):
     for k, ref in res["fp32"][2].items():
         tol = 5e-2 if k.endswith("freq") else TOL_BF16  # freq: cancelling sum over all rows and features
         assert relerr(res["bf16"][2][k], ref) < tol, k
+
+
+@pytest.mark.parametrize("name", ["fastkan", "sine", "cheby", "fourier"])
+@pytest.mark.parametrize("T,H,dh", [(394, 8, 24), (300, 2, 32)])
+def test_bf16_grouped_qkv_families_vs_own_fp32(name, T, H, dh):
+    """Per-head q/k/v maps of the other families: ChebyKAN / Fourier merge per head; FastKAN / SineKAN keep their
+    per-module prologue parameters, so the three groups of a slice add their input gradients with fp32 RED."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(8)
+    mods = [_family_layer(name, dh, dh).to(_dev()) for _ in range(3 * H)]
+    spec = make_spec(mods, x_share=3)
+    x0 = torch.randn(T, H * dh, device=_dev())
+    dy = torch.randn(T, 3 * H * dh, device=_dev())
+
+    def run(mode):
+        K.set_precision(mode)
+        for m in mods:
+            m.zero_grad(set_to_none=True)
+        x = x0.clone().requires_grad_(True)
+        y = ops.kan_apply(x, spec, [slots_of(m) for m in mods])
+        y.backward(dy)
+        return y.detach(), x.grad, [{k: p.grad.clone() for k, p in m.named_parameters() if p.grad is not None}
+                                    for m in mods]
+
+    y16, gx16, gp16 = run("bf16")
+    y32, gx32, gp32 = run("fp32")
+    K.set_precision("bf16")
+    assert relerr(y16, y32) < TOL_BF16
+    assert relerr(gx16, gx32) < TOL_BF16
+    for a, b in zip(gp16, gp32):
+        for k in b:
+            tol = 5e-2 if k.endswith("freq") else TOL_BF16
+            assert relerr(a[k], b[k]) < tol, k
