@@ -1518,6 +1518,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       const int t = row0 + st * 64 + tl;
       const bool row_ok = t < row1;
       const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
+      {
+        // the tile reads a 64-byte (spline) or 512-byte (SiLU / Linear) stripe of every row: a latency-bound
+        // gather.  Pull the stripe of a later stage into L2 now so that its load finds it there.
+        constexpr int PF = 8;
+        const int tp = t + PF * 64;
+        if (tile_live && tp < row1) {
+          const float* pf = p.X + (size_t)tp * d.ldx + xoff + (spline_tile ? feat0 + 4 * fb : feat0 + 32 * fb);
+          if ((spline_tile ? feat0 + 4 * fb : feat0 + 32 * fb) < in) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+        }
+      }
       float xv[32];
       if (tile_live) {
         if (spline_tile) {
