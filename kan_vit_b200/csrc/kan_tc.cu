@@ -1023,6 +1023,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
     ptx::mbar_wait(tmem_full, 0);
     ptx::tc_fence_after();
     const uint32_t trow = tmem_base + ((uint32_t)(q4 * 32) << 16);
+    constexpr bool kSmemWindow = true;
+    float* win = reinterpret_cast<float*>(sA) + (pw * 32 + lane);  // [14][256] floats; the operand rings are idle now
+    if (kSmemWindow) {
+      win[0] = win[256] = win[512] = 0.0f;
+      win[11 * 256] = win[12 * 256] = win[13 * 256] = 0.0f;
+    }
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
       const int c = tile * n_sub + j;
@@ -1048,12 +1054,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
         const float w2 = ok ? (-1.5f * s2 + s + 0.5f) * ginv_h : 0.0f;
         const float w3 = ok ? 0.5f * s2 * ginv_h : 0.0f;
         float acc = 0.0f;
+        if (kSmemWindow) {
+          // the 8 spline sums go into this thread's zero-padded window [3, 11) and the four that meet the
+          // non-zero derivative pieces are read back at j3 + 3 .. j3 + 6: 12 conflict-free shared-memory
+          // accesses instead of a 32-way select network
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          // coefficient of spline e: piece e - j3 of the derivative (branch-free selects)
-          const float coef = sel_eq(j3, e, w0, sel_eq(j3, e - 1, w1, sel_eq(j3, e - 2, w2, sel_eq(j3, e - 3, w3, 0.0f))));
-          const uint32_t sv = (f < 4) ? sa[f * 8 + e] : sb2[(f - 4) * 8 + e];
-          acc = fmaf(coef, __uint_as_float(sv), acc);
+          for (int e = 0; e < 8; ++e)
+            win[(3 + e) * 256] = __uint_as_float((f < 4) ? sa[f * 8 + e] : sb2[(f - 4) * 8 + e]);
+          const int jc = min(max(j3, -3), 7) + 3;
+          const float* wp = win + jc * 256;
+          acc = fmaf(w0, wp[0], fmaf(w1, wp[256], fmaf(w2, wp[512], w3 * wp[768])));
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            // coefficient of spline e: piece e - j3 of the derivative (branch-free selects)
+            const float coef = sel_eq(j3, e, w0, sel_eq(j3, e - 1, w1, sel_eq(j3, e - 2, w2, sel_eq(j3, e - 3, w3, 0.0f))));
+            const uint32_t sv = (f < 4) ? sa[f * 8 + e] : sb2[(f - 4) * 8 + e];
+            acc = fmaf(coef, __uint_as_float(sv), acc);
+          }
         }
         const float sg = __fdividef(1.0f, 1.0f + __expf(-xv));
         acc = fmaf(sg * (1.0f + xv * (1.0f - sg)), __uint_as_float(sbase[f]), acc);

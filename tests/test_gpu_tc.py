@@ -368,3 +368,30 @@ def test_bf16_grouped_qkv_families_vs_own_fp32(name, T, H, dh):
         for k in b:
             tol = 5e-2 if k.endswith("freq") else TOL_BF16
             assert relerr(a[k], b[k]) < tol, k
+
+
+def test_bf16_full_size_row_independence_cfg4():
+    """BASELINE config 4's MLP layer at the bench's full size (T = 197 * 256 token rows, 768 -> 3072, bf16): every
+    row is computed independently of the others, so the first rows of the full batch must equal, bit for bit, the
+    same rows run alone -- forward and input gradient (size-independent property; the oracle cannot run this size)."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(9)
+    T, i, o, n = 197 * 256, 768, 3072, 300
+    m = K.KANLinear(i, o).to(_dev())
+    spec = make_spec([m])
+    x_full = torch.randn(T, i, device=_dev())
+    dy_full = torch.randn(T, o, device=_dev())
+
+    def run(x0, dy):
+        x = x0.clone().requires_grad_(True)
+        y = ops.kan_apply(x, spec, [slots_of(m)])
+        y.backward(dy)
+        return y.detach(), x.grad
+
+    y_a, g_a = run(x_full, dy_full)
+    y_b, g_b = run(x_full[:n].contiguous(), dy_full[:n].contiguous())
+    assert torch.equal(y_a[:n], y_b)
+    assert torch.equal(g_a[:n], g_b)
+    assert torch.isfinite(y_a).all() and torch.isfinite(g_a).all()

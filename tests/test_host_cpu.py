@@ -104,3 +104,42 @@ def test_reference_quirks_kept():
     v = K.VisionTransformer((1, 28, 28))
     assert "pos_embeddings" not in v.state_dict()
     K.MSA(16, 2, type="bogus")  # the reference swallows the error at construction (attention.py:174-176)
+
+
+def test_tensor_core_coverage_table():
+    """Which layers the bf16 mode serves with tensor-core kernels (kv_kan_tc_bytes is a pure host query):
+    forward for M <= 24, weight gradient for every family, input gradient for M <= 16 and nn.Linear."""
+    import ctypes as C
+    from kan_vit_b200 import _lib as L
+    from kan_vit_b200.ops import KanSpec
+    lib = L.load()
+
+    def sizes(spec, T=1000, flags=0):
+        n_in = spec.n_slices * spec.in_features
+        d = spec.desc(T, n_in, spec.n_groups * spec.out_features, extra_flags=L.KV_FLAG_BF16_TC | flags)
+        a, b, c = C.c_size_t(0), C.c_size_t(0), C.c_size_t(0)
+        rc = lib.kv_kan_tc_bytes(C.byref(d), C.byref(a), C.byref(b), C.byref(c))
+        return rc, a.value, b.value, c.value
+
+    dense = {
+        "effkan": KanSpec(L.KV_EFFKAN, 768, 3072, grid_size=5, spline_order=3),
+        "cheby": KanSpec(L.KV_CHEBY, 64, 64, grid_size=4),
+        "fastkan": KanSpec(L.KV_FASTKAN, 192, 192, grid_size=8),
+        "sine": KanSpec(L.KV_SINE, 192, 192, grid_size=5),
+        "fourier": KanSpec(L.KV_FOURIER, 64, 64, grid_size=5),
+        "linear": KanSpec(L.KV_LINEAR, 768, 3072),
+    }
+    for name, spec in dense.items():
+        rc, fwd, bwd_in, dyimg = sizes(spec, flags=L.KV_FLAG_UNIFORM_GRID if name == "effkan" else 0)
+        assert rc == 0 and fwd > 0 and bwd_in > 0 and dyimg > 0, name
+    # more than 16 basis functions: weight gradient yes, input gradient on the exact kernels
+    rc, fwd, bwd_in, dyimg = sizes(KanSpec(L.KV_SINE, 192, 192, grid_size=20))
+    assert rc == 0 and fwd > 0 and bwd_in == 0 and dyimg > 0
+    # more than 24: no tensor-core kernel at all
+    assert sizes(KanSpec(L.KV_SINE, 192, 192, grid_size=28))[0] == L.KV_ERR_UNSUPPORTED
+    # per-head q/k/v maps: merged (effkan on a uniform grid) or served as groups sharing a slice (fastkan)
+    for spec, fl in ((KanSpec(L.KV_EFFKAN, 64, 64, n_groups=36, x_share=3, grid_size=5, spline_order=3),
+                      L.KV_FLAG_UNIFORM_GRID),
+                     (KanSpec(L.KV_FASTKAN, 24, 24, n_groups=24, x_share=3, grid_size=8), 0)):
+        rc, fwd, bwd_in, dyimg = sizes(spec, flags=fl)
+        assert rc == 0 and fwd > 0 and bwd_in > 0 and dyimg > 0
