@@ -15,6 +15,7 @@
 //
 // Warp roles (320 threads): warp 0 = TMEM allocator + B loader, warp 1 = barrier init + MMA issuer,
 //   warps 2..9 = A producers (basis prologue), then epilogue.
+#include <cstdlib>
 #include "basis.cuh"
 #include "internal.cuh"
 #include "tc_ptx.cuh"
@@ -781,6 +782,7 @@ constexpr int BI_A_STAGE = BM * BI_KS * KU * 2;  // 16 KB
 constexpr int BI_B_STAGE = 32 * 1024;          // >= n_sub * SW * 64 bytes
 constexpr int BI_STAGES = 4;
 constexpr int BI_SMEM = BI_STAGES * (BI_A_STAGE + BI_B_STAGE) + BAR_BYTES;
+constexpr int BI_SMEM_E8 = BI_SMEM + 14 * 256 * 4;  // + the epilogue's window scratch (default-effkan kernel)
 
 struct BwdGeom {
   int SW;        // columns (= B rows) per sub-MMA: one chunk = 16 * M
@@ -898,6 +900,7 @@ struct BwdInParams {
   const float* rstd;
   float* dXn;
   float* dfparams;
+  int tpc;  // effkan8 kernel: column tiles per CTA pair
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8_bwd_input_kernel(const BwdInParams p) {
@@ -909,14 +912,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
   auto full = [&](int s) { return bar0 + 8u * s; };
   auto empty = [&](int s) { return bar0 + 8u * (BI_STAGES + s); };
   const uint32_t tmem_full = bar0 + 8u * (2 * BI_STAGES);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * BI_STAGES + 1);
+  const uint32_t tmem_empty = bar0 + 8u * (2 * BI_STAGES + 1);  // (leader) the 16 epilogue warps of the pair have drained TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * BI_STAGES + 2);
+  float* win_base = reinterpret_cast<float*>(smem + BI_STAGES * (BI_A_STAGE + BI_B_STAGE) + BAR_BYTES);  // [14][256]
 
   const kv_kan_desc_t& d = p.d;
   const BwdGeom b = p.b;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
-  const int tile = blockIdx.y % b.n_tiles;
-  const int m_tile = (blockIdx.y / b.n_tiles) * 2 + (int)rank;
+  // one CTA pair = one 256-row block x `tpc` consecutive column tiles (set-up, TMEM allocation and pipeline fill
+  // are paid once; the loader runs ahead into the next tile while the epilogue drains the accumulator)
+  const int n_tgroups = (b.n_tiles + p.tpc - 1) / p.tpc;
+  const int tile0 = (blockIdx.y % n_tgroups) * p.tpc;
+  const int tile1 = min(tile0 + p.tpc, b.n_tiles);
+  const int m_tile = (blockIdx.y / n_tgroups) * 2 + (int)rank;
   const int g = blockIdx.z;
   const int t0 = m_tile * BM;
   const int SW = b.SW, n_sub = b.n_sub;
@@ -928,6 +937,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
       ptx::mbar_init(empty(s), 1);
     }
     ptx::mbar_init(tmem_full, 1);
+    ptx::mbar_init(tmem_empty, 2 * N_PRODUCER_WARPS);
     ptx::fence_mbar_init();
   }
   if (warp == 0) {
@@ -944,10 +954,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
       // ---- loader: per stage 16 x 1 KB of the dY image (this CTA's 128 rows) + one copy of the weight image
       const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.dyimg) +
                             ((size_t)g * b.T8 + (size_t)m_tile * 16) * b.O8 * 128;
-      const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.wtt) +
-                            (((size_t)g * b.n_tiles + tile) * b.n_stages * 2 + rank) * (size_t)b_stage_bytes;
       int s = 0;
       uint32_t ph = 1;
+      for (int tile = tile0; tile < tile1; ++tile) {
+      const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.wtt) +
+                            (((size_t)g * b.n_tiles + tile) * b.n_stages * 2 + rank) * (size_t)b_stage_bytes;
       for (int st = 0; st < b.n_stages; ++st) {
         ptx::mbar_wait(empty(s), ph);
         ptx::mbar_arrive_expect_tx(full(s), BI_A_STAGE + b_stage_bytes);
@@ -958,6 +969,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
         ptx::bulk_g2s(ptx::smem_u32(sB) + s * BI_B_STAGE, bsrc + (size_t)st * 2 * b_stage_bytes, b_stage_bytes,
                       full(s));
         if (++s == BI_STAGES) { s = 0; ph ^= 1; }
+      }
       }
     }
     __syncwarp();
@@ -971,6 +983,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
       const uint32_t b_k_step = (uint32_t)(2 * SW * 8) >> 4;   // next K=16 step: two 8-wide core columns
       int s = 0;
       uint32_t ph = 0;
+      for (int tile = tile0; tile < tile1; ++tile) {
+      if (tile > tile0) {  // the accumulator of the previous tile must have been read out by both CTAs
+        ptx::mbar_wait_cluster(tmem_empty, (uint32_t)((tile - tile0 - 1) & 1));
+        ptx::tc_fence_after();
+      }
       for (int st = 0; st < b.n_stages; ++st) {
         if (!(d.reserved & 256)) ptx::mbar_wait(full(s), ph);
         ptx::tc_fence_after();
@@ -989,10 +1006,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
         __syncwarp();
         if (++s == BI_STAGES) { s = 0; ph ^= 1; }
       }
+      }
     } else if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      for (int st = 0; st < b.n_stages; ++st) {
+      for (int st = 0; st < b.n_stages * (tile1 - tile0); ++st) {
         ptx::mbar_wait(full(s), ph);
         ptx::mbar_arrive_cluster(ptx::mapa(full(s), 0));
         if (++s == BI_STAGES) { s = 0; ph ^= 1; }
@@ -1013,6 +1031,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
     float* dxrow = p.dX + (size_t)(row_ok ? te : 0) * d.ldx + xoff;
     const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0) &&
                      ((reinterpret_cast<uintptr_t>(p.dX) & 15) == 0);
+    float* win = win_base + (pw * 32 + lane);  // this thread's zero-padded window [14][256]
+    win[0] = win[256] = win[512] = 0.0f;
+    win[11 * 256] = win[12 * 256] = win[13 * 256] = 0.0f;
+    for (int tile = tile0; tile < tile1; ++tile) {
     // prefetch the inputs of every chunk of this tile while the MMAs run
     float xs[3][8];
 #pragma unroll
@@ -1020,15 +1042,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
       const int c = tile * n_sub + j;
       if (j < n_sub && c < b.n_chunks) load_x8(xrow, c * KU + half * 8, in, row_ok, vec, xs[j]);
     }
-    ptx::mbar_wait(tmem_full, 0);
+    ptx::mbar_wait(tmem_full, (uint32_t)((tile - tile0) & 1));
     ptx::tc_fence_after();
     const uint32_t trow = tmem_base + ((uint32_t)(q4 * 32) << 16);
     constexpr bool kSmemWindow = true;
-    float* win = reinterpret_cast<float*>(sA) + (pw * 32 + lane);  // [14][256] floats; the operand rings are idle now
-    if (kSmemWindow) {
-      win[0] = win[256] = win[512] = 0.0f;
-      win[11 * 256] = win[12 * 256] = win[13 * 256] = 0.0f;
-    }
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
       const int c = tile * n_sub + j;
@@ -1090,6 +1107,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
       }
     }
     ptx::tc_fence_before();
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tmem_empty, 0));  // this warp has drained its TMEM lanes
+    }
   }
   ptx::cluster_sync_all();
   if (warp == 0) {
@@ -1808,7 +1828,7 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
   static bool attr_set = false;
   if (!attr_set) {
     KV_CUDA(cudaFuncSetAttribute(tc::effkan8_bwd_input_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 tc::BI_SMEM), "tc_bwd_input smem attribute");
+                                 tc::BI_SMEM_E8), "tc_bwd_input smem attribute");
     attr_set = true;
   }
   tc::BwdInParams p;
@@ -1840,7 +1860,20 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
     }
     return KV_ERR_BAD_FAMILY;
   }
-  tc::effkan8_bwd_input_kernel<<<grid, tc::NTHREADS, tc::BI_SMEM, st>>>(p);
+  // column tiles per CTA pair: as many (up to 8) as still leave ~8 waves of CTA pairs
+  p.tpc = 1;
+  {
+    // measured at T = 50 432: 4 tiles per pair for 48-stage main loops (+4 %), 16 for 12-stage ones (+20 %)
+    int want = 192 / (p.b.n_stages > 0 ? p.b.n_stages : 1);
+    if (want < 4) want = 4;
+    if (const char* e = getenv("KV_TPC")) want = atoi(e);    // timing experiments only
+    for (int t = want > 16 ? 16 : want; t > 1; --t) {
+      const long long ctas = (long long)n_pairs * ((p.b.n_tiles + t - 1) / t) * d.n_groups;
+      if (ctas >= 74 * 8) { p.tpc = t; break; }
+    }
+  }
+  grid = dim3(2, n_pairs * ((p.b.n_tiles + p.tpc - 1) / p.tpc), d.n_groups);
+  tc::effkan8_bwd_input_kernel<<<grid, tc::NTHREADS, tc::BI_SMEM_E8, st>>>(p);
   KV_CHECK_LAUNCH("effkan8_bwd_input_kernel");
   return KV_OK;
 }
