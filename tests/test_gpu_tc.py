@@ -395,3 +395,28 @@ def test_bf16_full_size_row_independence_cfg4():
     assert torch.equal(y_a[:n], y_b)
     assert torch.equal(g_a[:n], g_b)
     assert torch.isfinite(y_a).all() and torch.isfinite(g_a).all()
+
+
+def test_bf16_input_gradient_persistent_tiles_ragged():
+    """Default-effkan input gradient with several column tiles per CTA pair where the tile count (21) is not a multiple
+    of the tiles-per-pair, the last chunk is partial (in = 1000) and the last row block is ragged."""
+    import kan_vit_b200 as K
+    from kan_vit_b200 import ops
+    from kan_vit_b200._dispatch import make_spec, slots_of
+    torch.manual_seed(10)
+    T, i, o = 26000 + 37, 1000, 640
+    m = K.KANLinear(i, o).to(_dev())
+    spec = make_spec([m])
+    x0 = torch.randn(T, i, device=_dev())
+    dy = torch.randn(T, o, device=_dev())
+    g = {}
+    for mode in ("bf16", "fp32"):
+        K.set_precision(mode)
+        x = x0.clone().requires_grad_(True)
+        ops.kan_apply(x, spec, [slots_of(m)]).backward(dy)
+        g[mode] = x.grad
+    K.set_precision("bf16")
+    assert relerr(g["bf16"], g["fp32"]) < TOL_BF16
+    # every row block / column tile was written: no stale zeros, no non-finite values
+    assert torch.isfinite(g["bf16"]).all()
+    assert (g["bf16"].abs().sum(dim=0) > 0).all() and (g["bf16"].abs().sum(dim=1) > 0).all()
