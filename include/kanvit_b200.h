@@ -237,6 +237,31 @@ int kv_cls_rows_bwd(const float* dtokens, float* dv_class, int B, int N, int d, 
 int kv_gather_rows(const float* X, float* Y, int B, int row_stride, int d, void* stream);
 int kv_scatter_rows(const float* dY, float* dX, int B, int row_stride, int d, void* stream);
 
+/* ---- the two ops either side of the path in every iteration ---- */
+
+/* nn.CrossEntropyLoss() of train.py:22,36 (class-index targets, mean reduction, ignore_index -100 by
+ * default): loss[0] = mean_i (logsumexp(z_i) - z_i[y_i]) over the rows with y_i != ignore_index, and, when
+ * dlogits is non-null, d loss / d logits = (softmax(z_i) - onehot(y_i)) / n_valid (zero rows for ignored
+ * labels) in the same pass.  logits [B][n_classes] fp32, labels [B] int64.  workspace: device floats,
+ * kv_cross_entropy_workspace_floats() of them, zeroed ONCE by the caller (the kernel leaves it zeroed);
+ * the block partials are added in block order, so the loss is bit-reproducible.  A label outside
+ * [0, n_classes) makes the loss NaN. */
+int kv_cross_entropy_workspace_floats(void);
+int kv_cross_entropy(const float* logits, const long long* labels, int B, int n_classes,
+                     long long ignore_index, float* loss, float* dlogits, float* workspace, void* stream);
+
+/* torch.optim.Adam(params, lr) of train.py:23,39-40 (betas/eps arguments, no weight decay, no amsgrad)
+ * over FLAT buffers holding every parameter of the model: one launch for the whole model instead of
+ * one per parameter tensor.
+ *   g = grad * grad_scale  (grad_scale = 1/world turns the all-reduced sum into the data-parallel mean)
+ *   m = b1 m + (1-b1) g;  v = b2 v + (1-b2) g^2;  p -= lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)
+ * n: elements, a multiple of 4, all four buffers 16-byte aligned.  zero_grad != 0 clears grad after it
+ * is read (the next iteration's zero_grad()).  state: 3 device doubles {t, lr/(1-b1^t), sqrt(1-b2^t)},
+ * zero-initialised by the caller; t is advanced on the device so a captured CUDA graph keeps counting. */
+int kv_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, long long n,
+                 float lr, float beta1, float beta2, float eps, float grad_scale, int zero_grad,
+                 double* state, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

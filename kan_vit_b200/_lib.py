@@ -65,6 +65,10 @@ _SIGNATURES = {
     "kv_cls_rows_bwd": [_P, _P, _I, _I, _I, _P],
     "kv_gather_rows": [_P, _P, _I, _I, _I, _P],
     "kv_scatter_rows": [_P, _P, _I, _I, _I, _P],
+    "kv_cross_entropy_workspace_floats": [],
+    "kv_cross_entropy": [_P, _P, _I, _I, C.c_longlong, _P, _P, _P, _P],
+    "kv_adam_step": [_P, _P, _P, _P, C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _I,
+                     _P, _P],
 }
 EXPORTS = ["kv_version", "kv_status_string", "kv_last_cuda_error", "kv_launch_count"] + list(_SIGNATURES)
 

@@ -464,3 +464,63 @@ class _PatchifyFn(torch.autograd.Function):
 def patchify(images, n_patches):
     """VisionTransformer.patchify (model.py:111-126): (B,C,H,W) -> (B, np^2, C*ph*pw) float32."""
     return _PatchifyFn.apply(images.contiguous().float(), n_patches)
+
+
+_CE_WORKSPACE = {}
+
+
+def _ce_workspace(device):
+    ws = _CE_WORKSPACE.get(device)
+    if ws is None:
+        ws = torch.zeros((L.load().kv_cross_entropy_workspace_floats(),), dtype=torch.float32, device=device)
+        _CE_WORKSPACE[device] = ws
+    return ws
+
+
+def cross_entropy_with_grad(logits, labels, ignore_index=-100, need_grad=True):
+    """nn.CrossEntropyLoss() (train.py:22,36) and its gradient w.r.t. the logits in ONE pass:
+    returns (loss: 0-dim tensor, dlogits or None).  labels: int64 class indices."""
+    lib = L.load()
+    _require_cuda(logits, labels)
+    assert logits.dim() == 2 and logits.dtype == torch.float32
+    assert labels.shape == (logits.shape[0],) and labels.dtype == torch.int64
+    logits, labels = logits.contiguous(), labels.contiguous()
+    B, Cn = logits.shape
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    dz = torch.empty_like(logits) if need_grad else None
+    _call("kv_cross_entropy", lib.kv_cross_entropy, logits.data_ptr(), labels.data_ptr(), B, Cn, int(ignore_index),
+          loss.data_ptr(), L.ptr(dz), _ce_workspace(logits.device).data_ptr(), _stream(), work=8.0 * B * Cn)
+    return loss, dz
+
+
+class _CrossEntropyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels, ignore_index):
+        loss, dz = cross_entropy_with_grad(logits, labels, ignore_index, need_grad=logits.requires_grad)
+        ctx.save_for_backward(dz)
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (dz,) = ctx.saved_tensors
+        return dz * dloss, None, None
+
+
+def cross_entropy(logits, labels, ignore_index=-100):
+    """Drop-in for ``nn.CrossEntropyLoss()(logits, labels)`` on CUDA tensors (mean reduction)."""
+    return _CrossEntropyFn.apply(logits, labels, ignore_index)
+
+
+def adam_step(param, grad, exp_avg, exp_avg_sq, state, lr, beta1=0.9, beta2=0.999, eps=1e-8, grad_scale=1.0,
+              zero_grad=False):
+    """One torch.optim.Adam update (train.py:23,40) of flat fp32 buffers, in place; ``state`` = 3 device doubles
+    (step count and bias corrections, advanced on the device)."""
+    lib = L.load()
+    _require_cuda(param, grad, exp_avg, exp_avg_sq, state)
+    n = param.numel()
+    assert grad.numel() == n and exp_avg.numel() == n and exp_avg_sq.numel() == n
+    assert state.dtype == torch.float64 and state.numel() >= 3
+    for t in (param, grad, exp_avg, exp_avg_sq):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    _call("kv_adam_step", lib.kv_adam_step, param.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
+          n, lr, beta1, beta2, eps, grad_scale, 1 if zero_grad else 0, state.data_ptr(), _stream(), work=32.0 * n)

@@ -33,6 +33,7 @@ class FlatGradBuckets:
             offs.append(total)
             total += (p.numel() + 3) // 4 * 4
         self.flat = torch.zeros(total, dtype=dt, device=dev)
+        self.order, self.offsets = order, offs
         self.buckets = []          # (start, end, n_params)
         self._bucket_of = {}
         start, count, elems_per_bucket = 0, 0, max(bucket_bytes // self.flat.element_size(), 1)
@@ -53,8 +54,10 @@ class FlatGradBuckets:
             for p in self.params:
                 self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
 
-    def zero(self):
-        self.flat.zero_()
+    def zero(self, already_zero: bool = False):
+        """Start an iteration.  ``already_zero``: the optimizer kernel cleared the buffer as it read it."""
+        if not already_zero:
+            self.flat.zero_()
         for i, (_, _, n) in enumerate(self.buckets):
             self._pending[i] = n
         self._handles = []
@@ -75,9 +78,9 @@ class FlatGradBuckets:
         if self.world > 1:
             self._on_grad(p)
 
-    def finish(self):
+    def finish(self, scale: bool = True):
         """Wait for the collectives, reduce buckets whose hooks never fired (unused parameters),
-        and turn the sums into means."""
+        and turn the sums into means (``scale=False``: the optimizer kernel applies the 1/world)."""
         if self.world == 1:
             return
         for b, left in enumerate(self._pending):
@@ -89,7 +92,48 @@ class FlatGradBuckets:
         for h in self._handles:
             h.wait()
         self._handles = []
-        self.flat.mul_(1.0 / self.world)
+        if scale:
+            self.flat.mul_(1.0 / self.world)
+
+
+class FlatAdam:
+    """``torch.optim.Adam(params, lr)`` (train.py:23) as ONE kernel launch per iteration (kv_adam_step).
+
+    The parameters are re-homed into one flat buffer laid out like the gradient buffer of ``grads``
+    (every ``p.data`` becomes a view, values kept), the two moments are flat buffers of the same
+    layout, and the step counter lives on the device.  The launch also applies the 1/world of the
+    data-parallel mean and clears the gradient buffer for the next iteration.  CUDA only."""
+
+    def __init__(self, grads: FlatGradBuckets, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8):
+        if not grads.flat.is_cuda:
+            raise RuntimeError("FlatAdam runs on CUDA buffers only (there is no CPU path)")
+        self.grads = grads
+        self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
+        self.flat_param = torch.zeros_like(grads.flat)
+        with torch.no_grad():
+            for p, off in zip(grads.order, grads.offsets):
+                view = self.flat_param[off:off + p.numel()].view_as(p)
+                view.copy_(p.data)
+                p.data = view
+        self.exp_avg = torch.zeros_like(grads.flat)
+        self.exp_avg_sq = torch.zeros_like(grads.flat)
+        self.state = torch.zeros(4, dtype=torch.float64, device=grads.flat.device)
+
+    def step(self, zero_grad: bool = True):
+        from . import ops
+        ops.adam_step(self.flat_param, self.grads.flat, self.exp_avg, self.exp_avg_sq, self.state, self.lr,
+                      self.betas[0], self.betas[1], self.eps, grad_scale=1.0 / self.grads.world,
+                      zero_grad=zero_grad)
+
+    def state_dict(self):
+        return {"exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "state": self.state,
+                "lr": self.lr, "betas": self.betas, "eps": self.eps}
+
+    def load_state_dict(self, sd):
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        self.state.copy_(sd["state"])
+        self.lr, self.betas, self.eps = float(sd["lr"]), tuple(sd["betas"]), float(sd["eps"])
 
 
 class TrainStep:
@@ -105,28 +149,39 @@ class TrainStep:
         params = [p for p in model.parameters() if p.requires_grad]
         self.grads = FlatGradBuckets(params, bucket_bytes)
         self.cuda_graph = bool(cuda_graph) and params[0].is_cuda and self.grads.world == 1
-        if optimizer is None:
-            fused = params[0].is_cuda
-            optimizer = torch.optim.Adam(params, lr=lr, fused=fused, capturable=self.cuda_graph)
+        # On the GPU the loss and the update are the library's own kernels: one
+        # cross-entropy launch (loss + d logits) and one Adam launch over the flat buffers.  A caller's
+        # optimizer, or CPU tensors (the gloo tests of the host logic), take the torch route.
+        self.fused = optimizer is None and params[0].is_cuda
+        if self.fused:
+            optimizer = FlatAdam(self.grads, lr=lr)
+        elif optimizer is None:
+            optimizer = torch.optim.Adam(params, lr=lr)
         self.opt = optimizer
         self._calls = 0
+        self._clean = True         # gradient buffer known to be all zero
         self._graph = None
         self._static = None
 
     def _eager(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
-        self.grads.zero()
+        # fused: the previous Adam launch left the gradient buffer cleared (it is created zeroed)
+        self.grads.zero(already_zero=self.fused and self._clean)
+        self._clean = False
         logits = self.model(images)
-        loss = F.cross_entropy(logits, labels)
         if images.is_cuda:
             from . import ops
+            loss, dlogits = ops.cross_entropy_with_grad(logits.detach(), labels)
             ops.GRAD_SINK = self.grads
-        try:
-            loss.backward()
-        finally:
-            if images.is_cuda:
+            try:
+                logits.backward(dlogits)
+            finally:
                 ops.GRAD_SINK = None
-        self.grads.finish()
+        else:
+            loss = F.cross_entropy(logits, labels)
+            loss.backward()
+        self.grads.finish(scale=not self.fused)
         self.opt.step()
+        self._clean = True
         return loss.detach()
 
     def __call__(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:

@@ -322,3 +322,42 @@ def vit_forward(images: Tensor, sd: Dict[str, Tensor], *, n_patches: int, n_bloc
         x = block_forward(x, sd, f"blocks.{blk}.", n_heads, kind, kan_mlp)
     c = F.layer_norm(x[:, 0], (d,), sd["mlp_head.0.weight"], sd["mlp_head.0.bias"], 1e-5)
     return F.linear(c, sd["mlp_head.1.weight"], sd["mlp_head.1.bias"])
+
+
+# --------------------------------------------------------------------------
+# The two ops either side of the path in the training loop (train.py:22-23,35-40):
+# nn.CrossEntropyLoss() and torch.optim.Adam(lr).  The reference calls torch for both, so
+# these numpy restatements are pinned against torch itself (tests/test_oracle_golden.py).
+# --------------------------------------------------------------------------
+
+
+def cross_entropy_np(logits: np.ndarray, labels: np.ndarray, ignore_index: int = -100):
+    """(loss, d loss / d logits) of nn.CrossEntropyLoss() -- train.py:22,36: class-index targets, mean over
+    the rows whose label is not ``ignore_index``."""
+    z = logits.astype(np.float64)
+    valid = labels != ignore_index
+    n = int(valid.sum())
+    mx = z.max(axis=1, keepdims=True)
+    e = np.exp(z - mx)
+    s = e.sum(axis=1, keepdims=True)
+    lse = np.log(s[:, 0]) + mx[:, 0]
+    rows = np.arange(z.shape[0])
+    picked = z[rows, np.where(valid, labels, 0)]
+    loss = float(((lse - picked) * valid).sum() / n) if n else float("nan")
+    p = e / s
+    p[rows, np.where(valid, labels, 0)] -= 1.0
+    dz = p * valid[:, None] / max(n, 1)
+    return np.float32(loss), dz.astype(np.float32)
+
+
+def adam_step_np(p: np.ndarray, g: np.ndarray, m: np.ndarray, v: np.ndarray, t: int, lr: float = 1e-3,
+                 beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8):
+    """One torch.optim.Adam update (train.py:23,40; no weight decay / amsgrad), step count ``t`` >= 1.
+    fp32 state like torch; returns the new (p, m, v)."""
+    f = np.float32
+    m = (f(beta1) * m + f(1.0 - beta1) * g).astype(f)
+    v = (f(beta2) * v + f(1.0 - beta2) * g * g).astype(f)
+    step_size = f(lr / (1.0 - beta1 ** t))
+    bc2_sqrt = f(math.sqrt(1.0 - beta2 ** t))
+    denom = (np.sqrt(v) / bc2_sqrt + f(eps)).astype(f)
+    return (p - step_size * (m / denom)).astype(f), m, v

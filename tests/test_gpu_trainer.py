@@ -48,3 +48,99 @@ def test_cuda_graph_step_matches_eager():
         losses.append([float(step(x, y)) for x, y in zip(img, lab)])
     for a, b in zip(*losses):
         assert abs(a - b) <= 1e-4 * abs(a)
+
+
+# ---- the loss and the optimizer kernels ----
+
+@pytest.mark.parametrize("B,Cn,ignore", [(4, 10, False), (256, 10, False), (37, 100, True), (4096, 1000, True),
+                                         (1, 3, False)])
+def test_cross_entropy_matches_oracle_and_torch(B, Cn, ignore):
+    import numpy as np
+    from kan_vit_b200 import ops
+    from oracle import kan_oracle as O
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(B + Cn)
+    z = 4.0 * torch.randn(B, Cn, generator=g)
+    y = torch.randint(0, Cn, (B,), generator=g)
+    if ignore:
+        y[::7] = -100
+    loss, dz = ops.cross_entropy_with_grad(z.to(dev), y.to(dev))
+    lo, dzo = O.cross_entropy_np(z.numpy(), y.numpy())
+    assert abs(float(loss) - float(lo)) <= 2e-6 * abs(float(lo))          # fp32 tolerance, mean of B rows
+    assert np.abs(dz.cpu().numpy() - dzo).max() <= 2e-7
+    # torch on the same device, through the autograd wrapper
+    zt = z.to(dev).requires_grad_(True)
+    za = z.to(dev).requires_grad_(True)
+    (3.0 * torch.nn.functional.cross_entropy(zt, y.to(dev))).backward()
+    (3.0 * ops.cross_entropy(za, y.to(dev))).backward()
+    assert (za.grad - zt.grad).abs().max().item() <= 1e-6
+    # block partials are added in block order: bit-reproducible
+    loss2, dz2 = ops.cross_entropy_with_grad(z.to(dev), y.to(dev))
+    assert torch.equal(loss, loss2) and torch.equal(dz, dz2)
+
+
+def test_cross_entropy_all_ignored_is_nan_and_bad_label_poisons():
+    from kan_vit_b200 import ops
+    dev = torch.device("cuda:0")
+    z = torch.randn(5, 7, device=dev)
+    loss, dz = ops.cross_entropy_with_grad(z, torch.full((5,), -100, device=dev))
+    assert torch.isnan(loss) and dz.abs().max().item() == 0.0
+    loss, _ = ops.cross_entropy_with_grad(z, torch.tensor([0, 1, 2, 9, 3], device=dev))
+    assert torch.isnan(loss)
+    loss, _ = ops.cross_entropy_with_grad(z, torch.tensor([0, 1, 2, 6, 3], device=dev))  # workspace left clean
+    assert torch.isfinite(loss)
+
+
+@pytest.mark.parametrize("n", [4, 1000, 1 << 20, 5 * (1 << 20) + 12])
+def test_flat_adam_kernel_matches_oracle_and_torch(n):
+    import numpy as np
+    from kan_vit_b200 import ops
+    from oracle import kan_oracle as O
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(n % 1000)
+    p0 = torch.randn(n, generator=g)
+    p = p0.to(dev).clone()
+    m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    state = torch.zeros(4, dtype=torch.float64, device=dev)
+    pt = p0.to(dev).clone().requires_grad_(True)
+    opt = torch.optim.Adam([pt], lr=3e-3)
+    pn, mn, vn = p0.numpy().copy(), np.zeros(n, np.float32), np.zeros(n, np.float32)
+    for t in range(1, 5):
+        grad = torch.randn(n, generator=g) * (10.0 ** (t - 3))
+        gd = (2.0 * grad).to(dev)                      # the kernel applies grad_scale = 1/2
+        ops.adam_step(p, gd, m, v, state, 3e-3, grad_scale=0.5, zero_grad=(t % 2 == 0))
+        assert (gd.abs().max().item() == 0.0) == (t % 2 == 0)
+        pt.grad = grad.to(dev)
+        opt.step()
+        if n <= 1 << 20:
+            pn, mn, vn = O.adam_step_np(pn, grad.numpy(), mn, vn, t, lr=3e-3)
+            assert np.abs(p.cpu().numpy() - pn).max() <= 2e-6 * np.abs(pn).max()
+        assert (p - pt.detach()).abs().max().item() <= 2e-6 * pt.detach().abs().max().item()
+    assert float(state[0]) == 4.0
+
+
+@pytest.mark.parametrize("kind", ["efficientkan", "sine"])
+def test_fused_step_follows_torch_loss_and_adam(kind):
+    """TrainStep with the library's cross-entropy + flat Adam kernels follows the same model trained with
+    F.cross_entropy + torch.optim.Adam, and the parameters stay views of the flat buffer."""
+    from kan_vit_b200.trainer import FlatAdam, TrainStep
+    dev = torch.device("cuda:0")
+    img = [torch.randn(8, 1, 28, 28, device=dev) for _ in range(4)]
+    lab = [torch.randint(0, 10, (8,), device=dev) for _ in range(4)]
+    ma, mb = _model(kind, dev), _model(kind, dev)
+    fused = TrainStep(ma, lr=1e-3)
+    assert isinstance(fused.opt, FlatAdam) and fused.fused
+    plain = TrainStep(mb, optimizer=torch.optim.Adam(mb.parameters(), lr=1e-3))
+    assert not plain.fused
+    for x, y in zip(img, lab):
+        la, lb = float(fused(x, y)), float(plain(x, y))
+        assert abs(la - lb) <= 1e-4 * abs(lb)
+    lo = fused.opt.flat_param.data_ptr()
+    for (k, pa), pb in zip(ma.named_parameters(), mb.parameters()):
+        assert lo <= pa.data_ptr() < lo + fused.opt.flat_param.numel() * 4, k
+        # Adam's first steps move every weight by ~lr whatever the gradient scale, so compare against lr
+        assert (pa - pb).abs().max().item() <= 2e-4, k
+    assert fused.grads.flat.abs().max().item() == 0.0      # cleared by the Adam launch
+    sd = ma.state_dict()
+    mc = _model(kind, dev)
+    mc.load_state_dict(sd)                                  # strict: names and shapes unchanged by the re-homing

@@ -42,6 +42,12 @@ def test_bad_arguments_return_codes_without_a_gpu():
     assert lib.kv_kan_fwd(C.byref(d), 1, 1, None, 1, None, None, None, None, None, 1, None) == -3
     assert lib.kv_patchify(1, 1, 2, 1, 28, 28, 5, None) == -2  # 28 % 5 != 0 (model.py:58-59)
     assert lib.kv_attn_fwd(1, None, 1, 1, 1, 50, 2, 4096, None) == -2
+    assert lib.kv_cross_entropy(1, 1, 0, 10, -100, 1, 1, 1, None) == -1      # empty batch
+    assert lib.kv_cross_entropy(None, 1, 4, 10, -100, 1, 1, 1, None) == -1   # null logits
+    assert lib.kv_adam_step(16, 16, 16, 16, 6, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, 16, None) == -1   # n % 4
+    assert lib.kv_adam_step(16, 20, 16, 16, 8, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, 16, None) == -4   # alignment
+    assert lib.kv_adam_step(None, None, None, None, 0, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, None, None) == 0
+    assert lib.kv_cross_entropy_workspace_floats() >= 2
 
 
 @pytest.mark.parametrize("name,args", [

@@ -105,3 +105,36 @@ def test_layout_bit_exact():
     assert torch.equal(O.patchify(g.t("img_1x28"), 7), g.t("patches_1x28_np7"))
     assert torch.equal(O.positional_embeddings(17, 24), g.t("pos_17x24"))
     assert torch.equal(O.positional_embeddings(50, 64), g.t("pos_50x64"))
+
+
+def test_cross_entropy_restatement_matches_torch():
+    """train.py:22 uses torch's nn.CrossEntropyLoss: the numpy restatement is pinned against it."""
+    import numpy as np
+    g = torch.Generator().manual_seed(3)
+    for B, Cn, ignore in ((8, 10, False), (37, 100, True), (256, 1000, True)):
+        z = (3.0 * torch.randn(B, Cn, generator=g)).requires_grad_(True)
+        y = torch.randint(0, Cn, (B,), generator=g)
+        if ignore:
+            y[::5] = -100
+        loss = torch.nn.CrossEntropyLoss()(z, y)
+        loss.backward()
+        lo, dz = O.cross_entropy_np(z.detach().numpy(), y.numpy())
+        assert abs(float(lo) - float(loss)) <= 2e-6 * abs(float(loss))
+        assert np.abs(dz - z.grad.numpy()).max() <= 1e-7
+
+
+def test_adam_restatement_matches_torch():
+    """train.py:23 uses torch.optim.Adam(lr): five steps of the numpy restatement follow it."""
+    import numpy as np
+    g = torch.Generator().manual_seed(4)
+    p = torch.randn(1000, generator=g).requires_grad_(True)
+    opt = torch.optim.Adam([p], lr=1e-2)
+    pn = p.detach().numpy().copy()
+    m = np.zeros_like(pn)
+    v = np.zeros_like(pn)
+    for t in range(1, 6):
+        grad = torch.randn(1000, generator=g) * (10.0 ** float(torch.randint(-3, 2, (1,), generator=g)))
+        p.grad = grad.clone()
+        opt.step()
+        pn, m, v = O.adam_step_np(pn, grad.numpy(), m, v, t, lr=1e-2)
+        assert np.abs(pn - p.detach().numpy()).max() <= 2e-6 * np.abs(pn).max()
