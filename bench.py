@@ -165,7 +165,7 @@ def run_reference_arm(args):
                                    "restatement of the reference, torch CPU fp32, autograd + Adam)"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -421,12 +421,21 @@ def run_gpu_arm(args):
             "roofline": roofline,
             "cpu_baseline": cpu_baseline,
         }
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
+_OUT = sys.stdout
+
+
 def main():
+    # stdout carries exactly ONE JSON line: whatever libraries write to fd 1 (NCCL prints its version
+    # banner there when NCCL_DEBUG is set on the box) is sent to stderr instead.
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
