@@ -210,6 +210,32 @@ int kv_attn_fwd_bf16(const float* qkv, const float* residual, float* out, float*
 int kv_attn_bwd_bf16(const float* qkv, const float* dout, const float* lse, float* dqkv,
                      int B, int N, int H, int d_head, void* stream);
 
+/* Attention of the FlashAttention module (attention.py:61-109 -> FlashAttentionFunction, utils.py:137-295),
+ * the block of type="flash-attn" (model.py:93-95,156-159): q/k/v are separate fp32 matrices in
+ * 'b n (h d)' layout with row strides ldq/ldk/ldv (head h = columns [h*d_head, (h+1)*d_head); k and v may
+ * be the two halves of the to_kv output), Nk may differ from Nq (context), out has row stride ldo.
+ * mask: nullable bytes (torch.bool), element (b,h,i,j) at b*mask_stride_b + h*mask_stride_h +
+ * i*mask_stride_q + j, stride 0 = broadcast (a 'b n' key mask has strides (Nk,0,0)); false = hidden.
+ * causal != 0: key j is visible to query i iff j <= i - max(Nk-Nq,0) (the reference's rule, utils.py:142,
+ * 175,192-194).  Hidden scores are -FLT_MAX (not -inf), mask-false weights are zeroed after the
+ * exponential and the row sum is clamped at 1e-10, so fully hidden rows behave as in the reference.
+ * lse [B][H][Nq] and out are saved for the backward (D_i = sum(dO_i * O_i), utils.py:277).
+ * The q/k bucket sizes of the reference only change the summation order and have no counterpart.
+ * KV_ERR_BAD_SHAPE when a head does not fit in shared memory (roughly Nk <= 400 forward,
+ * Nq + Nk <= 430 backward at d_head 64). */
+typedef struct kv_attn_general {
+  int32_t B, H, Nq, Nk, d_head;
+  int32_t ldq, ldk, ldv, ldo;
+  int32_t causal;
+  int64_t mask_stride_b, mask_stride_h, mask_stride_q;
+} kv_attn_general_t;
+int kv_attn_general_fwd(const kv_attn_general_t* a, const float* q, const float* k, const float* v,
+                        const unsigned char* mask, float* out, float* lse, void* stream);
+/* dq/dk/dv use the layouts (row strides) of q/k/v and are overwritten. */
+int kv_attn_general_bwd(const kv_attn_general_t* a, const float* q, const float* k, const float* v,
+                        const unsigned char* mask, const float* out, const float* dout, const float* lse,
+                        float* dq, float* dk, float* dv, void* stream);
+
 /* nn.LayerNorm(d), eps 1e-5, affine (model.py:22,24,107).  mean/rstd [T] saved. */
 int kv_layernorm_fwd(const float* X, const float* gamma, const float* beta, float* Y,
                      float* mean, float* rstd, int T, int d, int ldx, float eps, void* stream);

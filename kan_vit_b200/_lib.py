@@ -37,6 +37,12 @@ class KanDesc(C.Structure):
     ]
 
 
+class AttnGeneral(C.Structure):
+    """kv_attn_general_t of include/kanvit_b200.h"""
+    _fields_ = [(n, C.c_int32) for n in ("B", "H", "Nq", "Nk", "d_head", "ldq", "ldk", "ldv", "ldo", "causal")] + \
+               [(n, C.c_int64) for n in ("mask_stride_b", "mask_stride_h", "mask_stride_q")]
+
+
 _P = C.c_void_p
 _I = C.c_int
 _DP = C.POINTER(KanDesc)
@@ -57,6 +63,8 @@ _SIGNATURES = {
     "kv_attn_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "kv_attn_fwd_bf16": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "kv_attn_bwd_bf16": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
+    "kv_attn_general_fwd": [C.POINTER(AttnGeneral)] + [_P] * 7,
+    "kv_attn_general_bwd": [C.POINTER(AttnGeneral)] + [_P] * 11,
     "kv_layernorm_fwd": [_P, _P, _P, _P, _P, _P, _I, _I, _I, C.c_float, _P],
     "kv_layernorm_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, C.c_float, _P],
     "kv_patchify": [_P, _P, _I, _I, _I, _I, _I, _P],

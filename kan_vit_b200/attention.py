@@ -16,6 +16,51 @@ from .models.fastkan import FastKANLayer
 from .models.sinekan import SineKANLayer
 
 
+class FlashAttention(torch.nn.Module):
+    """Drop-in for attention.py:13-109 (the block of ``type="flash-attn"``, model.py:93-95): bias-free
+    ``to_q`` / ``to_kv`` / ``to_out`` projections around FlashAttentionFunction (utils.py:137-295).
+
+    The three projections run as Linear GEMM launches and the attention itself (optional ``context``,
+    boolean ``mask``, the reference's ``causal`` rule) as one kernel per direction.  The q/k bucket sizes
+    only set the summation order of the reference's Python tile loops; they are accepted and ignored.
+    ``parallel=True`` cannot run in the reference either (attention.py:91-97 replaces q by a list);
+    ``mixed_precision`` is an autocast stub there (attention.py:58-59): use ``set_precision("bf16")``."""
+
+    def __init__(self, *, dim, heads=8, dim_head=64, causal=False, q_bucket_size=512, k_bucket_size=1024,
+                 parallel=False, mixed_precision=False):
+        super().__init__()
+        if parallel:
+            raise NotImplementedError("FlashAttention(parallel=True) does not work in the reference "
+                                      "(attention.py:91-97); use kan_vit_b200.trainer for data parallelism")
+        self.heads = heads
+        self.dim_head = dim_head
+        self.causal = causal
+        self.parallel = parallel
+        self.mixed_precision = mixed_precision
+        inner_dim = heads * dim_head
+        self.to_q = torch.nn.Linear(dim, inner_dim, bias=False)
+        self.to_kv = torch.nn.Linear(dim, inner_dim * 2, bias=False)
+        self.to_out = torch.nn.Linear(inner_dim, dim, bias=False)
+        self.q_bucket_size = q_bucket_size
+        self.k_bucket_size = k_bucket_size
+        self._specs = None
+
+    def forward(self, x, context=None, mask=None, q_bucket_size=None, k_bucket_size=None):
+        if self._specs is None:
+            self._specs = tuple(make_spec([m]) for m in (self.to_q, self.to_kv, self.to_out))
+        B, Nq, dim = x.shape
+        ctx = x if context is None else context
+        Nk = ctx.shape[1]
+        inner = self.heads * self.dim_head
+        x2d = x.reshape(B * Nq, dim)
+        q = ops.kan_apply(x2d, self._specs[0], [slots_of(self.to_q)])
+        kv = ops.kan_apply(x2d if context is None else ctx.reshape(B * Nk, dim), self._specs[1],
+                           [slots_of(self.to_kv)])
+        out = ops.attention_general(q, kv[:, :inner], kv[:, inner:], B, Nq, Nk, self.heads, self.dim_head,
+                                    mask=mask, causal=self.causal)
+        return ops.kan_apply(out, self._specs[2], [slots_of(self.to_out)]).reshape(B, Nq, dim)
+
+
 class MSA(torch.nn.Module):
     def __init__(self, d, n_heads=4, type: str = "vanilla"):
         super().__init__()

@@ -5,7 +5,7 @@ import torch.nn as nn
 
 from . import ops
 from ._dispatch import make_spec, slots_of
-from .attention import MSA
+from .attention import MSA, FlashAttention
 from .models.cheby import ChebyKANLayer
 from .models.effkan import KANLinear
 from .models.fastkan import FastKANLayer
@@ -74,17 +74,18 @@ class VisionTransformer(nn.Module):
             self.linear_mapper = FastKANLayer(self.input_d, d_hidden)
         else:
             raise ValueError(f"Unknown transformer type: {type}")
-        if type == "flash-attn":
-            raise NotImplementedError("type='flash-attn' (bare FlashAttention blocks) is the next-tier row "
-                                      "of SURVEY.md section 8f and is not built yet")
 
         self.v_class = nn.Parameter(torch.randn(1, d_hidden))
         self.register_buffer('pos_embeddings', self.positional_embeddings(n_patches ** 2 + 1, d_hidden),
                              persistent=False)
-        self.blocks = nn.ModuleList([
-            TransformerBlock(d_model=d_hidden, n_heads=n_heads, feedforward_dim=4 * d_hidden,
-                             attn_type=type, kan_mlp=kan_mlp)
-            for _ in range(n_blocks)])
+        if type == "flash-attn":
+            # bare attention modules: no LayerNorm / residual / MLP around them (model.py:93-95)
+            self.blocks = nn.ModuleList([FlashAttention(dim=d_hidden, heads=n_heads) for _ in range(n_blocks)])
+        else:
+            self.blocks = nn.ModuleList([
+                TransformerBlock(d_model=d_hidden, n_heads=n_heads, feedforward_dim=4 * d_hidden,
+                                 attn_type=type, kan_mlp=kan_mlp)
+                for _ in range(n_blocks)])
         self.mlp_head = nn.Sequential(nn.LayerNorm(d_hidden), nn.Linear(d_hidden, out_d))
         self._specs = None
 
@@ -111,8 +112,12 @@ class VisionTransformer(nn.Module):
         N, d = P2 + 1, self.d_hidden
         x = ops.kan_apply(patches.view(B * P2, input_d), self._specs[0], [slots_of(self.linear_mapper)],
                           pos=self.pos_embeddings, v_class=self.v_class, rows_in=P2, rows_out=N, row_shift=1)
-        for blk in self.blocks:
-            x = blk.forward2d(x, B, N)
+        if isinstance(self.blocks[0], FlashAttention):
+            for blk in self.blocks:
+                x = blk(x.view(B, N, d)).reshape(B * N, d)
+        else:
+            for blk in self.blocks:
+                x = blk.forward2d(x, B, N)
         cls = x.view(B, N * d)[:, :d]
         head_ln = self.mlp_head[0]
         h = ops.layer_norm(cls, head_ln.weight, head_ln.bias, head_ln.eps)

@@ -524,3 +524,57 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, state, lr, beta1=0.9, beta2=0.99
         assert t.dtype == torch.float32 and t.is_contiguous()
     _call("kv_adam_step", lib.kv_adam_step, param.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
           n, lr, beta1, beta2, eps, grad_scale, 1 if zero_grad else 0, state.data_ptr(), _stream(), work=32.0 * n)
+
+
+class _AttnGeneralFn(torch.autograd.Function):
+    """FlashAttentionFunction (utils.py:137-295): q [B*Nq, >=H*dh], k/v [B*Nk, ...] column views allowed."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, mask, causal, B, Nq, Nk, H, dh):
+        lib = L.load()
+        _require_cuda(q, k, v, mask)
+        for t in (q, k, v):
+            assert t.dim() == 2 and t.dtype == torch.float32 and t.stride(1) == 1
+        out = torch.empty((B * Nq, H * dh), dtype=torch.float32, device=q.device)
+        lse = torch.empty((B, H, Nq), dtype=torch.float32, device=q.device)
+        a = L.AttnGeneral(B, H, Nq, Nk, dh, q.stride(0), k.stride(0), v.stride(0), H * dh, 1 if causal else 0, 0, 0, 0)
+        if mask is not None:
+            assert mask.dtype == torch.bool and mask.dim() == 4 and mask.shape[-1] == Nk and mask.stride(3) == 1
+            a.mask_stride_b, a.mask_stride_h, a.mask_stride_q = mask.stride(0), mask.stride(1), mask.stride(2)
+        _call("kv_attn_general_fwd", lib.kv_attn_general_fwd, C.byref(a), q.data_ptr(), k.data_ptr(), v.data_ptr(),
+              L.ptr(mask), out.data_ptr(), lse.data_ptr(), _stream(), work=4.0 * B * H * Nq * Nk * dh)
+        ctx.a = a
+        ctx.save_for_backward(q, k, v, mask, out, lse)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = L.load()
+        q, k, v, mask, out, lse = ctx.saved_tensors
+        a = ctx.a
+        dout = dout.contiguous()
+        # gradients in the layouts of q / k / v (k and v are usually the halves of one to_kv output)
+        dq = torch.empty_strided(q.shape, q.stride(), dtype=torch.float32, device=q.device)
+        if k.stride(0) == v.stride(0) and v.data_ptr() - k.data_ptr() == 4 * k.shape[1] and k.stride(0) == 2 * k.shape[1]:
+            dkv = torch.empty((k.shape[0], 2 * k.shape[1]), dtype=torch.float32, device=q.device)
+            dk, dv = dkv[:, :k.shape[1]], dkv[:, k.shape[1]:]
+        else:
+            dk = torch.empty_strided(k.shape, k.stride(), dtype=torch.float32, device=q.device)
+            dv = torch.empty_strided(v.shape, v.stride(), dtype=torch.float32, device=q.device)
+        _call("kv_attn_general_bwd", lib.kv_attn_general_bwd, C.byref(a), q.data_ptr(), k.data_ptr(), v.data_ptr(),
+              L.ptr(mask), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), dq.data_ptr(), dk.data_ptr(),
+              dv.data_ptr(), _stream(), work=10.0 * a.B * a.H * a.Nq * a.Nk * a.d_head)
+        return dq, dk, dv, None, None, None, None, None, None, None
+
+
+def attention_general(q, k, v, B, Nq, Nk, H, dh, mask=None, causal=False):
+    """Attention of the FlashAttention module: q [B*Nq, H*dh], k / v [B*Nk, H*dh] (column views of a wider
+    matrix are fine), mask None or a bool tensor broadcastable to [B, H, Nq, Nk] -> out [B*Nq, H*dh]."""
+    if mask is not None:
+        if mask.dim() == 2:                       # 'b n' key mask (utils.py:154-155)
+            mask = mask[:, None, None, :]
+        mask = mask.to(torch.bool)
+        if mask.shape[-1] != Nk or mask.stride(-1) != 1:
+            mask = mask.expand(*mask.shape[:-1], Nk).contiguous()
+        mask = mask.expand(B, H, Nq, Nk)
+    return _AttnGeneralFn.apply(q, k, v, mask, bool(causal), B, Nq, Nk, H, dh)
