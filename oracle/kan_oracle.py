@@ -319,7 +319,10 @@ def vit_forward(images: Tensor, sd: Dict[str, Tensor], *, n_patches: int, n_bloc
     pos = sd["pos_embeddings"] if "pos_embeddings" in sd else positional_embeddings(p2 + 1, d)
     x = tok + pos[: tok.size(1)].to(tok.dtype)
     for blk in range(n_blocks):
-        x = block_forward(x, sd, f"blocks.{blk}.", n_heads, kind, kan_mlp)
+        if kind == "flash-attn":   # bare attention modules, model.py:93-95,156-159
+            x = flash_attention_forward(x, sd, f"blocks.{blk}.", n_heads)
+        else:
+            x = block_forward(x, sd, f"blocks.{blk}.", n_heads, kind, kan_mlp)
     c = F.layer_norm(x[:, 0], (d,), sd["mlp_head.0.weight"], sd["mlp_head.0.bias"], 1e-5)
     return F.linear(c, sd["mlp_head.1.weight"], sd["mlp_head.1.bias"])
 
@@ -361,3 +364,81 @@ def adam_step_np(p: np.ndarray, g: np.ndarray, m: np.ndarray, v: np.ndarray, t: 
     bc2_sqrt = f(math.sqrt(1.0 - beta2 ** t))
     denom = (np.sqrt(v) / bc2_sqrt + f(eps)).astype(f)
     return (p - step_size * (m / denom)).astype(f), m, v
+
+
+# --------------------------------------------------------------------------
+# FlashAttention module / type="flash-attn"  (attention.py:13-109, utils.py:134-295, model.py:93-95)
+# --------------------------------------------------------------------------
+
+_FLASH_EPS = 1e-10  # utils.py:10
+
+
+def _flash_causal_hidden(nq: int, nk: int) -> Tensor:
+    """[nq, nk] bool, True where the reference's causal fill hides key j from query i: the union over tiles of
+    ``ones.triu(q_start - k_start + 1)`` with ``q_start = tile_start - max(nk - nq, 0)`` (utils.py:142,175,
+    192-194), i.e. j > i - max(nk - nq, 0)."""
+    diff = max(nk - nq, 0)
+    i = torch.arange(nq)[:, None]
+    j = torch.arange(nk)[None, :]
+    return j > i - diff
+
+
+class FlashAttentionFunctionOracle(torch.autograd.Function):
+    """utils.py:137-295 with one tile per direction (the bucket sizes only reorder the sums).  The reference
+    defines its own backward, so the restatement does too: for rows whose keys are all hidden the custom
+    backward is NOT the derivative of the forward, and the kernels follow the reference there as well."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, mask, causal):
+        neg = -torch.finfo(q.dtype).max
+        if mask is not None and mask.ndim == 2:
+            mask = mask[:, None, None, :]                        # 'b n -> b 1 1 n', utils.py:154-155
+        s = torch.einsum("bhid,bhjd->bhij", q, k) * (q.shape[-1] ** -0.5)
+        if mask is not None:
+            s = s.masked_fill(~mask, neg)                        # utils.py:186-187
+        if causal:
+            s = s.masked_fill(_flash_causal_hidden(q.shape[-2], k.shape[-2]), neg)   # utils.py:189-195
+        m = s.amax(dim=-1, keepdim=True)
+        e = torch.exp(s - m)
+        if mask is not None:
+            e = e.masked_fill(~mask, 0.0)                        # utils.py:202-203
+        rs = e.sum(dim=-1, keepdim=True).clamp(min=_FLASH_EPS)   # utils.py:205-206
+        o = torch.einsum("bhij,bhjd->bhid", e, v) / rs
+        lse = rs.log() + m                                       # utils.py:222
+        ctx.causal, ctx.mask = causal, mask
+        ctx.save_for_backward(q, k, v, o, lse)
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, o, lse = ctx.saved_tensors
+        scale = q.shape[-1] ** -0.5
+        s = torch.einsum("bhid,bhjd->bhij", q, k) * scale
+        if ctx.causal:                                           # only the causal fill here, utils.py:267-273
+            s = s.masked_fill(_flash_causal_hidden(q.shape[-2], k.shape[-2]), -torch.finfo(q.dtype).max)
+        p = torch.exp(s - lse)
+        if ctx.mask is not None:
+            p = p.masked_fill(~ctx.mask, 0.0)                    # utils.py:276-277
+        dv = torch.einsum("bhij,bhid->bhjd", p, do)
+        dp = torch.einsum("bhid,bhjd->bhij", do, v)
+        D = (do * o).sum(dim=-1, keepdim=True)
+        ds = p * scale * (dp - D)
+        dq = torch.einsum("bhij,bhjd->bhid", ds, k)
+        dk = torch.einsum("bhij,bhid->bhjd", ds, q)
+        return dq, dk, dv, None, None
+
+
+def flash_attention_forward(x: Tensor, sd: Dict[str, Tensor], prefix: str, heads: int, *, context=None,
+                            mask=None, causal: bool = False) -> Tensor:
+    """FlashAttention.forward (attention.py:61-109): bias-free to_q / to_kv / to_out around the function above."""
+    ctx = x if context is None else context
+    q = F.linear(x, sd[prefix + "to_q.weight"])
+    k, v = F.linear(ctx, sd[prefix + "to_kv.weight"]).chunk(2, dim=-1)
+
+    def split(t):
+        b, n, hd = t.shape
+        return t.view(b, n, heads, hd // heads).permute(0, 2, 1, 3)
+
+    o = FlashAttentionFunctionOracle.apply(split(q), split(k), split(v), mask, causal)
+    b, h, n, d = o.shape
+    return F.linear(o.permute(0, 2, 1, 3).reshape(b, n, h * d), sd[prefix + "to_out.weight"])

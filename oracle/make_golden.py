@@ -28,7 +28,7 @@ def _np(t):
     return t.detach().cpu().numpy()
 
 
-def save_case(name, module, x, extra=None, out_fn=None):
+def save_case(name, module, x, extra=None, out_fn=None, f64=True):
     """Run module fwd+bwd on x with a seeded upstream grad; dump everything."""
     x = x.clone().requires_grad_(True)
     y = module(x) if out_fn is None else out_fn(module, x)
@@ -43,11 +43,12 @@ def save_case(name, module, x, extra=None, out_fn=None):
         if p.grad is not None:
             rec["g/" + k] = _np(p.grad)
     # float64 ground truth of the forward (settles summation-order disputes)
-    m64 = module.double()
-    with torch.no_grad():
-        y64 = m64(x.detach().double()) if out_fn is None else out_fn(m64, x.detach().double())
-    rec["y64"] = _np(y64)
-    module.float()
+    if f64:  # (the reference's FlashAttentionFunction builds fp32 state tensors and cannot run in float64)
+        m64 = module.double()
+        with torch.no_grad():
+            y64 = m64(x.detach().double()) if out_fn is None else out_fn(m64, x.detach().double())
+        rec["y64"] = _np(y64)
+        module.float()
     if extra:
         rec.update(extra)
     os.makedirs(OUT, exist_ok=True)
@@ -55,7 +56,63 @@ def save_case(name, module, x, extra=None, out_fn=None):
     print(f"{name}: y{tuple(y.shape)} {sum(v.nbytes for v in rec.values())/1024:.1f} KiB")
 
 
+def flash_cases():
+    """FlashAttention module / type="flash-attn" (SURVEY.md section 8f rank 2):
+    python oracle/make_golden.py --flash-only"""
+    sys.path.insert(0, REF)
+    import model as ref_model  # noqa
+    from attention import FlashAttention  # noqa
+
+    def xin(shape, seed, scale=1.0):
+        return torch.randn(shape, generator=torch.Generator().manual_seed(seed)) * scale
+
+    def bmask(shape, seed, p=0.7):
+        return torch.rand(shape, generator=torch.Generator().manual_seed(seed)) < p
+
+    def case(name, seed, x, causal=False, context=None, mask=None, qb=None, kb=None):
+        torch.manual_seed(seed)
+        m = FlashAttention(dim=16, heads=2, dim_head=8, causal=causal)
+        extra = {"causal": np.int64(causal)}
+        if context is not None:
+            extra["context"] = _np(context)
+        if mask is not None:
+            extra["mask"] = _np(mask)
+        save_case(name, m, x, extra=extra, f64=False,
+                  out_fn=lambda mod, xx: mod(xx, context=None if context is None else context.to(xx.dtype),
+                                             mask=mask, q_bucket_size=qb, k_bucket_size=kb))
+
+    case("flash_self", 60, xin((3, 5, 16), 61))
+    km = bmask((3, 5), 62)
+    km[1] = False                                   # one sample with every key hidden: o = 0
+    case("flash_keymask", 63, xin((3, 5, 16), 64), mask=km)
+    case("flash_causal", 65, xin((3, 6, 16), 66), causal=True)
+    # more keys than queries + causal: the first Nk-Nq query rows see no key and attend uniformly
+    case("flash_cross_causal", 67, xin((2, 4, 16), 68), causal=True, context=xin((2, 7, 16), 69))
+    case("flash_cross_mask", 70, xin((2, 6, 16), 71), context=xin((2, 4, 16), 72), mask=bmask((2, 4), 73))
+    case("flash_fullmask_causal_buckets", 74, xin((2, 7, 16), 75), causal=True, mask=bmask((2, 1, 7, 7), 76),
+         qb=3, kb=2)
+
+    torch.manual_seed(40)
+    vit = ref_model.VisionTransformer((1, 8, 8), n_patches=2, n_blocks=2, d_hidden=16, n_heads=2, out_d=10,
+                                      type="flash-attn")
+    x = xin((3, 1, 8, 8), 41).clone().requires_grad_(True)
+    y = vit(x)
+    dy = torch.randn(y.shape, generator=torch.Generator().manual_seed(1234))
+    y.backward(dy)
+    rec = {"x": _np(x), "dy": _np(dy), "y": _np(y), "gx": _np(x.grad), "pos_embeddings": _np(vit.pos_embeddings)}
+    for k, v in vit.state_dict().items():
+        rec["sd/" + k] = _np(v)
+    for k, p in vit.named_parameters():
+        if p.grad is not None:
+            rec["g/" + k] = _np(p.grad)
+    np.savez_compressed(os.path.join(OUT, "vit_flash-attn.npz"), **rec)
+    print(f"vit_flash-attn: y{tuple(y.shape)}")
+
+
 def main():
+    if "--flash-only" in sys.argv:
+        flash_cases()
+        return
     sys.path.insert(0, REF)
     import model as ref_model  # noqa
     from attention import MSA  # noqa
@@ -180,6 +237,7 @@ def main():
         keys[name] = {k: list(t.shape) for k, t in v.state_dict().items()}
     with open(os.path.join(OUT, "state_dict_keys.json"), "w") as f:
         json.dump(keys, f, indent=0, sort_keys=True)
+    flash_cases()
     print("done")
 
 

@@ -54,7 +54,7 @@ CASES = ["layer_effkan", "layer_effkan_g10k2_nonuniform", "layer_cheby", "layer_
          "layer_fastkan", "layer_sine", "layer_sine_g4", "layer_fourier",
          "msa_vanilla", "msa_efficientkan", "msa_cheby", "msa_fast", "msa_sine",
          "block_efficientkan", "block_efficientkan_kanmlp",
-         "vit_vanilla", "vit_efficientkan", "vit_fast", "vit_sine", "vit_cheby"]
+         "vit_vanilla", "vit_efficientkan", "vit_fast", "vit_sine", "vit_cheby", "vit_flash-attn"]
 
 
 @pytest.mark.parametrize("case", CASES)
@@ -256,3 +256,77 @@ def test_full_size_row_independence_cfg2():
         if p.grad is None or g_full[k].abs().max() < 1e-6:
             continue
         assert relerr(p.grad, g_full[k]) < 1e-4, k
+
+
+# ---- FlashAttention module / type="flash-attn"  ----
+
+FLASH = ["flash_self", "flash_keymask", "flash_causal", "flash_cross_causal", "flash_cross_mask",
+         "flash_fullmask_causal_buckets"]
+
+
+@pytest.mark.parametrize("case", FLASH)
+def test_flash_attention_matches_reference_golden(case):
+    import kan_vit_b200 as K
+    g = load_golden(case)
+    m = K.FlashAttention(dim=16, heads=2, dim_head=8, causal=bool(g.raw["causal"]))
+    m.load_state_dict(g.sd())
+    m = m.to(_dev())
+    x = g.t("x", _dev()).requires_grad_(True)
+    ctx = g.t("context", _dev()) if "context" in g.raw else None
+    mask = g.t("mask", _dev()) if "mask" in g.raw else None
+    y = m(x, context=ctx, mask=mask, q_bucket_size=3, k_bucket_size=2)
+    assert relerr(y, g.t("y")) < TOL_FP32
+    y.backward(g.t("dy", _dev()))
+    assert relerr(x.grad, g.t("gx")) < TOL_GRAD
+    params = dict(m.named_parameters())
+    for k, ref in g.grads().items():
+        assert grad_close(params[k].grad, ref), (k, relerr(params[k].grad, ref))
+
+
+@pytest.mark.parametrize("Nq,Nk,H,dh,causal,masked", [(197, 197, 3, 64, False, False), (197, 197, 2, 64, True, True),
+                                                      (50, 120, 4, 32, True, False), (130, 40, 2, 24, False, True),
+                                                      (1, 1, 1, 8, True, False)])
+def test_flash_attention_vs_oracle(Nq, Nk, H, dh, causal, masked):
+    import kan_vit_b200 as K
+    from oracle import kan_oracle as O
+    torch.manual_seed(Nq + Nk)
+    B, dim = 3, 48
+    m = K.FlashAttention(dim=dim, heads=H, dim_head=dh, causal=causal)
+    x = torch.randn(B, Nq, dim)
+    ctx = torch.randn(B, Nk, dim) if Nk != Nq else None
+    mask = None
+    if masked:
+        mask = torch.rand(B, Nk) < 0.8
+        mask[0, : Nk // 2] = False
+    dy = torch.randn(B, Nq, dim)
+    sd = {k: v.detach().clone().requires_grad_(True) for k, v in m.state_dict().items()}
+    xo = x.clone().requires_grad_(True)
+    yo = O.flash_attention_forward(xo, sd, "", H, context=ctx, mask=mask, causal=causal)
+    yo.backward(dy)
+    m = m.to(_dev())
+    xg = x.to(_dev()).requires_grad_(True)
+    y = m(xg, context=None if ctx is None else ctx.to(_dev()), mask=None if mask is None else mask.to(_dev()))
+    assert relerr(y, yo) < TOL_FP32
+    y.backward(dy.to(_dev()))
+    assert relerr(xg.grad, xo.grad) < TOL_GRAD
+    for k, p in m.named_parameters():
+        if sd[k].grad.abs().max() < 1e-6:      # analytically zero (a single key: softmax = 1, no q / k gradient)
+            assert p.grad.abs().max().item() < 1e-5, k
+            continue
+        assert grad_close(p.grad, sd[k].grad), (k, relerr(p.grad, sd[k].grad))
+
+
+def test_flash_attention_api_like_reference():
+    import kan_vit_b200 as K
+    with pytest.raises(TypeError):
+        K.FlashAttention(16)                      # keyword-only, attention.py:14-16
+    m = K.FlashAttention(dim=16)
+    assert m.to_q.weight.shape == (512, 16) and m.to_kv.weight.shape == (1024, 16) and m.to_out.weight.shape == (16, 512)
+    assert m.to_q.bias is None and m.to_out.bias is None
+    v = K.VisionTransformer((1, 8, 8), n_patches=2, n_blocks=2, d_hidden=16, n_heads=2, out_d=10, type="flash-attn")
+    assert sorted(k for k in v.state_dict() if k.startswith("blocks.0")) == [
+        "blocks.0.to_kv.weight", "blocks.0.to_out.weight", "blocks.0.to_q.weight"]
+    v = v.to(_dev())
+    with K.precision("bf16"):
+        y = v(torch.randn(4, 1, 8, 8, device=_dev()))
+    assert y.shape == (4, 10) and torch.isfinite(y).all()

@@ -138,3 +138,28 @@ def test_adam_restatement_matches_torch():
         opt.step()
         pn, m, v = O.adam_step_np(pn, grad.numpy(), m, v, t, lr=1e-2)
         assert np.abs(pn - p.detach().numpy()).max() <= 2e-6 * np.abs(pn).max()
+
+
+FLASH = ["flash_self", "flash_keymask", "flash_causal", "flash_cross_causal", "flash_cross_mask",
+         "flash_fullmask_causal_buckets"]
+
+
+@pytest.mark.parametrize("case", FLASH)
+def test_flash_attention_matches_reference(case):
+    """FlashAttention module (attention.py:13-109) incl. its custom backward (utils.py:229-295): key mask with a
+    fully hidden sample, causal, more keys than queries (uniform rows), full mask with non-default buckets."""
+    g = load_golden(case)
+    sd = _leafify(g.sd())
+    x = g.t("x").requires_grad_(True)
+    ctx = g.t("context") if "context" in g.raw else None
+    mask = g.t("mask") if "mask" in g.raw else None
+    y = O.flash_attention_forward(x, sd, "", 2, context=ctx, mask=mask, causal=bool(g.raw["causal"]))
+    _check(g, y, x, sd, tol=5e-6)
+
+
+def test_vit_flash_attn_matches_reference():
+    g = load_golden("vit_flash-attn")
+    sd = _leafify(g.sd())
+    x = g.t("x").requires_grad_(True)
+    y = O.vit_forward(x, sd, n_patches=2, n_blocks=2, n_heads=2, kind="flash-attn")
+    _check(g, y, x, sd, tol=1e-5)
