@@ -274,7 +274,20 @@ int kv_scatter_rows(const float* dY, float* dX, int B, int row_stride, int d, vo
  * [0, n_classes) makes the loss NaN. */
 int kv_cross_entropy_workspace_floats(void);
 int kv_cross_entropy(const float* logits, const long long* labels, int B, int n_classes,
-                     long long ignore_index, float* loss, float* dlogits, float* workspace, void* stream);
+                     long long ignore_index, float* loss, float* dlogits, float* workspace, float* probs,
+                     long long* pred, int* confusion, void* stream);
+/* The three nullable outputs serve the per-step metric collection of train.py:42-44,74-76 without a host
+ * round trip: probs [B][n_classes] = softmax(logits) (y_pred_proba), pred [B] = argmax (lowest index on
+ * ties, like torch.argmax), confusion [n_classes][n_classes] int32 += 1 at (label, pred) -- accuracy,
+ * balanced accuracy and weighted F1 (utils.py:38-40) are functions of that matrix, read once per epoch.
+ *
+ * The training transform of train.py:99-104 (RandomHorizontalFlip -> RandomCrop(H, padding=pad) -> ToTensor ->
+ * Normalize(mean, std)) from the dataset's uint8 [B][H][W][C] pixels to the fp32 [B][C][H][W] batch:
+ * flip [B] bytes (nullable = none), top/left [B] crop offsets in [0, 2*pad] (nullable = centred, i.e. the
+ * test transform of train.py:106-109), mean/stdv [C] device floats.  The random draws are the caller's. */
+int kv_image_augment(const unsigned char* images_hwc, const unsigned char* flip, const int* top, const int* left,
+                     int B, int H, int W, int C, int pad, const float* mean, const float* stdv, float* out,
+                     void* stream);
 
 /* torch.optim.Adam(params, lr) of train.py:23,39-40 (betas/eps arguments, no weight decay, no amsgrad)
  * over FLAT buffers holding every parameter of the model: one launch for the whole model instead of

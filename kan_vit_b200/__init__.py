@@ -9,7 +9,8 @@ from . import _lib  # noqa: F401
 from .attention import MSA, FlashAttention
 from .model import TransformerBlock, VisionTransformer
 from .ops import get_precision, precision, set_precision
+from .metrics import EpochMetrics
 from .models import (ChebyKANLayer, FastKANLayer, KANLinear, NaiveFourierKANLayer, SineKANLayer)
 
 __all__ = ["MSA", "FlashAttention", "TransformerBlock", "VisionTransformer", "KANLinear", "ChebyKANLayer", "FastKANLayer",
-           "SineKANLayer", "NaiveFourierKANLayer", "set_precision", "get_precision", "precision"]
+           "SineKANLayer", "NaiveFourierKANLayer", "set_precision", "get_precision", "precision", "EpochMetrics"]

@@ -74,7 +74,8 @@ _SIGNATURES = {
     "kv_gather_rows": [_P, _P, _I, _I, _I, _P],
     "kv_scatter_rows": [_P, _P, _I, _I, _I, _P],
     "kv_cross_entropy_workspace_floats": [],
-    "kv_cross_entropy": [_P, _P, _I, _I, C.c_longlong, _P, _P, _P, _P],
+    "kv_cross_entropy": [_P, _P, _I, _I, C.c_longlong, _P, _P, _P, _P, _P, _P, _P],
+    "kv_image_augment": [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P],
     "kv_adam_step": [_P, _P, _P, _P, C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _I,
                      _P, _P],
 }

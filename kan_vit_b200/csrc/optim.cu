@@ -67,7 +67,8 @@ constexpr int CE_MAX_BLOCKS = 148;
 __global__ void __launch_bounds__(CE_THREADS)
 cross_entropy_kernel(const float* __restrict__ Z, const long long* __restrict__ labels, int B, int Cn,
                      long long ignore_index, float* __restrict__ loss, float* __restrict__ dZ,
-                     float* __restrict__ workspace) {
+                     float* __restrict__ workspace, float* __restrict__ probs, long long* __restrict__ pred,
+                     int* __restrict__ confusion) {
   __shared__ float red[CE_WARPS];
   __shared__ int cnt[CE_WARPS];
   __shared__ int is_last;
@@ -88,13 +89,31 @@ cross_entropy_kernel(const float* __restrict__ Z, const long long* __restrict__ 
     const float* z = Z + (size_t)r * Cn;
     const long long y = labels[r];
     float mx = -INFINITY;
-    for (int j = lane; j < Cn; j += 32) mx = fmaxf(mx, z[j]);
+    int arg = 0x7fffffff;
+    for (int j = lane; j < Cn; j += 32) {
+      if (z[j] > mx) { mx = z[j]; arg = j; }   // strict: the lowest index of a lane's maximum
+    }
+    const float lane_mx = mx;
     mx = warp_max(mx);
+    if (pred || confusion) {
+      // torch.argmax (train.py:43): lowest index attaining the row maximum
+      int cand = lane_mx == mx ? arg : 0x7fffffff;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, o));
+      if (lane == 0) {
+        if (pred) pred[r] = cand;
+        if (confusion && y >= 0 && y < Cn && cand < Cn) atomicAdd(confusion + (size_t)y * Cn + cand, 1);
+      }
+    }
     float s = 0.0f;
     for (int j = lane; j < Cn; j += 32) s += __expf(z[j] - mx);
     s = warp_sum(s);
     const bool valid = y != ignore_index;
     const float inv_s = 1.0f / s;
+    if (probs) {  // softmax(y_hat, dim=1), train.py:44
+      float* pr = probs + (size_t)r * Cn;
+      for (int j = lane; j < Cn; j += 32) pr[j] = __expf(z[j] - mx) * inv_s;
+    }
     if (dZ) {
       float* dz = dZ + (size_t)r * Cn;
       for (int j = lane; j < Cn; j += 32) {
@@ -124,6 +143,36 @@ cross_entropy_kernel(const float* __restrict__ Z, const long long* __restrict__ 
     // torch: an all-ignored batch gives nan (0 / 0)
     *loss = n_valid > 0 ? total * inv_n : __int_as_float(0x7fc00000);
     *reinterpret_cast<unsigned*>(workspace) = 0u;
+  }
+}
+
+// ------------------------------------------------------------------------------
+// The training transform of train.py:99-104 on the GPU: RandomHorizontalFlip -> RandomCrop(size, padding)
+// -> ToTensor -> Normalize, from the dataset's uint8 HWC pixels to the fp32 CHW batch the model reads.
+// The random draws (flip, crop offsets in [0, 2*pad]) are made by the caller.  Padding is zero BEFORE
+// ToTensor, so a padded pixel becomes (0 - mean) / std.
+//   out[b,c,y,x] = (P(y + top_b, x + left_b) / 255 - mean_c) / std_c,
+//   P(r, q) = 0 outside [pad, pad+H) x [pad, pad+W), else src[b, r-pad, flip ? W-1-(q-pad) : q-pad, c]
+// ------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+augment_kernel(const unsigned char* __restrict__ src, const unsigned char* __restrict__ flip,
+               const int* __restrict__ top, const int* __restrict__ left, int B, int H, int W, int Cc, int pad,
+               const float* __restrict__ mean, const float* __restrict__ stdv, float* __restrict__ out) {
+  const long long total = (long long)B * Cc * H * W;
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total;
+       p += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(p % W);
+    const int y = (int)((p / W) % H);
+    const int c = (int)((p / ((long long)W * H)) % Cc);
+    const int b = (int)(p / ((long long)W * H * Cc));
+    const int r = y + (top ? top[b] : pad) - pad;
+    int q = x + (left ? left[b] : pad) - pad;
+    float v = 0.0f;
+    if (r >= 0 && r < H && q >= 0 && q < W) {
+      if (flip && flip[b]) q = W - 1 - q;
+      v = (float)src[(((size_t)b * H + r) * W + q) * Cc + c] / 255.0f;
+    }
+    out[p] = (v - mean[c]) / stdv[c];
   }
 }
 
@@ -157,14 +206,30 @@ int kv_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, l
 int kv_cross_entropy_workspace_floats(void) { return 1 + CE_MAX_BLOCKS; }
 
 int kv_cross_entropy(const float* logits, const long long* labels, int B, int n_classes,
-                     long long ignore_index, float* loss, float* dlogits, float* workspace, void* stream) {
+                     long long ignore_index, float* loss, float* dlogits, float* workspace, float* probs,
+                     long long* pred, int* confusion, void* stream) {
   if (B <= 0 || n_classes <= 0) return KV_ERR_BAD_ARG;
   if (!logits || !labels || !loss || !workspace) return KV_ERR_BAD_ARG;
   int grid = ceil_div(B, CE_WARPS);
   if (grid > CE_MAX_BLOCKS) grid = CE_MAX_BLOCKS;
   cross_entropy_kernel<<<grid, CE_THREADS, 0, (cudaStream_t)stream>>>(logits, labels, B, n_classes, ignore_index,
-                                                                     loss, dlogits, workspace);
+                                                                     loss, dlogits, workspace, probs, pred,
+                                                                     confusion);
   KV_CHECK_LAUNCH("cross_entropy_kernel");
+  return KV_OK;
+}
+
+int kv_image_augment(const unsigned char* images_hwc, const unsigned char* flip, const int* top, const int* left,
+                     int B, int H, int W, int C, int pad, const float* mean, const float* stdv, float* out,
+                     void* stream) {
+  if (B < 0 || H <= 0 || W <= 0 || C <= 0 || pad < 0) return KV_ERR_BAD_ARG;
+  if (B == 0) return KV_OK;
+  if (!images_hwc || !mean || !stdv || !out) return KV_ERR_BAD_ARG;
+  const long long total = (long long)B * C * H * W;
+  const long long want = (total + 255) / 256;
+  const int grid = (int)(want < 148 * 8 ? want : 148 * 8);
+  augment_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(images_hwc, flip, top, left, B, H, W, C, pad, mean, stdv, out);
+  KV_CHECK_LAUNCH("augment_kernel");
   return KV_OK;
 }
 

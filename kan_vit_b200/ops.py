@@ -477,19 +477,27 @@ def _ce_workspace(device):
     return ws
 
 
-def cross_entropy_with_grad(logits, labels, ignore_index=-100, need_grad=True):
+def cross_entropy_with_grad(logits, labels, ignore_index=-100, need_grad=True, probs_out=None, pred_out=None,
+                            confusion=None):
     """nn.CrossEntropyLoss() (train.py:22,36) and its gradient w.r.t. the logits in ONE pass:
-    returns (loss: 0-dim tensor, dlogits or None).  labels: int64 class indices."""
+    returns (loss: 0-dim tensor, dlogits or None).  labels: int64 class indices.
+    Optional metric outputs written by the same launch (train.py:42-44): ``probs_out`` [B, C] fp32 softmax,
+    ``pred_out`` [B] int64 argmax, ``confusion`` [C, C] int32 counts incremented at (label, prediction)."""
     lib = L.load()
     _require_cuda(logits, labels)
     assert logits.dim() == 2 and logits.dtype == torch.float32
     assert labels.shape == (logits.shape[0],) and labels.dtype == torch.int64
     logits, labels = logits.contiguous(), labels.contiguous()
     B, Cn = logits.shape
+    _require_cuda(probs_out, pred_out, confusion)
+    assert probs_out is None or (probs_out.shape == (B, Cn) and probs_out.dtype == torch.float32 and probs_out.is_contiguous())
+    assert pred_out is None or (pred_out.shape == (B,) and pred_out.dtype == torch.int64 and pred_out.is_contiguous())
+    assert confusion is None or (confusion.shape == (Cn, Cn) and confusion.dtype == torch.int32 and confusion.is_contiguous())
     loss = torch.empty((), dtype=torch.float32, device=logits.device)
     dz = torch.empty_like(logits) if need_grad else None
     _call("kv_cross_entropy", lib.kv_cross_entropy, logits.data_ptr(), labels.data_ptr(), B, Cn, int(ignore_index),
-          loss.data_ptr(), L.ptr(dz), _ce_workspace(logits.device).data_ptr(), _stream(), work=8.0 * B * Cn)
+          loss.data_ptr(), L.ptr(dz), _ce_workspace(logits.device).data_ptr(), L.ptr(probs_out), L.ptr(pred_out),
+          L.ptr(confusion), _stream(), work=8.0 * B * Cn)
     return loss, dz
 
 
@@ -578,3 +586,22 @@ def attention_general(q, k, v, B, Nq, Nk, H, dh, mask=None, causal=False):
             mask = mask.expand(*mask.shape[:-1], Nk).contiguous()
         mask = mask.expand(B, H, Nq, Nk)
     return _AttnGeneralFn.apply(q, k, v, mask, bool(causal), B, Nq, Nk, H, dh)
+
+
+def image_augment(images_u8_hwc, mean, std, pad=0, flip=None, top=None, left=None):
+    """The transform of train.py:99-109 on the GPU: uint8 [B, H, W, C] -> fp32 [B, C, H, W]
+    (horizontal flip where ``flip`` [B] bool/uint8 is set, zero padding ``pad`` and a crop at offsets
+    ``top`` / ``left`` [B] int32 in [0, 2*pad], /255, (v - mean) / std).  flip/top/left None = the test transform."""
+    lib = L.load()
+    _require_cuda(images_u8_hwc, mean, std, flip, top, left)
+    assert images_u8_hwc.dtype == torch.uint8 and images_u8_hwc.dim() == 4 and images_u8_hwc.is_contiguous()
+    B, H, W, Cc = images_u8_hwc.shape
+    assert mean.numel() == Cc and std.numel() == Cc and mean.dtype == torch.float32 and std.dtype == torch.float32
+    if flip is not None:
+        flip = flip.to(torch.uint8).contiguous()
+    for t in (top, left):
+        assert t is None or (t.dtype == torch.int32 and t.shape == (B,) and t.is_contiguous())
+    out = torch.empty((B, Cc, H, W), dtype=torch.float32, device=images_u8_hwc.device)
+    _call("kv_image_augment", lib.kv_image_augment, images_u8_hwc.data_ptr(), L.ptr(flip), L.ptr(top), L.ptr(left),
+          B, H, W, Cc, pad, mean.data_ptr(), std.data_ptr(), out.data_ptr(), _stream(), work=5.0 * B * Cc * H * W)
+    return out

@@ -140,12 +140,17 @@ class TrainStep:
     """One training iteration of a model on this rank's batch shard."""
 
     def __init__(self, model: torch.nn.Module, lr: float = 1e-3, bucket_bytes: int = 32 << 20,
-                 optimizer: Optional[torch.optim.Optimizer] = None, cuda_graph: bool = False):
+                 optimizer: Optional[torch.optim.Optimizer] = None, cuda_graph: bool = False, metrics=None):
         """``cuda_graph=True`` (single-GPU, CUDA only): after three eager warm-up calls the whole
         iteration (zero_grad .. Adam) is captured once into a CUDA graph and replayed, which removes
         the launch-bound host time of the small configurations (thousands of launches of a few
         microseconds each).  Inputs are copied into static buffers; shapes must not change."""
         self.model = model
+        # metrics: a kan_vit_b200.metrics.EpochMetrics; the loss launch then also records the batch's
+        # probabilities / predictions / confusion counts on the device (train.py:42-44)
+        self.metrics = metrics
+        if metrics is not None and cuda_graph:
+            raise ValueError("metric collection advances host-side offsets every step and cannot be graph-captured")
         params = [p for p in model.parameters() if p.requires_grad]
         self.grads = FlatGradBuckets(params, bucket_bytes)
         self.cuda_graph = bool(cuda_graph) and params[0].is_cuda and self.grads.world == 1
@@ -170,7 +175,10 @@ class TrainStep:
         logits = self.model(images)
         if images.is_cuda:
             from . import ops
-            loss, dlogits = ops.cross_entropy_with_grad(logits.detach(), labels)
+            if self.metrics is not None:
+                loss, dlogits = self.metrics.loss_and_grad(logits.detach(), labels)
+            else:
+                loss, dlogits = ops.cross_entropy_with_grad(logits.detach(), labels)
             ops.GRAD_SINK = self.grads
             try:
                 logits.backward(dlogits)

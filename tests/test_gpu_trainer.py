@@ -144,3 +144,87 @@ def test_fused_step_follows_torch_loss_and_adam(kind):
     sd = ma.state_dict()
     mc = _model(kind, dev)
     mc.load_state_dict(sd)                                  # strict: names and shapes unchanged by the re-homing
+
+
+# ---- metric collection and the input transform on the device ----
+
+def test_cross_entropy_metric_outputs():
+    from kan_vit_b200 import ops
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(9)
+    B, Cn = 513, 100
+    z = 3.0 * torch.randn(B, Cn, generator=g)
+    z[5, 7] = z[5, 3] = z[5].max() + 1.0                  # a tie: torch.argmax takes the lowest index
+    y = torch.randint(0, Cn, (B,), generator=g)
+    probs = torch.empty(B, Cn, device=dev)
+    pred = torch.empty(B, dtype=torch.int64, device=dev)
+    conf = torch.zeros(Cn, Cn, dtype=torch.int32, device=dev)
+    for _ in range(2):                                    # counts accumulate over steps
+        ops.cross_entropy_with_grad(z.to(dev), y.to(dev), probs_out=probs, pred_out=pred, confusion=conf)
+    assert (probs.cpu() - torch.softmax(z, 1)).abs().max().item() <= 1e-6
+    assert torch.equal(pred.cpu(), torch.argmax(z, 1)) and pred[5].item() == 3
+    ref = torch.zeros(Cn, Cn, dtype=torch.int32)
+    ref.index_put_((y, torch.argmax(z, 1)), torch.ones(B, dtype=torch.int32), accumulate=True)
+    assert torch.equal(conf.cpu(), 2 * ref)
+
+
+def test_epoch_metrics_match_reference_recipe():
+    """EpochMetrics over a short run equals utils.calculate_metrics' sklearn calls on the per-step host lists."""
+    from sklearn.metrics import accuracy_score, balanced_accuracy_score, f1_score, roc_auc_score
+    from kan_vit_b200.metrics import EpochMetrics
+    from kan_vit_b200.trainer import TrainStep
+    dev = torch.device("cuda:0")
+    m = _model("vanilla", dev)
+    em = EpochMetrics(10, 64, dev)
+    step = TrainStep(m, lr=1e-3, metrics=em)
+    y_true, y_pred, y_proba, losses = [], [], [], []
+    g = torch.Generator().manual_seed(2)
+    for _ in range(4):
+        x = torch.randn(16, 1, 28, 28, generator=g).to(dev)
+        y = torch.randint(0, 10, (16,), generator=g).to(dev)
+        with torch.no_grad():
+            y_hat = m(x)                                   # what the step is about to see (train.py:33)
+        losses.append(float(step(x, y)))
+        y_true.extend(y.cpu().numpy())
+        y_pred.extend(torch.argmax(y_hat, dim=1).cpu().numpy())
+        y_proba.extend(torch.softmax(y_hat, dim=1).cpu().numpy())
+    out = em.compute()
+    assert abs(out["loss"] - sum(losses) / 4) < 1e-6
+    assert abs(out["accuracy"] - accuracy_score(y_true, y_pred)) < 1e-12
+    assert abs(out["balanced_accuracy"] - balanced_accuracy_score(y_true, y_pred)) < 1e-12
+    assert abs(out["f1"] - f1_score(y_true, y_pred, average="weighted")) < 1e-12
+    onehot = torch.nn.functional.one_hot(torch.tensor(y_true), num_classes=10).numpy()
+    assert abs(out["roc_auc"] - roc_auc_score(onehot, y_proba, average="weighted", multi_class="ovr")) < 1e-6
+
+
+@pytest.mark.parametrize("train", [True, False])
+def test_image_augment_matches_torchvision(train):
+    """train.py:99-109: RandomHorizontalFlip -> RandomCrop(32, padding=4) -> ToTensor -> Normalize, with the
+    random draws fixed; bit-for-bit the torchvision arithmetic up to one rounding of the division."""
+    tvf = pytest.importorskip("torchvision.transforms.functional")
+    from kan_vit_b200 import ops
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(5)
+    B, H, W, Cc, pad = 9, 32, 32, 3, 4
+    img = torch.randint(0, 256, (B, H, W, Cc), dtype=torch.uint8, generator=g)
+    mean, std = [0.5071, 0.4867, 0.4408], [0.2675, 0.2565, 0.2761]
+    flip = torch.rand(B, generator=g) < 0.5
+    top = torch.randint(0, 2 * pad + 1, (B,), generator=g, dtype=torch.int32)
+    left = torch.randint(0, 2 * pad + 1, (B,), generator=g, dtype=torch.int32)
+    top[0], left[0], top[1], left[1] = 0, 0, 2 * pad, 2 * pad
+    ref = []
+    for b in range(B):
+        t = img[b].permute(2, 0, 1)                         # uint8 CHW, what PIL -> the transforms see
+        if train:
+            if flip[b]:
+                t = tvf.hflip(t)
+            t = tvf.crop(tvf.pad(t, pad), int(top[b]), int(left[b]), H, W)
+        ref.append(tvf.normalize(t.float().div(255), mean, std))
+    ref = torch.stack(ref)
+    md, sd = torch.tensor(mean, device=dev), torch.tensor(std, device=dev)
+    if train:
+        out = ops.image_augment(img.to(dev), md, sd, pad=pad, flip=flip.to(dev), top=top.to(dev), left=left.to(dev))
+    else:
+        out = ops.image_augment(img.to(dev), md, sd)
+    assert out.shape == (B, Cc, H, W)
+    assert (out.cpu() - ref).abs().max().item() <= 1e-6

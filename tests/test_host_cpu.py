@@ -42,8 +42,9 @@ def test_bad_arguments_return_codes_without_a_gpu():
     assert lib.kv_kan_fwd(C.byref(d), 1, 1, None, 1, None, None, None, None, None, 1, None) == -3
     assert lib.kv_patchify(1, 1, 2, 1, 28, 28, 5, None) == -2  # 28 % 5 != 0 (model.py:58-59)
     assert lib.kv_attn_fwd(1, None, 1, 1, 1, 50, 2, 4096, None) == -2
-    assert lib.kv_cross_entropy(1, 1, 0, 10, -100, 1, 1, 1, None) == -1      # empty batch
-    assert lib.kv_cross_entropy(None, 1, 4, 10, -100, 1, 1, 1, None) == -1   # null logits
+    assert lib.kv_cross_entropy(1, 1, 0, 10, -100, 1, 1, 1, None, None, None, None) == -1      # empty batch
+    assert lib.kv_cross_entropy(None, 1, 4, 10, -100, 1, 1, 1, None, None, None, None) == -1   # null logits
+    assert lib.kv_image_augment(None, None, None, None, 2, 32, 32, 3, 4, 1, 1, 1, None) == -1
     assert lib.kv_adam_step(16, 16, 16, 16, 6, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, 16, None) == -1   # n % 4
     assert lib.kv_adam_step(16, 20, 16, 16, 8, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, 16, None) == -4   # alignment
     assert lib.kv_adam_step(None, None, None, None, 0, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, None, None) == 0
@@ -149,3 +150,21 @@ def test_tensor_core_coverage_table():
                      (KanSpec(L.KV_FASTKAN, 24, 24, n_groups=24, x_share=3, grid_size=8), 0)):
         rc, fwd, bwd_in, dyimg = sizes(spec, flags=fl)
         assert rc == 0 and fwd > 0 and bwd_in > 0 and dyimg > 0
+
+
+def test_metrics_from_confusion_match_sklearn():
+    """utils.py:38-40: accuracy / balanced accuracy / weighted F1 are recomputed from a confusion matrix."""
+    import numpy as np
+    from sklearn.metrics import accuracy_score, balanced_accuracy_score, f1_score
+    from kan_vit_b200.metrics import metrics_from_confusion
+    rng = np.random.default_rng(0)
+    for n_classes, n in ((10, 500), (100, 3000), (5, 40)):
+        y = rng.integers(0, n_classes, n)
+        y[y == 3] = 2                                    # a class without samples that is still predicted
+        p = np.where(rng.random(n) < 0.6, y, rng.integers(0, n_classes, n))
+        conf = np.zeros((n_classes, n_classes), np.int64)
+        np.add.at(conf, (y, p), 1)
+        acc, bal, f1 = metrics_from_confusion(conf)
+        assert abs(acc - accuracy_score(y, p)) < 1e-12
+        assert abs(bal - balanced_accuracy_score(y, p)) < 1e-12
+        assert abs(f1 - f1_score(y, p, average="weighted")) < 1e-12
