@@ -109,9 +109,37 @@ def flash_cases():
     print(f"vit_flash-attn: y{tuple(y.shape)}")
 
 
+def maintenance_case():
+    """KANLinear.update_grid / curve2coeff / regularization_loss (models/effkan.py:134-264):
+    python oracle/make_golden.py --maint-only"""
+    sys.path.insert(0, REF)
+    from models.effkan import KANLinear  # noqa
+    torch.manual_seed(80)
+    m = KANLinear(6, 5)
+    g = torch.Generator().manual_seed(81)
+    x = torch.randn(64, 6, generator=g) * torch.tensor([0.3, 0.6, 1.0, 1.5, 0.8, 0.2]) + torch.tensor([0., .2, -.3, 0., .5, 0.])
+    probe = torch.randn(16, 6, generator=g) * 0.5
+    rec = {"x": _np(x), "probe": _np(probe)}
+    for k, v in m.state_dict().items():
+        rec["sd/" + k] = _np(v).copy()      # update_grid below writes these tensors in place
+    rec["reg_before"] = _np(m.regularization_loss(1.0, 1.0))
+    rec["y_before"] = _np(m(probe))
+    m.update_grid(x)
+    rec["grid_after"] = _np(m.grid)
+    rec["spline_weight_after"] = _np(m.spline_weight)
+    rec["reg_after"] = _np(m.regularization_loss(0.5, 2.0))
+    rec["y_after"] = _np(m(probe))
+    rec["y_after_x"] = _np(m(x))
+    np.savez_compressed(os.path.join(OUT, "maint_effkan.npz"), **rec)
+    print("maint_effkan:", {k: v.shape for k, v in rec.items() if not k.startswith("sd/")})
+
+
 def main():
     if "--flash-only" in sys.argv:
         flash_cases()
+        return
+    if "--maint-only" in sys.argv:
+        maintenance_case()
         return
     sys.path.insert(0, REF)
     import model as ref_model  # noqa
@@ -238,6 +266,7 @@ def main():
     with open(os.path.join(OUT, "state_dict_keys.json"), "w") as f:
         json.dump(keys, f, indent=0, sort_keys=True)
     flash_cases()
+    maintenance_case()
     print("done")
 
 

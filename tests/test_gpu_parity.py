@@ -330,3 +330,26 @@ def test_flash_attention_api_like_reference():
     with K.precision("bf16"):
         y = v(torch.randn(4, 1, 8, 8, device=_dev()))
     assert y.shape == (4, 10) and torch.isfinite(y).all()
+
+
+@pytest.mark.parametrize("mode,tol", [("fp32", 2e-4), ("bf16", 2e-2)])
+def test_update_grid_on_device_then_forward(mode, tol):
+    """the maintenance ops run on the device (torch sort / lstsq on CUDA tensors) and the
+    kernels honour the adapted, per-feature non-uniform grid: outputs against the reference's after update_grid.
+    (The refit is a least-squares solve, so the fp32 tolerance is the solve's, not the kernel's 1e-5; the kernel
+    itself is compared at 1e-5 with the reference's own refit weights loaded.)"""
+    import kan_vit_b200 as K
+    g = load_golden("maint_effkan")
+    m = K.KANLinear(6, 5)
+    m.load_state_dict(g.sd())
+    m = m.to(_dev())
+    with K.precision(mode):
+        assert relerr(m(g.t("probe", _dev())), g.t("y_before")) < (TOL_FP32 if mode == "fp32" else tol)
+        m.update_grid(g.t("x", _dev()))
+        assert relerr(m.grid, g.t("grid_after")) < 1e-6
+        # the refit reproduces the layer on the samples it was fitted to (update_grid's contract)
+        assert relerr(m(g.t("x", _dev())), g.t("y_after_x")) < tol
+        assert relerr(m(g.t("probe", _dev())), g.t("y_after")) < 10 * tol
+        with torch.no_grad():
+            m.spline_weight.copy_(g.t("spline_weight_after", _dev()))
+        assert relerr(m(g.t("probe", _dev())), g.t("y_after")) < (TOL_FP32 if mode == "fp32" else tol)

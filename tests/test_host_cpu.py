@@ -168,3 +168,19 @@ def test_metrics_from_confusion_match_sklearn():
         assert abs(acc - accuracy_score(y, p)) < 1e-12
         assert abs(bal - balanced_accuracy_score(y, p)) < 1e-12
         assert abs(f1 - f1_score(y, p, average="weighted")) < 1e-12
+
+
+def test_kanlinear_maintenance_ops_match_reference():
+    """update_grid / curve2coeff / regularization_loss of the drop-in KANLinear (plain torch, device-agnostic)
+    against values recorded from the reference (models/effkan.py:134-264)."""
+    from conftest import load_golden, relerr
+    import kan_vit_b200 as K
+    g = load_golden("maint_effkan")
+    m = K.KANLinear(6, 5)
+    m.load_state_dict(g.sd())
+    assert abs(float(m.regularization_loss(1.0, 1.0)) - float(g.raw["reg_before"])) < 1e-5 * abs(float(g.raw["reg_before"]))
+    m.update_grid(g.t("x"))
+    assert relerr(m.grid, g.t("grid_after")) < 1e-6
+    assert relerr(m.spline_weight, g.t("spline_weight_after")) < 1e-3      # lstsq: conditioning of the refit
+    assert abs(float(m.regularization_loss(0.5, 2.0)) - float(g.raw["reg_after"])) < 1e-4 * abs(float(g.raw["reg_after"]))
+    assert not m.grid_is_uniform()
