@@ -308,12 +308,20 @@ def run_gpu_arm(args):
     loss_evt = [torch.cuda.Event() for _ in range(2)]
     e2e_losses = []
 
+    from kan_vit_b200.trainer import BatchPrefetcher
+    feeder = BatchPrefetcher(dev, host_img[0], host_lab[0])
+
     def e2e_step(i):
-        # the call a user makes: host batch in (pinned -> device), loss value out.  The loss of every step
-        # is copied to pinned host memory and read on the host one step later, so the device->host read
-        # does not drain the launch queue (the usual way a training loop logs its loss).
-        x = host_img[i % n_host].to(dev, non_blocking=True)
-        y = host_lab[i % n_host].to(dev, non_blocking=True)
+        # the call a user makes: host batch in (pinned -> device), loss value out.  Every step's batch is
+        # copied from pinned host memory inside the timed region -- batch 0 right here, batch i+1 on the copy
+        # stream while step i computes (trainer.BatchPrefetcher, what DataLoader(pin_memory=True) + .to(device)
+        # do in train.py).  The loss of every step is copied to pinned host memory and read on the host one
+        # step later, so the device->host read does not drain the launch queue (the usual logging pattern).
+        if i == 0:
+            feeder.submit(host_img[0], host_lab[0])
+        x, y = feeder.next()
+        if i + 1 < args.steps:
+            feeder.submit(host_img[(i + 1) % n_host], host_lab[(i + 1) % n_host])
         loss = step(x, y)
         k = i % 2
         loss_host[k].copy_(loss, non_blocking=True)

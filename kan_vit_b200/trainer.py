@@ -136,6 +136,50 @@ class FlatAdam:
         self.lr, self.betas, self.eps = float(sd["lr"]), tuple(sd["betas"]), float(sd["eps"])
 
 
+class BatchPrefetcher:
+    """Host batches to the device one step ahead of the compute (the job of the reference's
+    ``DataLoader(pin_memory=True)`` + ``x.to(device)``, train.py:31-32,115-116).
+
+    Two static device slots; ``submit`` copies a pinned host batch into the free slot on a copy stream,
+    ``next`` makes the compute stream wait for the oldest submitted batch and returns its device tensors.
+    The copy of batch i+1 therefore runs under the kernels of step i.  Stream-ordered only: no host sync."""
+
+    def __init__(self, device, images_like: torch.Tensor, labels_like: torch.Tensor):
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(self.device)
+        self.img = [torch.empty(images_like.shape, dtype=images_like.dtype, device=self.device) for _ in range(2)]
+        self.lab = [torch.empty(labels_like.shape, dtype=labels_like.dtype, device=self.device) for _ in range(2)]
+        self.ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self.consumed = [None, None]     # recorded on the compute stream once the NEXT batch is taken
+        self.head = self.tail = 0        # batches submitted / taken
+
+    def submit(self, images: torch.Tensor, labels: torch.Tensor):
+        if self.head - self.tail >= 2:
+            raise RuntimeError("both slots hold batches that have not been taken yet")
+        k = self.head % 2
+        if self.consumed[k] is not None:
+            self.stream.wait_event(self.consumed[k])   # the step that read this slot has finished
+        with torch.cuda.stream(self.stream):
+            self.img[k].copy_(images, non_blocking=True)
+            self.lab[k].copy_(labels, non_blocking=True)
+            self.ready[k].record(self.stream)
+        self.head += 1
+
+    def next(self):
+        if self.tail >= self.head:
+            raise RuntimeError("no batch submitted")
+        cur = torch.cuda.current_stream(self.device)
+        if self.tail > 0:
+            # everything queued so far on the compute stream (the previous step) read the previous slot
+            prev = (self.tail - 1) % 2
+            self.consumed[prev] = torch.cuda.Event()
+            self.consumed[prev].record(cur)
+        k = self.tail % 2
+        cur.wait_event(self.ready[k])
+        self.tail += 1
+        return self.img[k], self.lab[k]
+
+
 class TrainStep:
     """One training iteration of a model on this rank's batch shard."""
 

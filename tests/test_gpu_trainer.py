@@ -228,3 +228,34 @@ def test_image_augment_matches_torchvision(train):
         out = ops.image_augment(img.to(dev), md, sd)
     assert out.shape == (B, Cc, H, W)
     assert (out.cpu() - ref).abs().max().item() <= 1e-6
+
+
+def test_batch_prefetcher_feeds_the_same_batches():
+    """Batches copied one step ahead on the copy stream arrive intact and in order, slots are not overwritten
+    before the step that reads them has run, and training through the prefetcher equals training on resident data."""
+    from kan_vit_b200.trainer import BatchPrefetcher, TrainStep
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(11)
+    imgs = [torch.randn(8, 1, 28, 28, generator=g).pin_memory() for _ in range(5)]
+    labs = [torch.randint(0, 10, (8,), generator=g).pin_memory() for _ in range(5)]
+    losses = []
+    for prefetch in (False, True):
+        step = TrainStep(_model("efficientkan", dev), lr=1e-3)
+        out = []
+        if prefetch:
+            feeder = BatchPrefetcher(dev, imgs[0], labs[0])
+            feeder.submit(imgs[0], labs[0])
+            for i in range(5):
+                x, y = feeder.next()
+                if i + 1 < 5:
+                    feeder.submit(imgs[i + 1], labs[i + 1])
+                assert torch.equal(x.cpu(), imgs[i]) and torch.equal(y.cpu(), labs[i])
+                out.append(float(step(x, y)))
+            with pytest.raises(RuntimeError):
+                feeder.next()
+        else:
+            for x, y in zip(imgs, labs):
+                out.append(float(step(x.to(dev), y.to(dev))))
+        losses.append(out)
+    for a, b in zip(*losses):      # atomically accumulated gradient sums are not bit-reproducible run to run
+        assert abs(a - b) <= 1e-5 * abs(a)
