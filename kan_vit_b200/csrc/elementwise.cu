@@ -107,6 +107,161 @@ layernorm_bwd_kernel(const float* __restrict__ X, int ldx, const float* __restri
 }
 
 // ------------------------------------------------------------------------------
+// Register-resident variants for the plain nn.LayerNorm case with d % 4 == 0, d <= 1024 and 16-byte
+// aligned rows: a lane owns the float4 columns {lane + 32 k}, the row is read ONCE with 16-byte loads,
+// and (backward) the d gamma / d beta partial sums stay in registers across all rows a warp visits;
+// they meet in shared memory once per block and leave with one atomic per column per block.
+// ------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(LN_THREADS)
+layernorm_fwd_vec_kernel(const float* __restrict__ X, const float* __restrict__ gamma,
+                         const float* __restrict__ beta, float* __restrict__ Y, float* __restrict__ mean,
+                         float* __restrict__ rstd, int T, int d, int ldx, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int nv = d >> 2;
+  float4 gm[NV], bt[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int c = lane + 32 * k;
+    gm[k] = (gamma && c < nv) ? reinterpret_cast<const float4*>(gamma)[c] : make_float4(1.f, 1.f, 1.f, 1.f);
+    bt[k] = (beta && c < nv) ? reinterpret_cast<const float4*>(beta)[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const float inv_d = 1.0f / (float)d;
+  for (int t = blockIdx.x * LN_WARPS + (threadIdx.x >> 5); t < T; t += gridDim.x * LN_WARPS) {
+    const float4* x4 = reinterpret_cast<const float4*>(X + (size_t)t * ldx);
+    float4 x[NV];
+    float s = 0.0f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = lane + 32 * k;
+      x[k] = c < nv ? __ldcs(x4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      s += (x[k].x + x[k].y) + (x[k].z + x[k].w);
+    }
+    const float mu = warp_sum(s) * inv_d;
+    float sq = 0.0f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      if (lane + 32 * k < nv) {
+        const float a = x[k].x - mu, b = x[k].y - mu, c2 = x[k].z - mu, e = x[k].w - mu;
+        sq += (a * a + b * b) + (c2 * c2 + e * e);
+      }
+    }
+    const float rs = rsqrtf(warp_sum(sq) * inv_d + eps);
+    float4* y4 = reinterpret_cast<float4*>(Y + (size_t)t * d);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = lane + 32 * k;
+      if (c < nv) {
+        float4 o;
+        o.x = (x[k].x - mu) * rs * gm[k].x + bt[k].x;
+        o.y = (x[k].y - mu) * rs * gm[k].y + bt[k].y;
+        o.z = (x[k].z - mu) * rs * gm[k].z + bt[k].z;
+        o.w = (x[k].w - mu) * rs * gm[k].w + bt[k].w;
+        y4[c] = o;
+      }
+    }
+    if (lane == 0) {
+      if (mean) mean[t] = mu;
+      if (rstd) rstd[t] = rs;
+    }
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(LN_THREADS, 2)
+layernorm_bwd_vec_kernel(const float* __restrict__ X, int ldx, const float* __restrict__ dY,
+                         const float* __restrict__ gamma, const float* __restrict__ mean,
+                         const float* __restrict__ rstd, const float* __restrict__ dresidual,
+                         float* __restrict__ dX, float* __restrict__ dgamma, float* __restrict__ dbeta, int T,
+                         int d) {
+  // smem: gamma [d], then per-warp private partial sums [LN_WARPS][2][d] (plain loads/stores: a lane owns its
+  // columns), which keeps the register count low enough for two blocks per SM
+  extern __shared__ float4 ln_smem4[];
+  float* gamma_s = reinterpret_cast<float*>(ln_smem4);
+  float* acc_s = gamma_s + d;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nv = d >> 2;
+  for (int p = threadIdx.x; p < d; p += LN_THREADS) gamma_s[p] = gamma ? gamma[p] : 1.0f;
+  for (int p = threadIdx.x; p < LN_WARPS * 2 * d; p += LN_THREADS) acc_s[p] = 0.0f;
+  __syncthreads();
+  const float4* gm4 = reinterpret_cast<const float4*>(gamma_s);
+  float4* ag4 = reinterpret_cast<float4*>(acc_s + (size_t)warp * 2 * d);
+  float4* ab4 = ag4 + nv;
+  const bool want_params = dgamma != nullptr || dbeta != nullptr;
+  const float inv_d = 1.0f / (float)d;
+  for (int t = blockIdx.x * LN_WARPS + warp; t < T; t += gridDim.x * LN_WARPS) {
+    const float4* x4 = reinterpret_cast<const float4*>(X + (size_t)t * ldx);
+    const float4* g4 = reinterpret_cast<const float4*>(dY + (size_t)t * d);
+    const float4* r4 = dresidual ? reinterpret_cast<const float4*>(dresidual + (size_t)t * d) : nullptr;
+    float4 xh[NV], gg[NV], rr[NV];
+    // every load of the row is issued before the first use
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = lane + 32 * k;
+      const bool in = c < nv;
+      xh[k] = in ? __ldcs(x4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      gg[k] = in ? __ldcs(g4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      rr[k] = (in && r4) ? __ldcs(r4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const float mu = mean[t], rs = rstd[t];
+    float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = lane + 32 * k;
+      if (c < nv) {
+        const float4 g = gg[k];
+        xh[k] = make_float4((xh[k].x - mu) * rs, (xh[k].y - mu) * rs, (xh[k].z - mu) * rs, (xh[k].w - mu) * rs);
+        if (want_params) {
+          float4 a = ag4[c], b = ab4[c];
+          a.x = fmaf(g.x, xh[k].x, a.x); a.y = fmaf(g.y, xh[k].y, a.y);
+          a.z = fmaf(g.z, xh[k].z, a.z); a.w = fmaf(g.w, xh[k].w, a.w);
+          b.x += g.x; b.y += g.y; b.z += g.z; b.w += g.w;
+          ag4[c] = a;
+          ab4[c] = b;
+        }
+        const float4 gm = gm4[c];
+        gg[k] = make_float4(g.x * gm.x, g.y * gm.y, g.z * gm.z, g.w * gm.w);
+        s1 += (gg[k].x + gg[k].y) + (gg[k].z + gg[k].w);
+        s2 += (gg[k].x * xh[k].x + gg[k].y * xh[k].y) + (gg[k].z * xh[k].z + gg[k].w * xh[k].w);
+      }
+    }
+    s1 = warp_sum(s1) * inv_d;
+    s2 = warp_sum(s2) * inv_d;
+    float4* dx4 = reinterpret_cast<float4*>(dX + (size_t)t * d);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = lane + 32 * k;
+      if (c < nv) {
+        float4 o;
+        o.x = rs * (gg[k].x - s1 - xh[k].x * s2) + rr[k].x;
+        o.y = rs * (gg[k].y - s1 - xh[k].y * s2) + rr[k].y;
+        o.z = rs * (gg[k].z - s1 - xh[k].z * s2) + rr[k].z;
+        o.w = rs * (gg[k].w - s1 - xh[k].w * s2) + rr[k].w;
+        dx4[c] = o;
+      }
+    }
+  }
+  __syncthreads();
+  if (want_params) {
+    for (int c = threadIdx.x; c < 2 * d; c += LN_THREADS) {
+      float v = 0.0f;
+#pragma unroll
+      for (int w = 0; w < LN_WARPS; ++w) v += acc_s[(size_t)w * 2 * d + c];
+      if (c < d) {
+        if (dgamma) atomicAdd(&dgamma[c], v);
+      } else if (dbeta) {
+        atomicAdd(&dbeta[c - d], v);
+      }
+    }
+  }
+}
+
+static bool ln_vec_ok(const void* a, const void* b, const void* c, const void* e, int d, int ldx) {
+  const uintptr_t bits = (uintptr_t)a | (uintptr_t)b | (uintptr_t)c | (uintptr_t)e;
+  return (bits & 15) == 0 && d % 4 == 0 && ldx % 4 == 0 && d <= 1024;
+}
+
+// ------------------------------------------------------------------------------
 // patchify (model.py:111-126): patches[b, i*np+j, c*ph*pw + y*pw + x] = img[b,c,i*ph+y,j*pw+x]
 // One thread per image element, indexed in IMAGE order so reads coalesce (rows of W
 // floats); writes land in runs of pw floats.
@@ -184,6 +339,22 @@ extern "C" int kv_layernorm_fwd(const float* X, const float* gamma, const float*
   if (T == 0) return KV_OK;
   if (X == nullptr || Y == nullptr || T < 0 || d <= 0 || ldx < d) return KV_ERR_BAD_ARG;
   int blocks = ceil_div(T, LN_WARPS);
+  if (ln_vec_ok(X, Y, gamma, beta, d, ldx)) {
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    const int nvl = ceil_div(d / 4, 32);
+#define KV_LN_FWD(NV) layernorm_fwd_vec_kernel<NV><<<blocks, LN_THREADS, 0, (cudaStream_t)stream>>>(X, gamma, beta, Y, mean, rstd, T, d, ldx, eps)
+    switch (nvl) {
+      case 1: KV_LN_FWD(1); break;
+      case 2: KV_LN_FWD(2); break;
+      case 3: KV_LN_FWD(3); break;
+      case 4: KV_LN_FWD(4); break;
+      case 5: case 6: KV_LN_FWD(6); break;
+      default: KV_LN_FWD(8); break;
+    }
+#undef KV_LN_FWD
+    KV_CHECK_LAUNCH("layernorm_fwd_vec");
+    return KV_OK;
+  }
   if (blocks > 148 * 8) blocks = 148 * 8;
   layernorm_fwd_kernel<<<blocks, LN_THREADS, 0, (cudaStream_t)stream>>>(X, gamma, beta, Y, mean, rstd, T, d, ldx, eps);
   KV_CHECK_LAUNCH("layernorm_fwd");
@@ -201,6 +372,31 @@ extern "C" int kv_layernorm_bwd(const float* X, const float* dY, const float* ga
   if (T == 0) return KV_OK;
   const size_t smem = sizeof(float) * 2 * (size_t)d;
   if (smem > 200 * 1024) return KV_ERR_BAD_SHAPE;
+  if (ln_vec_ok(X, dY, dX, dresidual, d, ldx) && ln_vec_ok(gamma, dgamma, dbeta, nullptr, d, ldx)) {
+    int vb = ceil_div(T, LN_WARPS * 8);
+    if (vb > 148 * 2) vb = 148 * 2;
+    const int nvl = ceil_div(d / 4, 32);
+    const size_t vsmem = sizeof(float) * (size_t)d * (1 + 2 * LN_WARPS);
+#define KV_LN_BWD(NV)                                                                                              \
+  do {                                                                                                             \
+    if (vsmem > 48 * 1024)                                                                                         \
+      KV_CUDA(cudaFuncSetAttribute(layernorm_bwd_vec_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                   (int)vsmem), "layernorm_bwd_vec smem");                                         \
+    layernorm_bwd_vec_kernel<NV><<<vb, LN_THREADS, vsmem, (cudaStream_t)stream>>>(X, ldx, dY, gamma, mean, rstd,   \
+                                                                                 dresidual, dX, dgamma, dbeta, T, d); \
+  } while (0)
+    switch (nvl) {
+      case 1: KV_LN_BWD(1); break;
+      case 2: KV_LN_BWD(2); break;
+      case 3: KV_LN_BWD(3); break;
+      case 4: KV_LN_BWD(4); break;
+      case 5: case 6: KV_LN_BWD(6); break;
+      default: KV_LN_BWD(8); break;
+    }
+#undef KV_LN_BWD
+    KV_CHECK_LAUNCH("layernorm_bwd_vec");
+    return KV_OK;
+  }
   int blocks = ceil_div(T, LN_WARPS * 4);
   if (blocks > 148 * 4) blocks = 148 * 4;
   if (smem > 48 * 1024)

@@ -73,13 +73,16 @@ def test_matches_reference_golden(case):
     y.backward(g.t("dy", _dev()))
     assert relerr(x.grad, g.t("gx")) < TOL_GRAD
     params = dict(m.named_parameters())
+    # gradients that are a cancelling sum (q/k projections under a nearly uniform softmax) carry the fp32 rounding
+    # of the large terms they cancel: allow 1e-7 of the model's largest gradient as an absolute floor
+    floor = 1e-7 * max(ref.abs().max().item() for ref in g.grads().values())
     for k, ref in g.grads().items():
         got = params[k].grad
         assert got is not None, k
         if ref.abs().max() < 1e-6:  # analytically zero (key bias under softmax)
             assert got.abs().max() < 1e-5, k
             continue
-        assert grad_close(got, ref), (k, relerr(got, ref))
+        assert grad_close(got, ref) or (got.cpu() - ref).abs().max().item() <= floor, (k, relerr(got, ref))
 
 
 def test_patchify_and_pos_bit_exact():
@@ -353,3 +356,25 @@ def test_update_grid_on_device_then_forward(mode, tol):
         with torch.no_grad():
             m.spline_weight.copy_(g.t("spline_weight_after", _dev()))
         assert relerr(m(g.t("probe", _dev())), g.t("y_after")) < (TOL_FP32 if mode == "fp32" else tol)
+
+
+@pytest.mark.parametrize("T,d", [(5, 16), (1000, 64), (333, 192), (2049, 768), (70, 1024), (64, 520), (33, 1028), (40, 770),
+                                 (17, 4)])
+def test_layer_norm_vs_torch(T, d):
+    """nn.LayerNorm (model.py:22,24,107) forward/backward, register-resident kernels (d % 4 == 0, d <= 1024) and
+    the generic ones, contiguous and row-strided inputs."""
+    from kan_vit_b200 import ops
+    dev = _dev()
+    g = torch.Generator().manual_seed(T * d)
+    w = (1.0 + 0.1 * torch.randn(d, generator=g)).to(dev).requires_grad_(True)
+    b = (0.1 * torch.randn(d, generator=g)).to(dev).requires_grad_(True)
+    for strided in (False, True):
+        base = (2.0 * torch.randn(T, 2 * d if strided else d, generator=g) + 0.5).to(dev).requires_grad_(True)
+        x = base[:, :d] if strided else base
+        dy = torch.randn(T, d, generator=g).to(dev)
+        y = ops.layer_norm(x, w, b)
+        gx, gw, gb = torch.autograd.grad(y, (base, w, b), dy)
+        yr = torch.nn.functional.layer_norm(x.double(), (d,), w.double(), b.double(), 1e-5)
+        rx, rw, rb = torch.autograd.grad(yr, (base, w, b), dy.double())
+        assert relerr(y, yr) < TOL_FP32
+        assert relerr(gx, rx) < TOL_GRAD and relerr(gw, rw) < TOL_GRAD and relerr(gb, rb) < TOL_GRAD
