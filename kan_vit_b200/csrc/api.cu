@@ -171,6 +171,25 @@ __global__ void unpack_grads_kernel(const kv_kan_desc_t d, const float* __restri
           if (gb) put(gb + p, src[nb]);
           const float scale = sc ? sc[p] : 1.0f;
           float acc = 0.0f;
+          if (nb == 8 && gs && ((((uintptr_t)gs) | ((uintptr_t)sw)) & 15) == 0) {
+            // default effkan (8 coefficients per (o,i) = 32 bytes): 16-byte loads / stores of the row
+            const float4* sw4 = reinterpret_cast<const float4*>(sw + p * 8);
+            float4* gs4 = reinterpret_cast<float4*>(gs + p * 8);
+            const float4 w0 = __ldcs(sw4), w1 = __ldcs(sw4 + 1);
+            float4 o0 = make_float4(src[0] * scale, src[1] * scale, src[2] * scale, src[3] * scale);
+            float4 o1 = make_float4(src[4] * scale, src[5] * scale, src[6] * scale, src[7] * scale);
+            acc = (src[0] * w0.x + src[1] * w0.y) + (src[2] * w0.z + src[3] * w0.w) +
+                  (src[4] * w1.x + src[5] * w1.y) + (src[6] * w1.z + src[7] * w1.w);
+            if (accum) {
+              const float4 a0 = gs4[0], a1 = gs4[1];
+              o0.x += a0.x; o0.y += a0.y; o0.z += a0.z; o0.w += a0.w;
+              o1.x += a1.x; o1.y += a1.y; o1.z += a1.z; o1.w += a1.w;
+            }
+            gs4[0] = o0;
+            gs4[1] = o1;
+            if (gsc) put(gsc + p, acc);
+            break;
+          }
           for (int m = 0; m < nb; ++m) {
             const float gv = src[m];
             if (gs) put(gs + p * nb + m, gv * scale);
@@ -339,7 +358,7 @@ int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32
     pack_fparams_kernel<<<dim3(8, d->n_groups), 256, 0, st>>>(*d, ptr_table, fparams, bias);
     KV_CHECK_LAUNCH("pack_fparams");
     if (fparams != nullptr && d->family == KV_EFFKAN) {
-      effkan_probe_kernel<<<d->n_groups, 256, 0, st>>>(*d, ptr_table, fparams);
+      effkan_probe_kernel<<<d->n_groups, 1024, 0, st>>>(*d, ptr_table, fparams);
       KV_CHECK_LAUNCH("effkan_probe");
     }
   }

@@ -414,6 +414,7 @@ class _LayerNormFn(torch.autograd.Function):
                                      rstd.data_ptr(), T, d, ldx, eps, _stream(), work=8.0 * T * d)
         ctx.save_for_backward(x, gamma, mean, rstd)
         ctx.eps, ctx.ldx = eps, ldx
+        ctx.beta = beta          # identity only (gradient sink lookup); beta's values are not needed in backward
         return y
 
     @staticmethod
@@ -423,11 +424,25 @@ class _LayerNormFn(torch.autograd.Function):
         T, d = x.shape
         dy = dy.contiguous()
         dx = torch.empty((T, d), dtype=torch.float32, device=x.device)
-        dgamma = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
-        dbeta = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
+        # the kernel ADDS its d gamma / d beta partial sums: with a gradient sink they go straight into the
+        # parameters' flat gradient views (no zero-fill, no autograd accumulation launch)
+        sink = GRAD_SINK
+        beta = ctx.beta
+        tg = sink.target(gamma) if sink is not None and gamma is not None and gamma.requires_grad else None
+        tb = sink.target(beta) if sink is not None and beta is not None and beta.requires_grad else None
+        direct = tg is not None and tb is not None and tg.is_contiguous() and tb.is_contiguous()
+        if direct:
+            dgamma, dbeta = tg, tb
+        else:
+            dgamma = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
+            dbeta = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
         _call("kv_layernorm_bwd", lib.kv_layernorm_bwd, x.data_ptr(), dy.data_ptr(), L.ptr(gamma), mean.data_ptr(),
                                      rstd.data_ptr(), None, dx.data_ptr(), L.ptr(dgamma), L.ptr(dbeta),
                                      T, d, ctx.ldx, ctx.eps, _stream(), work=12.0 * T * d)
+        if direct:
+            sink.done(gamma)
+            sink.done(beta)
+            return dx, None, None, None, None
         return dx, dgamma, dbeta, None, None
 
 
