@@ -109,16 +109,30 @@ template <int DHP>
 __device__ __forceinline__ void stage_rows(__nv_bfloat16* const* tiles, int n_parts, const float* __restrict__ src,
                                            size_t row_stride, int N, int Np, int dh, int tid, int nth) {
   constexpr int LD = DHP + 8;
+  constexpr int U = 8;  // 16-byte loads in flight per thread: the staging is latency-bound otherwise
   const int f_per_row = n_parts * dh / 4;
-  for (int idx = tid; idx < Np * f_per_row; idx += nth) {
-    const int n = idx / f_per_row, f = idx - n * f_per_row;
-    const int col = f * 4, part = col / dh, c = col - part * dh;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (n < N) v = __ldg(reinterpret_cast<const float4*>(src + (size_t)n * row_stride + col));
-    uint2 w;
-    w.x = pack2(v.x, v.y);
-    w.y = pack2(v.z, v.w);
-    *reinterpret_cast<uint2*>(tiles[part] + n * LD + c) = w;
+  const int total = Np * f_per_row;
+  for (int base = tid; base < total; base += U * nth) {
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = base + u * nth;
+      const int n = idx / f_per_row, f = idx - n * f_per_row;
+      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (idx < total && n < N) v[u] = __ldcs(reinterpret_cast<const float4*>(src + (size_t)n * row_stride + f * 4));
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = base + u * nth;
+      if (idx < total) {
+        const int n = idx / f_per_row, f = idx - n * f_per_row;
+        const int col = f * 4, part = col / dh, c = col - part * dh;
+        uint2 w;
+        w.x = pack2(v[u].x, v[u].y);
+        w.y = pack2(v[u].z, v[u].w);
+        *reinterpret_cast<uint2*>(tiles[part] + n * LD + c) = w;
+      }
+    }
   }
   if (dh < DHP) {
     const int padw = (DHP - dh) / 4;  // dh % 4 == 0
@@ -155,6 +169,15 @@ attn_tc_fwd_kernel(const float* __restrict__ qkv, const float* __restrict__ resi
   const float sl2 = rsqrtf((float)dh) * LOG2E;
   const int nrb = (N + 15) / 16;
   for (int rb = warp; rb < nrb; rb += nwarps) {
+    if (residual) {
+      // the epilogue adds the residual rows of this block: start pulling them towards L2 now
+      // (16 rows x d_h floats; a lane takes one 128-byte line: row lane/2, half lane%2)
+      const int pr = rb * 16 + (lane >> 1), pc = (lane & 1) * 32;
+      if (pr < N && pc < dh) {
+        const float* pa = residual + ((size_t)b * N + pr) * (size_t)(H * dh) + (size_t)h * dh + pc;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pa));
+      }
+    }
     uint32_t qf[DHP / 16][4];
     load_a_frags<DHP>(qf, Qs, rb * 16, lane);
     float o[DHP / 8][4];
