@@ -33,11 +33,11 @@ class TransformerBlock(nn.Module):
     def forward2d(self, x, B, N):
         if self._specs is None:
             self._specs = (make_spec([self.ff[0]]), make_spec([self.ff[-1]]))
-        h = ops.layer_norm(x, self.norm1.weight, self.norm1.bias, self.norm1.eps)
-        x = self.attn.forward2d(h, B, N, residual=x)
-        h = ops.layer_norm(x, self.norm2.weight, self.norm2.bias, self.norm2.eps)
+        h, skip = ops.layer_norm_fork(x, self.norm1.weight, self.norm1.bias, self.norm1.eps)
+        x = self.attn.forward2d(h, B, N, residual=skip)
+        h, skip = ops.layer_norm_fork(x, self.norm2.weight, self.norm2.bias, self.norm2.eps)
         h = ops.kan_apply(h, self._specs[0], [slots_of(self.ff[0])], relu=not self.kan_mlp)
-        return ops.kan_apply(h, self._specs[1], [slots_of(self.ff[-1])], residual=x)
+        return ops.kan_apply(h, self._specs[1], [slots_of(self.ff[-1])], residual=skip)
 
     def forward(self, x):
         B, N, d = x.shape

@@ -401,8 +401,12 @@ def attention(qkv, B, N, H, dh, residual=None):
 
 
 class _LayerNormFn(torch.autograd.Function):
+    """fork=True also returns x itself (the skip branch of model.py:34,36): autograd then hands the gradients
+    of BOTH uses of x to one backward call, and the kernel adds the skip gradient while it writes dX --
+    instead of a separate elementwise add over the whole activation."""
+
     @staticmethod
-    def forward(ctx, x, gamma, beta, eps, ldx):
+    def forward(ctx, x, gamma, beta, eps, ldx, fork=False):
         lib = L.load()
         _require_cuda(x, gamma, beta)
         T, d = x.shape
@@ -415,14 +419,23 @@ class _LayerNormFn(torch.autograd.Function):
         ctx.save_for_backward(x, gamma, mean, rstd)
         ctx.eps, ctx.ldx = eps, ldx
         ctx.beta = beta          # identity only (gradient sink lookup); beta's values are not needed in backward
+        ctx.fork = fork
+        if fork:
+            ctx.set_materialize_grads(False)
+            return y, x.view_as(x)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dskip=None):
         lib = L.load()
         x, gamma, mean, rstd = ctx.saved_tensors
         T, d = x.shape
+        if dy is None:                      # only the skip branch was used
+            return dskip, None, None, None, None, None
         dy = dy.contiguous()
+        if dskip is not None:
+            dskip = dskip.contiguous()
+            assert dskip.shape == (T, d)
         dx = torch.empty((T, d), dtype=torch.float32, device=x.device)
         # the kernel ADDS its d gamma / d beta partial sums: with a gradient sink they go straight into the
         # parameters' flat gradient views (no zero-fill, no autograd accumulation launch)
@@ -437,13 +450,13 @@ class _LayerNormFn(torch.autograd.Function):
             dgamma = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
             dbeta = torch.zeros((d,), dtype=torch.float32, device=x.device) if gamma is not None else None
         _call("kv_layernorm_bwd", lib.kv_layernorm_bwd, x.data_ptr(), dy.data_ptr(), L.ptr(gamma), mean.data_ptr(),
-                                     rstd.data_ptr(), None, dx.data_ptr(), L.ptr(dgamma), L.ptr(dbeta),
-                                     T, d, ctx.ldx, ctx.eps, _stream(), work=12.0 * T * d)
+                                     rstd.data_ptr(), L.ptr(dskip), dx.data_ptr(), L.ptr(dgamma), L.ptr(dbeta),
+                                     T, d, ctx.ldx, ctx.eps, _stream(), work=(12.0 if dskip is None else 16.0) * T * d)
         if direct:
             sink.done(gamma)
             sink.done(beta)
-            return dx, None, None, None, None
-        return dx, dgamma, dbeta, None, None
+            return dx, None, None, None, None, None
+        return dx, dgamma, dbeta, None, None, None
 
 
 def layer_norm(x2d, gamma, beta, eps=1e-5):
@@ -451,6 +464,14 @@ def layer_norm(x2d, gamma, beta, eps=1e-5):
     if x2d.stride(1) != 1:
         x2d = x2d.contiguous()
     return _LayerNormFn.apply(x2d, gamma, beta, eps, x2d.stride(0))
+
+
+def layer_norm_fork(x2d, gamma, beta, eps=1e-5):
+    """(LayerNorm(x), x): use the second value for the skip connection around the normalised branch
+    (x + f(LN(x)), model.py:34,36); the backward then fuses the skip gradient into the LayerNorm gradient."""
+    if x2d.stride(1) != 1 or x2d.stride(0) != x2d.shape[1]:
+        x2d = x2d.contiguous()
+    return _LayerNormFn.apply(x2d, gamma, beta, eps, x2d.stride(0), True)
 
 
 class _PatchifyFn(torch.autograd.Function):

@@ -378,3 +378,33 @@ def test_layer_norm_vs_torch(T, d):
         rx, rw, rb = torch.autograd.grad(yr, (base, w, b), dy.double())
         assert relerr(y, yr) < TOL_FP32
         assert relerr(gx, rx) < TOL_GRAD and relerr(gw, rw) < TOL_GRAD and relerr(gb, rb) < TOL_GRAD
+
+
+@pytest.mark.parametrize("T,d", [(300, 768), (37, 100), (5, 16)])
+def test_layer_norm_fork_fuses_skip_gradient(T, d):
+    """(LN(x), x) with both branches used: one backward call receives both gradients and the kernel adds the skip
+    gradient into dX (model.py:34,36 residual structure); also each branch alone."""
+    from kan_vit_b200 import ops
+    dev = _dev()
+    g = torch.Generator().manual_seed(d)
+    w = (1.0 + 0.1 * torch.randn(d, generator=g)).to(dev).requires_grad_(True)
+    b = (0.1 * torch.randn(d, generator=g)).to(dev).requires_grad_(True)
+    x = torch.randn(T, d, generator=g).to(dev).requires_grad_(True)
+    a1, a2 = torch.randn(T, d, generator=g).to(dev), torch.randn(T, d, generator=g).to(dev)
+    for use_y, use_s in ((True, True), (True, False), (False, True)):
+        y, s = ops.layer_norm_fork(x, w, b)
+        assert torch.equal(s, x)
+        out = 0.0
+        if use_y:
+            out = out + (y * a1).sum()
+        if use_s:
+            out = out + (s * a2).sum()
+        got = torch.autograd.grad(out, (x, w, b), allow_unused=True)
+        yr = torch.nn.functional.layer_norm(x.double(), (d,), w.double(), b.double(), 1e-5)
+        ref_out = ((yr * a1).sum() if use_y else 0.0) + ((x.double() * a2).sum() if use_s else 0.0)
+        ref = torch.autograd.grad(ref_out, (x, w, b), allow_unused=True)
+        for a, r in zip(got, ref):
+            if r is None:
+                assert a is None or a.abs().max().item() == 0.0
+            else:
+                assert relerr(a, r) < TOL_GRAD

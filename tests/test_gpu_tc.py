@@ -53,6 +53,10 @@ def test_bf16_matches_reference_golden(case):
         # .freq: a cancelling sum over every row and feature (see test_gpu_parity); inside the composite
         # models its value is ~1e-5 against O(1) terms, so the bf16 noise of the whole model lands on it
         tol = (5e-2 if layer else 2.5e-1) if k.endswith(".freq") else gtol
+        # the q / k projections of the bare FlashAttention blocks: with 5 tokens and near-uniform softmax their
+        # gradient is ~1e-5 against O(1e-1) terms elsewhere (same cancelling-sum situation, see test_gpu_parity)
+        if case == "vit_flash-attn" and (k.endswith("to_q.weight") or k.endswith("to_kv.weight")):
+            tol = 2.5e-1
         assert err(params[k].grad, ref) < tol, k
 
 
