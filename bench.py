@@ -10,7 +10,9 @@ zero_grad -> forward -> CrossEntropy -> backward -> (gradient all-reduce) -> Ada
 (the step shape of the reference's train.py:31-40).  Workload at every N: the configuration
 BASELINE.json's metric ("train images/sec at 1/2/4/8 B200") is quoted on, configs[3]: the
 ViT-B/16-shaped KAN-ViT (efficient-kan MLP, 224x224, 197 tokens, dim 768, depth 12), bf16
-tensor-core arithmetic, data-parallel, 256 images per GPU (weak scaling).  It fits one GPU, so it
+tensor-core arithmetic, data-parallel, 336 images per GPU (weak scaling; 336 x 197 token rows = 259
+row blocks of 256, which the three layer shapes turn into exactly 7 / 21 / 42 waves of CTA pairs on the
+74 pair slots of a B200 -- a multiple of 48 images does that).  It fits one GPU, so it
 is also the N=1 workload.  The other configs (cfg1 .. cfg3, parity-test shapes) are selectable
 with --config for the record; cfg1/cfg2 default to the exact fp32 kernels.
 """
@@ -33,7 +35,7 @@ CONFIGS = {
     "cfg2": ((1, 28, 28), 7, 4, 64, 2, 10, "cheby", False, 1024, 1024),
     "cfg3_fast": ((3, 32, 32), 4, 6, 192, 8, 10, "fast", False, 1024, 32),
     "cfg3_sine": ((3, 32, 32), 4, 6, 192, 8, 10, "sine", False, 1024, 32),
-    "cfg4": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", True, 256, 1),
+    "cfg4": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", True, 336, 1),
     "cfg4_faithful": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", False, 64, 2),
 }
 DEFAULT_PRECISION = {"cfg1": "fp32", "cfg2": "fp32", "cfg3_fast": "bf16", "cfg3_sine": "bf16", "cfg4": "bf16",
