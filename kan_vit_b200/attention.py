@@ -44,6 +44,7 @@ class FlashAttention(torch.nn.Module):
         self.q_bucket_size = q_bucket_size
         self.k_bucket_size = k_bucket_size
         self._specs = None
+        self._spec_cat = None
 
     def forward(self, x, context=None, mask=None, q_bucket_size=None, k_bucket_size=None):
         if self._specs is None:
@@ -53,6 +54,18 @@ class FlashAttention(torch.nn.Module):
         Nk = ctx.shape[1]
         inner = self.heads * self.dim_head
         x2d = x.reshape(B * Nq, dim)
+        if (ops.get_precision() == "bf16" and context is None and mask is None and not self.causal
+                and ops.attention_tc_ok(Nq, self.heads, self.dim_head)):
+            # plain self-attention in bf16 mode: one projection GEMM whose output rows are ordered
+            # (head, {q,k,v}, d_head) -- the layout of the tensor-core attention kernels used by MSA
+            H, dh = self.heads, self.dim_head
+            w = torch.cat([self.to_q.weight.view(H, dh, dim), self.to_kv.weight[:inner].view(H, dh, dim),
+                           self.to_kv.weight[inner:].view(H, dh, dim)], dim=1).reshape(3 * inner, dim)
+            if self._spec_cat is None:
+                self._spec_cat = ops.KanSpec(L.KV_LINEAR, dim, 3 * inner)
+            qkv = ops.kan_apply(x2d, self._spec_cat, [[w, None]])
+            out = ops.attention(qkv, B, Nq, H, dh)
+            return ops.kan_apply(out, self._specs[2], [slots_of(self.to_out)]).reshape(B, Nq, dim)
         q = ops.kan_apply(x2d, self._specs[0], [slots_of(self.to_q)])
         kv = ops.kan_apply(x2d if context is None else ctx.reshape(B * Nk, dim), self._specs[1],
                            [slots_of(self.to_kv)])

@@ -395,6 +395,11 @@ class _AttnFn(torch.autograd.Function):
         return dqkv, (dout if ctx.has_res else None), None, None, None, None
 
 
+def attention_tc_ok(N, H, dh) -> bool:
+    """True when the bf16 tensor-core attention kernels serve this head shape (shape probe, nothing launched)."""
+    return dh <= 64 and dh % 4 == 0 and L.load().kv_attn_bwd_bf16(None, None, None, None, 0, N, H, dh, None) == 0
+
+
 def attention(qkv, B, N, H, dh, residual=None):
     """softmax(q k^T / sqrt(dh)) v per (sample, head) on qkv [B*N, H*3*dh] -> [B*N, H*dh] (+residual)."""
     return _AttnFn.apply(qkv.contiguous(), residual, B, N, H, dh)
