@@ -35,12 +35,12 @@ CONFIGS = {
     "cfg2": ((1, 28, 28), 7, 4, 64, 2, 10, "cheby", False, 1024, 1024),
     "cfg3_fast": ((3, 32, 32), 4, 6, 192, 8, 10, "fast", False, 1024, 32),
     "cfg3_sine": ((3, 32, 32), 4, 6, 192, 8, 10, "sine", False, 1024, 32),
-    "cfg4": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", True, 336, 1),
+    "cfg4": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", True, 336, 4),
     "cfg4_faithful": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", False, 64, 2),
 }
 DEFAULT_PRECISION = {"cfg1": "fp32", "cfg2": "fp32", "cfg3_fast": "bf16", "cfg3_sine": "bf16", "cfg4": "bf16",
                      "cfg4_faithful": "bf16"}
-CPU_TIME_BUDGET_S = 150.0  # the reference arm stops early (and says so) once its timed steps have used this
+CPU_TIME_BUDGET_S = 120.0  # the reference arm stops early (and says so) once its timed steps have used this
 METRIC = "train_images_per_sec"
 UNIT = "images/s"
 
@@ -105,36 +105,37 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------
 # CPU arm: the reference algorithm (oracle port) on the host cores
 # ---------------------------------------------------------------------------------------------
-def cpu_reference_step_fn(name, batch, seed=0):
-    """Returns (step, n_images).  TEST-INFRASTRUCTURE oracle used as the reported CPU baseline."""
+def cpu_reference_step_fn(name, batch, seed=0, optimizer=True):
+    """Returns (step, n_images).  TEST-INFRASTRUCTURE oracle used as the reported CPU baseline.  Nothing of the
+    product package is imported here: the initial state comes from oracle.kan_oracle.init_state."""
     from oracle import kan_oracle as O
-    import kan_vit_b200 as K
     chw, npatch, nb, d, h, out_d, kind, kan_mlp, _, _ = CONFIGS[name]
-    torch.manual_seed(seed)
-    proto = K.VisionTransformer(chw, npatch, nb, d, h, out_d, kind, kan_mlp=kan_mlp)  # init only (CPU tensors)
-    sd = {k: v.detach().clone().requires_grad_(v.is_floating_point() and k.split(".")[-1] not in ("grid", "phase"))
-          for k, v in proto.state_dict().items()}
+    sd = O.init_state(chw, npatch, nb, d, h, out_d, kind, kan_mlp=kan_mlp, seed=seed)
+    sd = {k: v.requires_grad_(v.is_floating_point() and k.split(".")[-1] not in ("grid", "phase", "arange"))
+          for k, v in sd.items()}
     params = [v for v in sd.values() if v.requires_grad]
-    opt = torch.optim.Adam(params, lr=1e-3)
+    opt = torch.optim.Adam(params, lr=1e-3) if optimizer else None
     g = torch.Generator().manual_seed(seed)
     img = torch.randn((batch,) + tuple(chw), generator=g)
     lab = torch.randint(0, out_d, (batch,), generator=g)
 
     def step():
-        opt.zero_grad(set_to_none=True)
+        for p in params:
+            p.grad = None
         y = O.vit_forward(img, sd, n_patches=npatch, n_blocks=nb, n_heads=h, kind=kind, kan_mlp=kan_mlp)
         loss = torch.nn.functional.cross_entropy(y, lab)
         loss.backward()
-        opt.step()
+        if opt is not None:
+            opt.step()
         return loss.item()
 
     return step, batch
 
 
-def time_cpu(name, batch, steps, warmup, budget_s=None):
+def time_cpu(name, batch, steps, warmup, budget_s=None, optimizer=True):
     """(images/s, ms/step, steps actually timed).  With budget_s the loop stops once the timed steps
     have used that much wall time (the ViT-B-shaped config takes seconds per image on the host)."""
-    step, n = cpu_reference_step_fn(name, batch)
+    step, n = cpu_reference_step_fn(name, batch, optimizer=optimizer)
     for _ in range(warmup):
         step()
     ts = []
@@ -148,23 +149,54 @@ def time_cpu(name, batch, steps, warmup, budget_s=None):
     return n / mean, mean * 1e3, len(ts)
 
 
+def host_threads():
+    """All the host threads the CPU arm can use: torchrun exports OMP_NUM_THREADS=1 to its workers, which would
+    pin the arm to one core at N > 1, so the count is set explicitly."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
+def time_config1(cores, steps=3):
+    """BASELINE.json configs[0] exactly as stated: ViKANformer efficient-kan (grid 5, order 3), 1x28x28, patch 7,
+    dim 64, depth 4, batch 64, forward + CrossEntropy + backward on the CPU (no optimizer), with all host threads
+    and with one (the reference path is dispatch-bound: SURVEY.md section 6)."""
+    out = {"workload": workload_name("cfg1", 64).replace("+Adam", "") + " (fwd+CE+bwd, BASELINE configs[0])"}
+    v, ms, n = time_cpu("cfg1", 64, steps, 1, 40.0, optimizer=False)
+    out.update({"value": v, "unit": UNIT, "cores": cores, "ms_per_step": ms, "steps": n})
+    torch.set_num_threads(1)
+    v1, ms1, n1 = time_cpu("cfg1", 64, steps, 1, 40.0, optimizer=False)
+    torch.set_num_threads(cores)
+    out["one_thread"] = {"value": v1, "unit": UNIT, "cores": 1, "ms_per_step": ms1, "steps": n1}
+    return out
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     name = args.config
     sample = CONFIGS[name][9]
-    cores = torch.get_num_threads()
-    val, ms, done = time_cpu(name, sample, args.steps, 1, CPU_TIME_BUDGET_S)
+    cores = host_threads()
+    print(f"[bench reference arm] {cores} host threads (torch.get_num_threads), sample batch {sample}",
+          file=sys.stderr, flush=True)
+    warm = 1
+    val, ms, done = time_cpu(name, sample, args.steps, warm, CPU_TIME_BUDGET_S)
+    cfg1 = time_config1(cores)
     line = {
         "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
-        "warmup": 1, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
         "config": {"workload": workload_name(name, CONFIGS[name][8]),
-                   "reference_sample": f"batch {sample} per step on the host CPU"},
+                   "reference_sample": f"batch {sample} per step on the host CPU, {done} timed steps "
+                                       f"(stops after {CPU_TIME_BUDGET_S:.0f} s of timed steps)"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{done} steps of batch {sample} (same model, oracle/kan_oracle.py "
-                                   "restatement of the reference, torch CPU fp32, autograd + Adam)"},
+                         "sample": f"{done} steps of batch {sample} (same model and step, oracle/kan_oracle.py "
+                                   "restatement of the reference, torch CPU fp32, autograd + Adam)",
+                         "config1": cfg1},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), file=_OUT, flush=True)
@@ -407,10 +439,11 @@ def run_gpu_arm(args):
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cores = torch.get_num_threads()
-        cval, cms, _ = time_cpu(name, cpu_batch, 3, 1)
+        cores = host_threads()
+        n_cpu = 2 if name.startswith("cfg4") else 3
+        cval, cms, n_done = time_cpu(name, cpu_batch, n_cpu, 1, 30.0)
         cpu_baseline = {"value": cval, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": f"3 steps of batch {cpu_batch} of the same model and step "
+                        "sample": f"{n_done} steps of batch {cpu_batch} of the same model and step "
                                   f"(oracle/kan_oracle.py, torch CPU fp32, {cms:.0f} ms/step)"}
 
     if rank == 0:

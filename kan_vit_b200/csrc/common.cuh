@@ -27,6 +27,20 @@ extern unsigned long long g_launches;
     if (_e != cudaSuccess) return kv::record_cuda_error(_e, where); \
   } while (0)
 
+// Opt a kernel in to more than 48 KB of dynamic shared memory, once per DEVICE (the attribute is per device;
+// a process may touch several GPUs).
+#define KV_SMEM_OPT_IN(kernel, bytes, where)                                                          \
+  do {                                                                                                \
+    static unsigned long long _done = 0ull; /* bit per device ordinal; same value on every writer */ \
+    int _dev = 0;                                                                                     \
+    KV_CUDA(cudaGetDevice(&_dev), where);                                                             \
+    const unsigned long long _bit = 1ull << (_dev & 63);                                              \
+    if (!(__atomic_load_n(&_done, __ATOMIC_RELAXED) & _bit)) {                                        \
+      KV_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (bytes)), where); \
+      __atomic_fetch_or(&_done, _bit, __ATOMIC_RELAXED);                                              \
+    }                                                                                                 \
+  } while (0)
+
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -754,12 +754,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
 
 template <int F>
 static int launch_fwd(const FwdParams& p, cudaStream_t st) {
-  static bool attr_set = false;  // benign race: the attribute value is always the same
-  if (!attr_set) {
-    KV_CUDA(cudaFuncSetAttribute(kan_tc_fwd_kernel<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES),
-            "tc_fwd smem attribute");
-    attr_set = true;
-  }
+  KV_SMEM_OPT_IN(kan_tc_fwd_kernel<F>, SMEM_BYTES, "tc_fwd smem attribute");
   const int n_pairs = ceil_div(p.d.T, 2 * BM);
   if ((long long)n_pairs * p.gm.n_tiles > 65535 || p.d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
   dim3 grid(2, n_pairs * p.gm.n_tiles, p.d.n_groups);  // x = CTA pair; output tiles of one row pair adjacent
@@ -1798,12 +1793,7 @@ int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const flo
 
 template <int F>
 static int launch_bwd_input_generic(const tc::BwdInParams& p, dim3 grid, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    KV_CUDA(cudaFuncSetAttribute(tc::kan_tc_bwd_input_generic_kernel<F>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 tc::BI_SMEM), "tc_bwd_input smem attribute");
-    attr_set = true;
-  }
+  KV_SMEM_OPT_IN(tc::kan_tc_bwd_input_generic_kernel<F>, tc::BI_SMEM, "tc_bwd_input smem attribute");
   tc::kan_tc_bwd_input_generic_kernel<F><<<grid, tc::NTHREADS, tc::BI_SMEM, st>>>(p);
   KV_CHECK_LAUNCH("kan_tc_bwd_input_generic_kernel");
   return KV_OK;
@@ -1825,12 +1815,7 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
     q.in_mask = (d.flags & KV_FLAG_RELU) ? act_mask : nullptr;
     return tc::launch_fwd<KV_LINEAR>(q, st);
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    KV_CUDA(cudaFuncSetAttribute(tc::effkan8_bwd_input_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 tc::BI_SMEM_E8), "tc_bwd_input smem attribute");
-    attr_set = true;
-  }
+  KV_SMEM_OPT_IN(tc::effkan8_bwd_input_kernel, tc::BI_SMEM_E8, "tc_bwd_input smem attribute");
   tc::BwdInParams p;
   p.d = d;
   p.X = X;
@@ -1880,12 +1865,7 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
 
 template <int F>
 static int launch_bwd_weight(const tc::BwdWParams& p, dim3 grid, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    KV_CUDA(cudaFuncSetAttribute(tc::kan_tc_bwd_weight_kernel<F>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 tc::BW_SMEM), "tc_bwd_weight smem attribute");
-    attr_set = true;
-  }
+  KV_SMEM_OPT_IN(tc::kan_tc_bwd_weight_kernel<F>, tc::BW_SMEM, "tc_bwd_weight smem attribute");
   tc::kan_tc_bwd_weight_kernel<F><<<grid, tc::NTHREADS, tc::BW_SMEM, st>>>(p);
   KV_CHECK_LAUNCH("kan_tc_bwd_weight_kernel");
   return KV_OK;

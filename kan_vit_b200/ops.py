@@ -511,10 +511,13 @@ _CE_WORKSPACE = {}
 
 
 def _ce_workspace(device):
-    ws = _CE_WORKSPACE.get(device)
+    # keyed by (device, stream): the kernel's arrival counter lives in the workspace, so two launches that may
+    # overlap (train and eval streams) must not share it
+    key = (device, _stream())
+    ws = _CE_WORKSPACE.get(key)
     if ws is None:
         ws = torch.zeros((L.load().kv_cross_entropy_workspace_floats(),), dtype=torch.float32, device=device)
-        _CE_WORKSPACE[device] = ws
+        _CE_WORKSPACE[key] = ws
     return ws
 
 

@@ -50,6 +50,14 @@ class FlatGradBuckets:
         self._pending = [0] * len(self.buckets)
         self._handles = []
         self._hooks = []
+        # Events per parameter per iteration.  A parameter reports in through ops.GRAD_SINK `done` once per use (a
+        # tied parameter applied by two layers: twice) AND through autograd's post-accumulate hook, which fires
+        # once per backward pass even when a layer returned no gradient for it (it wrote into the bucket view
+        # itself) -- always after the last use.  The bucket may only be reduced after the LAST event, so the
+        # counts are learnt in the first iteration (no early all-reduce there: finish() reduces everything)
+        # and checked afterwards.
+        self._uses = {}
+        self._expected_uses = None
         if self.world > 1:
             for p in self.params:
                 self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
@@ -61,9 +69,19 @@ class FlatGradBuckets:
         for i, (_, _, n) in enumerate(self.buckets):
             self._pending[i] = n
         self._handles = []
+        self._uses = {}
 
     def _on_grad(self, p):
         b = self._bucket_of[id(p)]
+        n = self._uses[id(p)] = self._uses.get(id(p), 0) + 1
+        if self._expected_uses is None:
+            return                      # first iteration: learn the use counts, reduce in finish()
+        want = self._expected_uses.get(id(p), 1)
+        if n < want:
+            return
+        if n > want:
+            raise RuntimeError("a parameter received more gradient contributions than in the previous iteration; "
+                               "its bucket was already all-reduced (rebuild TrainStep after changing the graph)")
         self._pending[b] -= 1
         if self._pending[b] == 0:
             s, e, _ = self.buckets[b]
@@ -83,6 +101,8 @@ class FlatGradBuckets:
         and turn the sums into means (``scale=False``: the optimizer kernel applies the 1/world)."""
         if self.world == 1:
             return
+        if self._expected_uses is None or any(self._uses.get(k, 0) < v for k, v in self._expected_uses.items()):
+            self._expected_uses = {k: max(v, 1) for k, v in self._uses.items()}
         for b, left in enumerate(self._pending):
             if left > 0:
                 s, e, _ = self.buckets[b]
@@ -197,7 +217,15 @@ class TrainStep:
             raise ValueError("metric collection advances host-side offsets every step and cannot be graph-captured")
         params = [p for p in model.parameters() if p.requires_grad]
         self.grads = FlatGradBuckets(params, bucket_bytes)
-        self.cuda_graph = bool(cuda_graph) and params[0].is_cuda and self.grads.world == 1
+        if cuda_graph and not params[0].is_cuda:
+            raise ValueError("cuda_graph=True needs a CUDA model")
+        if cuda_graph and optimizer is not None:
+            raise ValueError("cuda_graph=True captures the library's own Adam launch (device-side step count); a "
+                             "caller-supplied torch optimizer is not capturable here")
+        if cuda_graph and self.grads.world > 1:
+            raise ValueError("cuda_graph=True is single-GPU: the bucketed all-reduces are issued from host-side "
+                             "bookkeeping during backward and are not captured")
+        self.cuda_graph = bool(cuda_graph)
         # On the GPU the loss and the update are the library's own kernels: one
         # cross-entropy launch (loss + d logits) and one Adam launch over the flat buffers.  A caller's
         # optimizer, or CPU tensors (the gloo tests of the host logic), take the torch route.
@@ -207,6 +235,18 @@ class TrainStep:
         elif optimizer is None:
             optimizer = torch.optim.Adam(params, lr=lr)
         self.opt = optimizer
+        if self.grads.world > 1:
+            # replicas must start identical: rank 0's parameters win (models built under different seeds would
+            # otherwise diverge silently)
+            with torch.no_grad():
+                if self.fused:
+                    dist.broadcast(self.opt.flat_param, 0, group=self.grads.group)
+                else:
+                    for p in params:
+                        dist.broadcast(p.data, 0, group=self.grads.group)
+                for b in model.buffers():
+                    if b.is_floating_point():
+                        dist.broadcast(b, 0, group=self.grads.group)
         self._calls = 0
         self._clean = True         # gradient buffer known to be all zero
         self._graph = None

@@ -442,3 +442,78 @@ def flash_attention_forward(x: Tensor, sd: Dict[str, Tensor], prefix: str, heads
     o = FlashAttentionFunctionOracle.apply(split(q), split(k), split(v), mask, causal)
     b, h, n, d = o.shape
     return F.linear(o.permute(0, 2, 1, 3).reshape(b, n, h * d), sd[prefix + "to_out.weight"])
+
+
+# --------------------------------------------------------------------------
+# Harness-side initial state for the timed CPU arm (bench.py --impl reference, cpu_baseline)
+# --------------------------------------------------------------------------
+
+
+def init_state(chw, n_patches: int, n_blocks: int, d: int, n_heads: int, out_d: int, kind: str,
+               kan_mlp: bool = False, seed: int = 0) -> Dict[str, Tensor]:
+    """A state dict with the reference's key names and shapes (model.py:49-109, attention.py:136-170, the
+    constructors in models/*.py) for one VisionTransformer configuration, drawn here so that the CPU arm of
+    bench.py does not import the product package.  The distributions follow the reference's scale
+    (kaiming-uniform-like Linear / base weights, small spline coefficients, SineKAN / FastKAN defaults); the
+    timing of a training step does not depend on the draw.  ``kan_mlp``: ff = (KANLinear, KANLinear) under
+    ff.0 / ff.1."""
+    g = torch.Generator().manual_seed(seed)
+    sd: Dict[str, Tensor] = {}
+
+    def uni(shape, fan_in):
+        b = 1.0 / math.sqrt(fan_in)
+        return (torch.rand(shape, generator=g) * 2 - 1) * b
+
+    def layer(prefix, k, i, o, grid=None):
+        if k in ("vanilla", "flash-attn", "fourier", "linear"):
+            sd[prefix + "weight"] = uni((o, i), i)
+            sd[prefix + "bias"] = uni((o,), i)
+        elif k == "efficientkan":
+            sd[prefix + "base_weight"] = uni((o, i), i)
+            sd[prefix + "spline_weight"] = torch.randn((o, i, 8), generator=g) * 0.02
+            sd[prefix + "spline_scaler"] = uni((o, i), i)
+            sd[prefix + "grid"] = effkan_default_grid(i)
+        elif k == "cheby":
+            deg = 4
+            sd[prefix + "cheby_coeffs"] = torch.randn((i, o, deg + 1), generator=g) / (i * (deg + 1))
+            sd[prefix + "arange"] = torch.arange(0, deg + 1)
+        elif k == "fast":
+            sd[prefix + "layernorm.weight"] = torch.ones(i)
+            sd[prefix + "layernorm.bias"] = torch.zeros(i)
+            sd[prefix + "rbf.grid"] = torch.linspace(-2.0, 2.0, 8)
+            sd[prefix + "spline_linear.weight"] = torch.randn((o, i * 8), generator=g).clamp(-2, 2) * 0.1
+            sd[prefix + "base_linear.weight"] = uni((o, i), i)
+            sd[prefix + "base_linear.bias"] = uni((o,), i)
+        elif k == "sine":
+            G = grid or 5
+            sd[prefix + "amplitudes"] = torch.randn((o, i, G), generator=g) * 0.4 / o / (G / 5.0) ** 0.5
+            sd[prefix + "freq"] = sinekan_default_freq(G)
+            sd[prefix + "bias"] = torch.ones(1, o) / o
+            sd[prefix + "phase"] = sinekan_phase(i, G)
+        else:
+            raise ValueError(f"Unknown layer kind: {k}")
+
+    c, hh, ww = chw
+    input_d = c * (hh // n_patches) * (ww // n_patches)
+    layer("linear_mapper.", kind, input_d, d, grid=28)
+    sd["v_class"] = torch.randn((1, d), generator=g)
+    dh = d // n_heads
+    map_kind = "vanilla" if kind in ("vanilla", "flash-attn", "fourier") else kind
+    for b in range(n_blocks):
+        p = f"blocks.{b}."
+        for n in ("norm1", "norm2"):
+            sd[p + n + ".weight"] = torch.ones(d)
+            sd[p + n + ".bias"] = torch.zeros(d)
+        for nm in ("q", "k", "v"):
+            for h in range(n_heads):
+                layer(f"{p}attn.{nm}_mappings.{h}.", map_kind, dh, dh, grid=4)
+        if kan_mlp:
+            layer(p + "ff.0.", "efficientkan", d, 4 * d)
+            layer(p + "ff.1.", "efficientkan", 4 * d, d)
+        else:
+            layer(p + "ff.0.", "linear", d, 4 * d)
+            layer(p + "ff.2.", "linear", 4 * d, d)
+    sd["mlp_head.0.weight"] = torch.ones(d)
+    sd["mlp_head.0.bias"] = torch.zeros(d)
+    layer("mlp_head.1.", "linear", d, out_d)
+    return sd

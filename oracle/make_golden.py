@@ -134,7 +134,82 @@ def maintenance_case():
     print("maint_effkan:", {k: v.shape for k, v in rec.items() if not k.startswith("sd/")})
 
 
+def big_cases():
+    """Parity fixtures at BASELINE config 3 / 4 geometry: python oracle/make_golden.py --big
+
+    Weights and inputs come from tests/seeded.py (regenerated from the seed by the tests, never stored); the
+    UNMODIFIED reference modules run on them and a sub-sample of every output / gradient is committed
+    (about 4096 values per tensor at an odd stride -- 384 per parameter gradient of the multi-layer models -- plus the tensor's max |value| for the norm-wise error)."""
+    sys.path.insert(0, REF)
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
+    import model as ref_model  # noqa
+    from models.effkan import KANLinear  # noqa
+    from seeded import seeded_input, seeded_state, subsample  # noqa
+
+    def run(module, x, dy):
+        x = x.clone().requires_grad_(True)
+        y = module(x)
+        module.zero_grad()
+        y.backward(dy.to(y.dtype))
+        out = {"y": y.detach(), "gx": x.grad}
+        for k, p in module.named_parameters():
+            if p.grad is not None:
+                out["g/" + k] = p.grad.detach().clone()
+        return out
+
+    def record(name, module, x, seed):
+        """Stored per tensor: the float64 run of the reference (ground truth, sub-sampled), its max |value|, and
+        `@ref32err` = the norm-wise distance of the reference's own float32 run from it (how well-conditioned the
+        tensor is in fp32: the SineKAN ViT's input gradient is 1e-3 away from its own fp64 value)."""
+        module.load_state_dict(seeded_state(module.state_dict(), seed))
+        with torch.no_grad():
+            shape = module(x).shape
+        dy = seeded_input(tuple(shape), seed + 7)
+        r32 = run(module, x, dy)
+        module.double()
+        if hasattr(module, "patchify"):
+            # labelled shim, float64 ground-truth run only: patchify allocates float32 whatever the input dtype
+            # (model.py:116), which the float64 LayerNorm / Linear behind it reject
+            orig = module.patchify
+            module.patchify = lambda images, n: orig(images, n).double()
+        r64 = run(module, x.double(), dy)
+        if hasattr(module, "patchify"):
+            del module.patchify
+        module.float()
+        rec = {}
+        n_par = len(list(module.parameters()))
+        for key, t in r64.items():
+            v, k = subsample(t, 4096 if (n_par < 8 or not key.startswith("g/")) else 384)
+            rec[key] = _np(v).astype(np.float32)   # the float64 values, stored to float32 precision
+            amax = t.abs().max().item()
+            e32 = (r32[key].double() - t).abs().max().item() / (amax if amax > 0 else 1.0)
+            rec[key + "@meta"] = np.array([k, amax, e32], dtype=np.float64)   # stride, max |value|, ref32err
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
+        worst = max((float(rec[k][2]), k) for k in rec if k.endswith("@meta") and float(rec[k][1]) > 1e-9)
+        print(f"{name}: y{tuple(shape)} {sum(v.nbytes for v in rec.values())/1024:.1f} KiB; reference fp32 vs fp64: "
+              f"y {rec['y@meta'][2]:.1e}, gx {rec['gx@meta'][2]:.1e}, worst {worst[0]:.1e} {worst[1]}")
+
+    torch.manual_seed(0)
+    record("big_effkan_768x3072_T300", KANLinear(768, 3072), seeded_input((300, 768), 101), 100)
+    record("big_effkan_3072x768_T300", KANLinear(3072, 768), seeded_input((300, 3072), 111), 110)
+    blk = ref_model.TransformerBlock(768, 12, feedforward_dim=3072, attn_type="efficientkan")
+    blk.ff = torch.nn.Sequential(KANLinear(768, 3072), KANLinear(3072, 768))  # KAN-MLP extension (SURVEY 0.2)
+    record("big_block_cfg4_kanmlp_B2", blk, seeded_input((2, 197, 768), 121), 120)
+    for kind in ("fast", "sine"):
+        vit = ref_model.VisionTransformer((3, 32, 32), n_patches=4, n_blocks=6, d_hidden=192, n_heads=8, out_d=10,
+                                          type=kind)
+        record(f"big_vit_cfg3_{kind}_B4", vit, seeded_input((4, 3, 32, 32), 131), 130)
+    vit = ref_model.VisionTransformer((3, 224, 224), n_patches=14, n_blocks=2, d_hidden=768, n_heads=12, out_d=10,
+                                      type="efficientkan")
+    for b in vit.blocks:
+        b.ff = torch.nn.Sequential(KANLinear(768, 3072), KANLinear(3072, 768))
+    record("big_vit_cfg4_2blk_kanmlp_B2", vit, seeded_input((2, 3, 224, 224), 141), 140)
+
+
 def main():
+    if "--big" in sys.argv:
+        big_cases()
+        return
     if "--flash-only" in sys.argv:
         flash_cases()
         return

@@ -163,3 +163,20 @@ def test_vit_flash_attn_matches_reference():
     x = g.t("x").requires_grad_(True)
     y = O.vit_forward(x, sd, n_patches=2, n_blocks=2, n_heads=2, kind="flash-attn")
     _check(g, y, x, sd, tol=1e-5)
+
+
+def test_init_state_has_the_reference_keys_and_shapes():
+    """oracle.init_state (the initial weights of bench.py's CPU arm, drawn without importing the product package)
+    names and shapes every tensor like the reference's state_dict (tests/golden/state_dict_keys.json, recorded from
+    the unmodified reference)."""
+    import json
+    import os
+    from conftest import GOLDEN
+    with open(os.path.join(GOLDEN, "state_dict_keys.json")) as f:
+        keys = json.load(f)
+    cfg = {"cfg1_efficientkan": ((1, 28, 28), 7, 4, 64, 2, 10, "efficientkan"),
+           "cfg3_fast": ((3, 32, 32), 4, 6, 192, 8, 10, "fast"), "cfg3_sine": ((3, 32, 32), 4, 6, 192, 8, 10, "sine"),
+           "cfg2_cheby": ((1, 28, 28), 7, 4, 64, 2, 10, "cheby"), "vanilla": ((1, 28, 28), 7, 2, 64, 2, 10, "vanilla")}
+    for name, a in cfg.items():
+        got = {k: list(v.shape) for k, v in O.init_state(*a).items()}
+        assert got == keys[name], name
