@@ -37,7 +37,8 @@ constexpr int BAR_BYTES = 1024;
 constexpr int DBG_BYTES = 16 * 1024;  // clock stamps of timing experiments (d.reserved & 32)
 constexpr int SMEM_BYTES = A_RING_BYTES + B_RING_BYTES + BAR_BYTES + DBG_BYTES;
 constexpr int TMEM_COLS = 512;
-constexpr int MAX_M_TC = 24;
+constexpr int MAX_M_TC = KV_MAX_M;  // forward / weight gradient: any M (chunks are walked in parts of <= 9 bases)
+constexpr int MAX_M_TC_DX = 32;    // input gradient: one 16-feature chunk = 16 M <= 512 TMEM columns
 
 // K-order of the units inside a 16-feature chunk
 enum { LAYOUT_BASIS_MAJOR = 0,  // unit m = 16 features x basis m            (every family)
@@ -50,7 +51,9 @@ struct Geom {
   int BN;        // outputs per tile (multiple of 16, <= 512)
   int S;         // units per B stage (one bulk copy, one barrier round trip)
   int NB;        // B ring slots (stages)
-  int NCH;       // A ring slots (chunks)
+  int NCH;       // A ring slots (each holds one PART of a chunk: Mp units)
+  int npart;     // parts per chunk: the bases of a chunk are produced / consumed in npart slices of <= Mp bases,
+  int Mp;        //   so that the ring always holds >= 2 slots (M > 13) and layers with M > 27 fit at all
   int effkan8;   // host-side candidate for LAYOUT_EFFKAN8 (the device-side grid probe decides)
   __host__ __device__ size_t tile_elems() const { return (size_t)n_units * BN * KU; }
 };
@@ -67,7 +70,9 @@ __host__ __device__ inline Geom make_geom(const kv_kan_desc_t& d) {
   g.S = g.S < 1 ? 1 : (g.S > 8 ? 8 : g.S);
   int nb = B_RING_BYTES / (g.S * half_unit);
   g.NB = nb > NB_MAX ? NB_MAX : nb;
-  g.NCH = A_UNITS / d.M;
+  g.npart = (d.M + 8) / 9;
+  g.Mp = (d.M + g.npart - 1) / g.npart;
+  g.NCH = A_UNITS / g.Mp;
   g.effkan8 = (d.family == KV_EFFKAN && d.spline_order == 3 && d.grid_size == 5 &&
                (d.flags & KV_FLAG_UNIFORM_GRID)) ? 1 : 0;
   return g;
@@ -313,6 +318,38 @@ __device__ __forceinline__ void effkan8_chunk(uint8_t* base, int wg, const float
          pack_bf16(sv[4], sv[5]), pack_bf16(sv[6], sv[7]));
 }
 
+// The same for a thread that owns 4 consecutive features 4*qg .. 4*qg+3 of the chunk (16 producer warps: twice the
+// warps per scheduler to hide the latency of the dependent cubic / shift / pack chains).
+__device__ __forceinline__ void effkan8_chunk4(uint8_t* base, int qg, const float (&x)[4], float t0, float inv_h) {
+  float sv[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float xv = x[q];
+    const float u = (xv - t0) * inv_h;
+    const float jf = floorf(u);
+    const float s = u - jf;
+    const int j = (int)jf;
+    const bool ok = (u >= 0.0f) && (u < 11.0f);  // x in [t_0, t_11): models/effkan.py:115
+    const float s2 = s * s, s3 = s2 * s, om = 1.0f - s;
+    const float w0 = om * om * om * (1.0f / 6.0f);
+    const float w1 = fmaf(0.5f, s3, fmaf(-1.0f, s2, 2.0f / 3.0f));
+    const float w2 = fmaf(-0.5f, s3, fmaf(0.5f, s2, fmaf(0.5f, s, 1.0f / 6.0f)));
+    const float w3 = s3 * (1.0f / 6.0f);
+    uint64_t W = (uint64_t)pack_bf16(w0, w1) | ((uint64_t)pack_bf16(w2, w3) << 32);
+    if (!ok) W = 0;
+    const int b = (j - 3) * 16;
+    const uint64_t lo = shl64(W, b) | shr64(W, -b);
+    const uint64_t hi = shl64(W, b - 64) | shr64(W, 64 - b);
+    // feature f = 4*qg + q: unit f / 2, k-half f % 2
+    sts128(base + (qg * 2 + (q >> 1)) * A_UNIT_BYTES + (q & 1) * 2048, (uint32_t)lo, (uint32_t)(lo >> 32),
+           (uint32_t)hi, (uint32_t)(hi >> 32));
+    sv[q] = fast_silu(xv);
+  }
+  // SiLU unit: k-half (4*qg) / 8, elements (4*qg) % 8 .. +3 of the row's 16-byte vector
+  *reinterpret_cast<uint2*>(base + 8 * A_UNIT_BYTES + (qg >> 1) * 2048 + (qg & 1) * 8) =
+      make_uint2(pack_bf16(sv[0], sv[1]), pack_bf16(sv[2], sv[3]));
+}
+
 // Basis-major layout, basis index outermost: 8 features x one m = one 16-byte store.
 // basis_octet: the values of 8 consecutive features (one 16-byte vector per basis function m) for the bases
 // m0 <= m < m0 + Mt, written at dst + (m - m0) * stride.
@@ -384,7 +421,7 @@ __device__ __forceinline__ void basis_octet(uint8_t* dst, int stride, int m0, in
     }
     const float* gr = c.fp + 2 * c.in;
     const float inv_den = 1.0f / c.rbf_denom;
-    for (int m = 0; m < c.G; ++m) {
+    for (int m = max(m0, 0); m < min(c.G, m0 + Mt); ++m) {   // only the bases of this part
       const float gm = gr[m];
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
@@ -393,7 +430,7 @@ __device__ __forceinline__ void basis_octet(uint8_t* dst, int stride, int m0, in
       }
       emit(m);
     }
-    if (!(c.flags & KV_FLAG_NO_BASE)) {
+    if (!(c.flags & KV_FLAG_NO_BASE) && c.G >= m0 && c.G < m0 + Mt) {
 #pragma unroll
       for (int q = 0; q < 8; ++q) v[q] = fast_silu(x[q]);
       emit(c.G);
@@ -401,7 +438,7 @@ __device__ __forceinline__ void basis_octet(uint8_t* dst, int stride, int m0, in
   } else if (F == KV_SINE) {
     const float* freq = c.fp;
     const float* ph = c.fp + c.G;
-    for (int m = 0; m < c.G; ++m) {
+    for (int m = max(m0, 0); m < min(c.G, m0 + Mt); ++m) {
       const float fr = freq[m];
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
@@ -411,27 +448,34 @@ __device__ __forceinline__ void basis_octet(uint8_t* dst, int stride, int m0, in
       emit(m);
     }
   } else if (F == KV_FOURIER) {
+    // bases m < G: cos((m+1) x), m >= G: sin((m-G+1) x).  Inside a run of consecutive harmonics the angle-addition
+    // recurrence steps by x; each run (a part may start anywhere, and crosses m = G at most once) starts from a
+    // direct evaluation.
     float c1[8], s1[8], ck[8], sk[8];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      __sincosf(x[q], &s1[q], &c1[q]);
-      ck[q] = c1[q];
-      sk[q] = s1[q];
-    }
-    for (int m = 0; m < 2 * c.G; ++m) {
-      if (m == c.G) {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) { ck[q] = c1[q]; sk[q] = s1[q]; }
-      }
+    for (int q = 0; q < 8; ++q) __sincosf(x[q], &s1[q], &c1[q]);
+    int m = max(m0, 0);
+    const int mend = min(2 * c.G, m0 + Mt);
+    while (m < mend) {
+      const bool is_sin = m >= c.G;
+      const int run_end = min(mend, is_sin ? 2 * c.G : c.G);
+      const float kf = (float)((is_sin ? m - c.G : m) + 1);
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
-        v[q] = (m < c.G) ? ck[q] : sk[q];
-        const float nc = ck[q] * c1[q] - sk[q] * s1[q];
-        const float ns = sk[q] * c1[q] + ck[q] * s1[q];
-        ck[q] = nc;
-        sk[q] = ns;
+        if (kf == 1.0f) { ck[q] = c1[q]; sk[q] = s1[q]; }
+        else __sincosf(kf * x[q], &sk[q], &ck[q]);
       }
-      emit(m);
+      for (; m < run_end; ++m) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          v[q] = is_sin ? sk[q] : ck[q];
+          const float nc = ck[q] * c1[q] - sk[q] * s1[q];
+          const float ns = sk[q] * c1[q] + ck[q] * s1[q];
+          ck[q] = nc;
+          sk[q] = ns;
+        }
+        emit(m);
+      }
     }
   }
 }
@@ -442,8 +486,11 @@ __device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const f
   basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, 0, c.M, x, c, i0, mu, rs);
 }
 
-template <int F>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_fwd_kernel(const FwdParams p) {
+// NPW = producer / epilogue warps: 8 (a thread owns 8 features of a chunk) or 16 (4 features; effkan only)
+template <int F, int NPW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) kan_tc_fwd_kernel(const FwdParams p) {
+  constexpr int NTH = 32 * (2 + NPW);
+  constexpr int FPT = 64 / NPW;  // features per producer thread
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + A_RING_BYTES;
@@ -472,7 +519,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < NCH_MAX; ++s) {
-      ptx::mbar_init(fullA(s), 2 * N_PRODUCER_WARPS);  // (leader) local + peer producer warps
+      ptx::mbar_init(fullA(s), 2 * NPW);  // (leader) local + peer producer warps
       ptx::mbar_init(emptyA(s), 1);
     }
     for (int s = 0; s < NB_MAX; ++s) {
@@ -530,13 +577,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), (BM / 8) * 128, sbo);
       const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)n1 * 8, sbo);
       const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 16, (uint32_t)n2 * 8, sbo);
-      const uint32_t a_chunk_step = (uint32_t)(M * A_UNIT_BYTES) >> 4, b_unit_step = b_unit_bytes >> 4;
+      const uint32_t a_slot_step = (uint32_t)(gm.Mp * A_UNIT_BYTES) >> 4, b_unit_step = b_unit_bytes >> 4;
       int sc = 0, sb = 0, ub = 0, u = 0;
       uint32_t phA = 0, phB = 0;
       for (int ch = 0; ch < gm.n_chunks; ++ch) {
+        for (int m0 = 0; m0 < M; m0 += gm.Mp) {     // one ring slot per part of the chunk
+        const int m1 = min(M, m0 + gm.Mp);
         if (!(d.reserved & 2)) ptx::mbar_wait(fullA(sc), phA);
-        uint64_t da = da0 + (uint64_t)(sc * a_chunk_step);
-        for (int q = 0; q < M; ++q, ++u) {
+        uint64_t da = da0 + (uint64_t)(sc * a_slot_step);
+        for (int q = m0; q < m1; ++q, ++u) {
           if (ub == 0) {
             stamp(0, u, 0);
             if (!(d.reserved & 64)) ptx::mbar_wait(fullB(sb), phB);
@@ -551,7 +600,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
               if (n2 && !(d.reserved & 128)) ptx::mma2_bf16_ss(tmem_base + 256, da, db2_0 + boff, idesc2, u > 0);
             }
             if (last_of_stage) ptx::tc_commit2(emptyB(sb));
-            if (q == M - 1) ptx::tc_commit2(emptyA(sc));
+            if (q == m1 - 1) ptx::tc_commit2(emptyA(sc));
             if (u + 1 == n_units) ptx::tc_commit2(tmem_full);
           }
           __syncwarp();
@@ -565,6 +614,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
           }
         }
         if (++sc == NCH) { sc = 0; phA ^= 1; }
+        }
       }
     } else if (lane == 0) {
       // ================= peer CTA: tell the leader when our half of each B stage has landed ===========
@@ -582,7 +632,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
   } else {
     // ================= A producers: basis prologue =================
     const int ptid = threadIdx.x - 64;
-    const int r = ptid & (BM - 1), wg = ptid >> 7;
+    const int r = ptid & (BM - 1), wg = ptid >> 7;  // wg: which FPT-feature slice of the 16-feature chunk
     const int n_slices = d.n_groups / d.x_share;
     const int slice = g / d.x_share;
     const int xoff = slice * d.in_features;
@@ -609,64 +659,88 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     const float* mrow = (F == KV_LINEAR && p.in_mask != nullptr)
                             ? p.in_mask + (size_t)(row_ok ? t : 0) * d.ldx + xoff : nullptr;
     const bool mvec = vec && ((reinterpret_cast<uintptr_t>(p.in_mask) & 15) == 0);
-    auto gate = [&](int i0g, float (&v)[8]) {
-      if (F == KV_LINEAR && mrow != nullptr) {
-        float mk[8];
-        load_x8(mrow, i0g, in, row_ok, mvec, mk);
+    // FPT consecutive features of this row, starting at i0g (zero beyond `in` / beyond T)
+    auto load_xf = [&](const float* row, bool v16, int i0g, float (&v)[FPT]) {
+      if constexpr (FPT == 8) {
+        load_x8(row, i0g, in, row_ok, v16, v);
+      } else {
+        if (row_ok && v16 && i0g + 4 <= in) {
+          const float4 a = __ldg(reinterpret_cast<const float4*>(row + i0g));
+          v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+        } else {
 #pragma unroll
-        for (int q = 0; q < 8; ++q) v[q] = mk[q] > 0.0f ? v[q] : 0.0f;
+          for (int q = 0; q < 4; ++q) v[q] = (row_ok && i0g + q < in) ? __ldg(row + i0g + q) : 0.0f;
+        }
       }
     };
-    float cur[8];
-    load_x8(xrow, wg * 8, in, row_ok, vec, cur);
-    gate(wg * 8, cur);
+    auto gate = [&](int i0g, float (&v)[FPT]) {
+      if (F == KV_LINEAR && mrow != nullptr) {
+        float mk[FPT];
+        load_xf(mrow, mvec, i0g, mk);
+#pragma unroll
+        for (int q = 0; q < FPT; ++q) v[q] = mk[q] > 0.0f ? v[q] : 0.0f;
+      }
+    };
+    float cur[FPT];
+    load_xf(xrow, vec, wg * FPT, cur);
+    gate(wg * FPT, cur);
     for (int ch = 0; ch < gm.n_chunks; ++ch) {
-      float nxt[8];
+      float nxt[FPT];
       if (ch + 1 < gm.n_chunks) {
-        load_x8(xrow, (ch + 1) * KU + wg * 8, in, row_ok, vec, nxt);
-        gate((ch + 1) * KU + wg * 8, nxt);
+        load_xf(xrow, vec, (ch + 1) * KU + wg * FPT, nxt);
+        gate((ch + 1) * KU + wg * FPT, nxt);
       } else {
 #pragma unroll
-        for (int q = 0; q < 8; ++q) nxt[q] = 0.0f;
+        for (int q = 0; q < FPT; ++q) nxt[q] = 0.0f;
       }
-      const int sc = ch % NCH;
-      ptx::mbar_wait(emptyA(sc), ((ch / NCH) & 1) ^ 1);
+      const int i0 = ch * KU + wg * FPT;
+      for (int pt = 0; pt < gm.npart; ++pt) {      // one ring slot per part: bases [m0, m0 + Mt) of the chunk
+      const int slot_i = ch * gm.npart + pt;
+      const int sc = slot_i % NCH;
+      const int m0 = pt * gm.Mp, Mt = min(gm.Mp, M - m0);
+      ptx::mbar_wait(emptyA(sc), ((slot_i / NCH) & 1) ^ 1);
       if (ptid == 0) stamp(2, ch, 0);
-      uint8_t* base = sA + sc * M * A_UNIT_BYTES + row_off;
-      const int i0 = ch * KU + wg * 8;
-      if (F == KV_EFFKAN) {
-        if (layout == LAYOUT_EFFKAN8) {
-          effkan8_chunk(base, wg, cur, gt0, ginv_h);
+      uint8_t* base = sA + sc * gm.Mp * A_UNIT_BYTES + row_off;
+      if constexpr (F == KV_EFFKAN) {
+        if (layout == LAYOUT_EFFKAN8) {            // M = 9: one part
+          if constexpr (FPT == 8) effkan8_chunk(base, wg, cur, gt0, ginv_h);
+          else effkan8_chunk4(base, wg, cur, gt0, ginv_h);
         } else {
+          // arbitrary knots: Cox-de Boor per feature, scattered 2-byte stores; feature f = wg*FPT + q of the chunk
+          // sits in k-half f / 8 at element f % 8
 #pragma unroll 1
-          for (int q = 0; q < 8; ++q) {
-            UnitSink sink{base + wg * 2048 + q * 2};
+          for (int q = 0; q < FPT; ++q) {
+            const int f = wg * FPT + q;
+            StrideSink sink{base + (f >> 3) * 2048 + (f & 7) * 2, A_UNIT_BYTES, m0, Mt};
             if (i0 + q < in) {
               basis_eval<F>(c, i0 + q, cur[q], cur[q], sink);
             } else {
-              for (int m = 0; m < M; ++m) sink.put(m, 0.0f);
+              for (int m = m0; m < m0 + Mt; ++m) sink.put(m, 0.0f);
             }
           }
         }
       } else {
-        basis_major_chunk<F>(base, wg, cur, c, i0, mu, rs);
+        static_assert(F == KV_EFFKAN || FPT == 8, "the octet producers own 8 features per thread");
+        if constexpr (FPT == 8) basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, m0, Mt, cur, c, i0, mu, rs);
       }
       ptx::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(sc), 0));  // the leader's barrier
       if (ptid == 0) stamp(2, ch, 1);
+      }
 #pragma unroll
-      for (int q = 0; q < 8; ++q) cur[q] = nxt[q];
+      for (int q = 0; q < FPT; ++q) cur[q] = nxt[q];
     }
     // ================= epilogue: TMEM -> registers -> smem transpose -> coalesced global stores =========
     ptx::mbar_wait(tmem_full, 0);
     ptx::tc_fence_after();
     const int pw = warp - 2;
     const int q4 = warp & 3;            // TMEM lane quadrant this warp may read
-    const int half = pw >> 2;           // two warps per quadrant split the column blocks
+    const int half = pw >> 2;           // NPW / 4 warps per quadrant split the column blocks
     const int out = d.out_features;
     const int ncols_total = d.n_groups * out;
     constexpr int LDT = 36;             // staging row stride in floats (conflict-free float4 access)
+    static_assert(NPW * 32 * LDT * 4 <= A_RING_BYTES, "epilogue staging lives in the idle A ring");
     float* stg = reinterpret_cast<float*>(sA) + pw * (32 * LDT);  // the operand rings are idle by now
     const int c4 = (lane & 7) * 4, rsub = lane >> 3;
     // the 8 rows this lane stores in the row-wise phase
@@ -689,7 +763,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
                        (!p.residual || (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0) &&
                        (!p.pos || (reinterpret_cast<uintptr_t>(p.pos) & 15) == 0) &&
                        (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
-    for (int cb = half; cb * 32 < BN; cb += 2) {
+    for (int cb = half; cb * 32 < BN; cb += NPW / 4) {
       uint32_t rr[32];
       ptx::tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + cb * 32, rr);
       ptx::tmem_ld_wait();
@@ -743,7 +817,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
   }
   ptx::cluster_sync_all();  // the peer's smem / TMEM stay alive until every MMA and epilogue is done
   if (dbg) {
-    for (int i = threadIdx.x; i < 4096; i += NTHREADS)
+    for (int i = threadIdx.x; i < 4096; i += NTH)
       reinterpret_cast<uint32_t*>(p.Y)[(size_t)(rank * 128 + i / 512) * d.ldy + (i % 512)] = dbuf[i];
   }
   if (warp == 0) {
@@ -754,11 +828,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
 
 template <int F>
 static int launch_fwd(const FwdParams& p, cudaStream_t st) {
-  KV_SMEM_OPT_IN(kan_tc_fwd_kernel<F>, SMEM_BYTES, "tc_fwd smem attribute");
+  // effkan: 16 producer warps (4 features per thread); every other family: 8 (the octet producers)
+  constexpr int NPW = (F == KV_EFFKAN) ? 16 : 8;
+  KV_SMEM_OPT_IN((kan_tc_fwd_kernel<F, NPW>), SMEM_BYTES, "tc_fwd smem attribute");
   const int n_pairs = ceil_div(p.d.T, 2 * BM);
   if ((long long)n_pairs * p.gm.n_tiles > 65535 || p.d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
   dim3 grid(2, n_pairs * p.gm.n_tiles, p.d.n_groups);  // x = CTA pair; output tiles of one row pair adjacent
-  kan_tc_fwd_kernel<F><<<grid, NTHREADS, SMEM_BYTES, st>>>(p);
+  kan_tc_fwd_kernel<F, NPW><<<grid, 32 * (2 + NPW), SMEM_BYTES, st>>>(p);
   KV_CHECK_LAUNCH("kan_tc_fwd_kernel");
   return KV_OK;
 }
@@ -786,6 +862,7 @@ struct BwdGeom {
   int n_stages;  // contraction stages of 64 outputs
   int T8, O8;    // dY image extents in core matrices (T padded to 256, out padded to 64)
   int n_chunks;
+  int W1;        // M > 16 (SW > 256, n_sub = 1): the chunk is two MMAs of 256 and W1 = SW - 256 columns; else 0
 };
 
 __host__ __device__ inline BwdGeom make_bwd_geom(const kv_kan_desc_t& d) {
@@ -803,6 +880,7 @@ __host__ __device__ inline BwdGeom make_bwd_geom(const kv_kan_desc_t& d) {
     b.O8 = (cover > b.n_stages * 64 ? (cover + 7) / 8 : b.n_stages * 8);
   }
   b.T8 = (d.T + 255) / 256 * 32;
+  b.W1 = b.SW > 256 ? b.SW - 256 : 0;
   return b;
 }
 
@@ -850,15 +928,27 @@ __global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, 
   for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total64;
        idx += (size_t)gridDim.x * blockDim.x) {
     size_t r = idx;
-    const int n8 = r % (half / 8); r /= (half / 8);
-    const int o8 = r % 8; r /= 8;
-    const int j = r % b.n_sub; r /= b.n_sub;
+    int n8, o8, j, cc;
+    if (b.W1 == 0) {
+      n8 = r % (half / 8); r /= (half / 8);
+      o8 = r % 8; r /= 8;
+      j = r % b.n_sub; r /= b.n_sub;
+    } else {
+      // split chunk: [MMA 0: o8 (8)][n8 (16)] then [MMA 1: o8 (8)][n8 (W1 / 16)]
+      int q = (int)(r % half); r /= half;
+      j = 0;
+      if (q < 128) { n8 = q % 16; o8 = q / 16; }
+      else { q -= 128; n8 = q % (b.W1 / 16); o8 = q / (b.W1 / 16); n8 += 1 << 20; }
+    }
     const int rank = r % 2; r /= 2;
     const int st = r % b.n_stages; r /= b.n_stages;
     const int tile = r % b.n_tiles; r /= b.n_tiles;
     const int g = (int)r;
     const int c = tile * b.n_sub + j;
-    const int cc = rank * half + n8 * 8;  // first column of this core matrix inside the chunk
+    // first column of this core matrix inside the chunk
+    if (b.W1 == 0) cc = rank * half + n8 * 8;
+    else if (n8 < (1 << 20)) cc = rank * 128 + n8 * 8;
+    else cc = 256 + rank * (b.W1 / 2) + (n8 - (1 << 20)) * 8;
     const int q = cc / 16, h = (cc / 8) & 1;
     uint32_t w[8][4];  // [column r8][4 output pairs]
     float v[8][8];     // [output oe][column r8]
@@ -1115,20 +1205,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
 
 
 // S values staged in shared memory, element m at s[m * stride]
+// (only the bases mlo <= m < mhi are staged: the scratch holds at most 24 of them, larger M take two passes)
 struct StridedDotSink {
   static constexpr bool kDense = false;
   const float* s;
-  int stride;
+  int stride, mlo, mhi;
   float acc;
-  __device__ __forceinline__ void put(int m, float v) { acc = fmaf(v, s[m * stride], acc); }
+  __device__ __forceinline__ void put(int m, float v) {
+    if (m >= mlo && m < mhi) acc = fmaf(v, s[(m - mlo) * stride], acc);
+  }
 };
 struct StridedFastkanDotSink {  // RBF part (m < G) and SiLU part (m == G) kept apart (LayerNorm backward needs the first)
   static constexpr bool kDense = false;
   const float* s;
-  int stride, G;
+  int stride, G, mlo, mhi;
   float acc_rbf, acc_base;
   __device__ __forceinline__ void put(int m, float v) {
-    if (m < G) acc_rbf = fmaf(v, s[m * stride], acc_rbf); else acc_base = fmaf(v, s[m * stride], acc_base);
+    if (m < mlo || m >= mhi) return;
+    if (m < G) acc_rbf = fmaf(v, s[(m - mlo) * stride], acc_rbf); else acc_base = fmaf(v, s[(m - mlo) * stride], acc_base);
   }
 };
 
@@ -1164,7 +1258,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     ptx::fence_mbar_init();
   }
   float* dfreq_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);  // SineKAN: d freq of this CTA
-  if (warp == 2) dfreq_s[lane] = 0.0f;
+  if (warp == 2) dfreq_s[lane] = dfreq_s[lane + 32] = 0.0f;
   if (warp == 0) {
     ptx::tmem_alloc2(ptx::smem_u32(tmem_slot), TMEM_COLS);
     ptx::tmem_relinquish2();
@@ -1199,11 +1293,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
   } else if (warp == 1) {
     if (rank == 0) {
       // ---- MMA issuer: S[256 rows, n_sub x SW] += dY[256, 16] . Wt[SW, 16]^T
-      const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, SW);
+      // M <= 16: n_sub chunks of SW columns, one MMA each.  M > 16: one chunk, two MMAs of W0 = 256 and W1 columns
+      // (each CTA stages W/2 rows of each, the second block behind the first)
+      const int W0 = b.W1 ? 256 : SW;
+      const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, W0);
+      const uint32_t idesc1 = b.W1 ? ptx::make_idesc_bf16(2 * BM, b.W1) : 0u;
       const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), 128, 1024);
-      const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)SW * 8, 128);
+      const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)W0 * 8, 128);
+      const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + W0 * 64, (uint32_t)b.W1 * 8, 128);
       const uint32_t b_sub_step = (uint32_t)(SW * 64) >> 4;    // next sub-MMA's rows
-      const uint32_t b_k_step = (uint32_t)(2 * SW * 8) >> 4;   // next K=16 step: two 8-wide core columns
+      const uint32_t b_k_step = (uint32_t)(2 * W0 * 8) >> 4;   // next K=16 step: two 8-wide core columns
+      const uint32_t b_k_step1 = (uint32_t)(2 * b.W1 * 8) >> 4;
       int s = 0;
       uint32_t ph = 0;
       for (int st = 0; st < b.n_stages; ++st) {
@@ -1212,11 +1312,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         if (ptx::elect_one()) {
           const uint64_t da = da0 + (uint64_t)((s * BI_A_STAGE) >> 4);
           const uint64_t db = db0 + (uint64_t)((s * BI_B_STAGE) >> 4);
+          const uint64_t db1 = db1_0 + (uint64_t)((s * BI_B_STAGE) >> 4);
 #pragma unroll
           for (int ks = 0; ks < BI_KS; ++ks) {
-            for (int j = 0; j < ((d.reserved & 1024) ? 1 : n_sub); ++j)
-              ptx::mma2_bf16_ss(tmem_base + j * SW, da + (uint64_t)(ks * 16), db + (uint64_t)(j * b_sub_step + ks * b_k_step),
-                                idesc, (st | ks) > 0);
+            if (b.W1) {
+              ptx::mma2_bf16_ss(tmem_base, da + (uint64_t)(ks * 16), db + (uint64_t)(ks * b_k_step), idesc, (st | ks) > 0);
+              ptx::mma2_bf16_ss(tmem_base + 256, da + (uint64_t)(ks * 16), db1 + (uint64_t)(ks * b_k_step1), idesc1,
+                                (st | ks) > 0);
+            } else {
+              for (int j = 0; j < ((d.reserved & 1024) ? 1 : n_sub); ++j)
+                ptx::mma2_bf16_ss(tmem_base + j * SW, da + (uint64_t)(ks * 16), db + (uint64_t)(j * b_sub_step + ks * b_k_step),
+                                  idesc, (st | ks) > 0);
+            }
           }
           ptx::tc_commit2(empty(s));
           if (st + 1 == b.n_stages) ptx::tc_commit2(tmem_full);
@@ -1268,14 +1375,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       if (cch >= b.n_chunks) break;  // warp-uniform
       float x8[8];
       load_x8(xrow, cch * KU + half * 8, in, row_ok, vec, x8);
-      for (int m = 0; m < M; ++m) {
+      float dx[8], dxn_acc[8];
+#pragma unroll
+      for (int f = 0; f < 8; ++f) dx[f] = dxn_acc[f] = 0.0f;
+      const int n_pass = M > 24 ? 2 : 1, Mh = (M + n_pass - 1) / n_pass;
+      for (int pass = 0; pass < n_pass; ++pass) {
+      const int mlo = pass * Mh, mhi = min(M, mlo + Mh);
+      for (int m = mlo; m < mhi; ++m) {
         uint32_t r8[8];
         ptx::tmem_ld8(trow + j * SW + m * 16 + half * 8, r8);
         ptx::tmem_ld_wait();
 #pragma unroll
-        for (int f = 0; f < 8; ++f) scratch[m * MS + f * 256 + etid] = __uint_as_float(r8[f]);
+        for (int f = 0; f < 8; ++f) scratch[(m - mlo) * MS + f * 256 + etid] = __uint_as_float(r8[f]);
       }
-      float dx[8];
 #pragma unroll
       for (int f = 0; f < 8; ++f) {
         const int i = cch * KU + half * 8 + f;
@@ -1287,9 +1399,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         if (F == KV_SINE) {
           const float* freq = c.fp;
           const float* ph = c.fp + c.G + (size_t)ic * c.G;
-          for (int q = 0; q < c.G; ++q) {
+          for (int q = mlo; q < min(mhi, c.G); ++q) {
             const float cs = cosf(fmaf(xv, freq[q], ph[q]));
-            const float sv = srow[q * MS];
+            const float sv = srow[(q - mlo) * MS];
             acc = fmaf(freq[q] * cs, sv, acc);
             float contrib = live ? xv * cs * sv : 0.0f;  // d freq_q (models/sinekan.py:87), reduced over the CTA
             contrib = warp_sum(contrib);
@@ -1297,17 +1409,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
           }
         } else if (F == KV_FASTKAN) {
           const float xn = fastkan_xn(c, ic, xv, mu, rs);
-          StridedFastkanDotSink sk{srow, MS, c.G, 0.0f, 0.0f};
+          StridedFastkanDotSink sk{srow, MS, c.G, mlo, mhi, 0.0f, 0.0f};
           basis_deriv<F>(c, ic, xv, xn, sk);
           acc = sk.acc_base;
           if (!ln) acc += sk.acc_rbf;
-          else if (live) p.dXn[(size_t)te * ((size_t)d.n_groups * in) + (size_t)g * in + i] = sk.acc_rbf;
+          else dxn_acc[f] += sk.acc_rbf;
         } else {
-          StridedDotSink sk{srow, MS, 0.0f};
+          StridedDotSink sk{srow, MS, mlo, mhi, 0.0f};
           basis_deriv<F>(c, ic, xv, xv, sk);
           acc = sk.acc;
         }
-        dx[f] = acc;
+        dx[f] += acc;
+      }
+      }
+      if (ln) {
+#pragma unroll
+        for (int f = 0; f < 8; ++f) {
+          const int i = cch * KU + half * 8 + f;
+          if (row_ok && i < in) p.dXn[(size_t)te * ((size_t)d.n_groups * in) + (size_t)g * in + i] = dxn_acc[f];
+        }
       }
       if (row_ok && shared_slice) {
         const int i0 = cch * KU + half * 8;
@@ -1546,14 +1666,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(s), 0));
         if (++s == BW_NA) { s = 0; ph ^= 1; }
       }
-    } else
-    for (int st = 0; st < n_stages; ++st) {
+    } else {
+    // The tile reads a 64-byte (spline) or 512-byte (SiLU / Linear) stripe of every row: a latency-bound gather.
+    // Two levels of prefetch: the stripe of stage st + PF is pulled into L2, and the registers of stage st + 1 are
+    // loaded BEFORE stage st is evaluated, so the L2 round trip hides under a whole stage instead of stalling
+    // every stage (the producers, not the tensor pipe, paced the out = 768 layers).
+    constexpr int XN = 32;
+    auto load_stage = [&](int st, float (&xv)[XN]) {
       const int t = row0 + st * 64 + tl;
       const bool row_ok = t < row1;
       const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
       {
-        // the tile reads a 64-byte (spline) or 512-byte (SiLU / Linear) stripe of every row: a latency-bound
-        // gather.  Pull the stripe of a later stage into L2 now so that its load finds it there.
         constexpr int PF = 8;
         const int tp = t + PF * 64;
         if (tile_live && tp < row1) {
@@ -1561,28 +1684,33 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
           if ((spline_tile ? feat0 + 4 * fb : feat0 + 32 * fb) < in) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
         }
       }
-      float xv[32];
-      if (tile_live) {
-        if (spline_tile) {
-          // 4 features per thread: features feat0 + 4*fb .. +3
-          const int i0 = feat0 + 4 * fb;
-          if (row_ok && vec && i0 + 4 <= in) {
-            const float4 a = __ldg(reinterpret_cast<const float4*>(xrow + i0));
-            xv[0] = a.x; xv[1] = a.y; xv[2] = a.z; xv[3] = a.w;
-          } else {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) xv[q] = (row_ok && i0 + q < in) ? __ldg(xrow + i0 + q) : 0.0f;
-          }
+      if (!tile_live) return;
+      if (spline_tile) {
+        // 4 features per thread: features feat0 + 4*fb .. +3
+        const int i0 = feat0 + 4 * fb;
+        if (row_ok && vec && i0 + 4 <= in) {
+          const float4 a = __ldg(reinterpret_cast<const float4*>(xrow + i0));
+          xv[0] = a.x; xv[1] = a.y; xv[2] = a.z; xv[3] = a.w;
         } else {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            float t8v[8];
-            load_x8(xrow, feat0 + 32 * fb + 8 * k, in, row_ok, vec, t8v);
+          for (int q = 0; q < 4; ++q) xv[q] = (row_ok && i0 + q < in) ? __ldg(xrow + i0 + q) : 0.0f;
+        }
+      } else {
 #pragma unroll
-            for (int q = 0; q < 8; ++q) xv[8 * k + q] = t8v[q];
-          }
+        for (int k = 0; k < 4; ++k) {
+          float t8v[8];
+          load_x8(xrow, feat0 + 32 * fb + 8 * k, in, row_ok, vec, t8v);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) xv[8 * k + q] = t8v[q];
         }
       }
+    };
+    float xv[XN], xnext[XN];
+#pragma unroll
+    for (int q = 0; q < XN; ++q) xv[q] = xnext[q] = 0.0f;
+    if (n_stages > 0) load_stage(0, xv);
+    for (int st = 0; st < n_stages; ++st) {
+      if (st + 1 < n_stages) load_stage(st + 1, xnext);
       ptx::mbar_wait(emptyA(s), ph);
       uint8_t* base = sA + s * BW_A_STAGE + row_off;
       if (tile_live) {
@@ -1622,6 +1750,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(s), 0));
       if (++s == BW_NA) { s = 0; ph ^= 1; }
+#pragma unroll
+      for (int q = 0; q < XN; ++q) xv[q] = xnext[q];
+    }
     }
     // ---- epilogue: TMEM lane = basis column K', column = output; fp32 RED into dWp[g][o][i*M+m]
     ptx::mbar_wait(tmem_full, 0);
@@ -1693,7 +1824,7 @@ static bool tc_bwd_generic(const kv_kan_desc_t& d) {
 }
 // input-gradient kernel: one chunk (16 features x M bases) is one MMA of N = 16 M <= 256 columns
 static bool tc_bwd_ok(const kv_kan_desc_t& d) {
-  return tc_bwd_effkan8(d) || tc_bwd_linear(d) || (tc_bwd_generic(d) && d.M <= 16);
+  return tc_bwd_effkan8(d) || tc_bwd_linear(d) || (tc_bwd_generic(d) && d.M <= tc::MAX_M_TC_DX);
 }
 static bool tc_bwd_w_ok(const kv_kan_desc_t& d) { return tc_bwd_effkan8(d) || tc_bwd_linear(d) || tc_bwd_generic(d); }
 // Linear: dX = dY . W runs as the forward kernel of the transposed layer

@@ -6,8 +6,10 @@ import kan_vit_b200 as K
 from kan_vit_b200 import ops
 from kan_vit_b200._dispatch import make_spec, slots_of
 dev = torch.device("cuda:0")
-m = K.KANLinear(768, 3072).to(dev)
-x = torch.randn(25216, 768, device=dev)
+INF = int(sys.argv[2]) if len(sys.argv) > 2 else 768
+OUTF = int(sys.argv[3]) if len(sys.argv) > 3 else 3072
+m = K.KANLinear(INF, OUTF).to(dev)
+x = torch.randn(25216, INF, device=dev)
 spec = make_spec([m]); K.set_precision("bf16")
 for _ in range(2):
     y = ops.kan_apply(x, spec, [slots_of(m)])

@@ -40,6 +40,19 @@ def _case(name):
         seed = 100 if i == 768 else 110
         m = K.KANLinear(i, o)
         return m, (lambda x, sd: O.layer_forward("efficientkan", x, sd, "")), seeded_input((T, i), seed + 1), seed
+    if name.startswith("big_layer_"):
+        # BASELINE config 5's large grids: more basis functions per input than one 27-unit operand ring slot
+        # (forward walks a chunk in parts), than 16 (two MMAs per chunk in the input gradient) or 24 (two passes)
+        _, _, fam, gtag = name.split("_")
+        G = int(gtag[1:])
+        i, o, T = 192, 272, 520
+        mk = {"effkan": (lambda: K.KANLinear(i, o, grid_size=G), "efficientkan"),
+              "cheby": (lambda: K.ChebyKANLayer(i, o, G), "cheby"),
+              "fastkan": (lambda: K.FastKANLayer(i, o, num_grids=G), "fast"),
+              "sine": (lambda: K.SineKANLayer(i, o, grid_size=G), "sine"),
+              "fourier": (lambda: K.NaiveFourierKANLayer(i, o, G), "fourier")}[fam]
+        kind = mk[1]
+        return mk[0](), (lambda x, sd: O.layer_forward(kind, x, sd, "")), seeded_input((T, i), 161 + G), 160 + G
     if name == "big_block_cfg4_kanmlp_B2":
         m = K.TransformerBlock(768, 12, feedforward_dim=3072, attn_type="efficientkan", kan_mlp=True)
         return m, (lambda x, sd: O.block_forward(x, sd, "", 12, "efficientkan", kan_mlp=True)), \
@@ -216,6 +229,10 @@ ORACLE_CASES = [
     # (d) config 3 as stated: (3,32,32), n_patches 4, d 192, 8 heads (d_h = 24), 6 blocks; SineKAN's patch
     #     embedding has grid_size 28
     "big_vit_cfg3_fast_B4", "big_vit_cfg3_sine_B4",
+    # (f) config 5's grid column: M = 14 / 24 (effkan 10 / 20), 21 (cheby, fastkan 20), 20 / 28 (sine 20 / 28),
+    #     20 / 40 (fourier 10 / 20)
+    "big_layer_effkan_g10", "big_layer_effkan_g20", "big_layer_cheby_g20", "big_layer_fastkan_g20",
+    "big_layer_sine_g20", "big_layer_sine_g28", "big_layer_fourier_g10", "big_layer_fourier_g20",
 ]
 
 
