@@ -103,6 +103,13 @@ kan_fwd_f32_kernel(const kv_kan_desc_t d, const float* __restrict__ X, const flo
       Bs[kk * LDB + o] = w;
     }
     __syncthreads();
+    // two-level summation: the K chunk is summed on its own and then added to the running total, so the rounding
+    // of a K = in*M <= 27 648 contraction grows like sqrt(chunks), not sqrt(K) (the 1e-5 fp32 parity bar)
+    float part[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) part[r][q] = 0.0f;
     for (int kk = 0; kk < cw; ++kk) {
       const float4 a = *reinterpret_cast<const float4*>(&As[kk * LDA + ty * 4]);
       const float4 b = *reinterpret_cast<const float4*>(&Bs[kk * LDB + tx * 4]);
@@ -111,8 +118,12 @@ kan_fwd_f32_kernel(const kv_kan_desc_t d, const float* __restrict__ X, const flo
 #pragma unroll
       for (int r = 0; r < 4; ++r)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) acc[r][q] = fmaf(av[r], bv[q], acc[r][q]);
+        for (int q = 0; q < 4; ++q) part[r][q] = fmaf(av[r], bv[q], part[r][q]);
     }
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[r][q] += part[r][q];
     __syncthreads();
   }
   // ---- epilogue
@@ -212,6 +223,11 @@ kan_bwd_input_f32_kernel(const kv_kan_desc_t d, const float* __restrict__ X,
         }
       }
       __syncthreads();
+      float part[4][4];   // two-level summation over the outputs (see the forward kernel)
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) part[r][q] = 0.0f;
 #pragma unroll 8
       for (int oo = 0; oo < BO; ++oo) {
         const float4 a = *reinterpret_cast<const float4*>(&As[oo * LDA + ty * 4]);
@@ -221,8 +237,12 @@ kan_bwd_input_f32_kernel(const kv_kan_desc_t d, const float* __restrict__ X,
 #pragma unroll
         for (int r = 0; r < 4; ++r)
 #pragma unroll
-          for (int q = 0; q < 4; ++q) acc[r][q] = fmaf(av[r], bv[q], acc[r][q]);
+          for (int q = 0; q < 4; ++q) part[r][q] = fmaf(av[r], bv[q], part[r][q]);
       }
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[r][q] += part[r][q];
       __syncthreads();
     }
     // S[row][kk] = (dY . Wp)[row, i0*M + kk]
@@ -371,6 +391,11 @@ kan_bwd_weight_f32_kernel(const kv_kan_desc_t d, int tsplit, const float* __rest
       }
     }
     __syncthreads();
+    float part[4][4];   // two-level summation over the rows (see the forward kernel)
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) part[r][q] = 0.0f;
 #pragma unroll 4
     for (int tt = 0; tt < BT; ++tt) {
       const float4 a = *reinterpret_cast<const float4*>(&As[tt * LDA + ty * 4]);
@@ -381,8 +406,12 @@ kan_bwd_weight_f32_kernel(const kv_kan_desc_t d, int tsplit, const float* __rest
 #pragma unroll
       for (int r = 0; r < 4; ++r)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) acc[r][q] = fmaf(av[r], bv[q], acc[r][q]);
+        for (int q = 0; q < 4; ++q) part[r][q] = fmaf(av[r], bv[q], part[r][q]);
     }
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[r][q] += part[r][q];
     if (dbias != nullptr && blockIdx.x == 0 && tid < BN) {
       for (int tt = 0; tt < BT; ++tt) bsum += As[tt * LDA + tid];
     }
