@@ -427,6 +427,23 @@ int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, cons
   return simt_fwd(*d, X, wp_f32, fparams, bias, mean, rstd, residual, pos, Y, (cudaStream_t)stream);
 }
 
+int kv_kan_fwd_attn_image(const kv_kan_desc_t* d, const float* X, const void* wtiles_bf16, const float* fparams,
+                          const float* bias, const float* mean, const float* rstd, void* attn_image,
+                          int tokens_per_sample, void* stream) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  if (!(d->flags & KV_FLAG_BF16_TC)) return KV_ERR_UNSUPPORTED;
+  if (d->T == 0) return KV_OK;
+  if (X == nullptr || wtiles_bf16 == nullptr || attn_image == nullptr) return KV_ERR_BAD_ARG;
+  if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;
+  rc = tc_supported(*d);
+  if (rc != KV_OK) return rc;
+  const kv_kan_desc_t v = tc_view(*d);
+  if (v.n_groups == d->n_groups && d->x_share != 1) return KV_ERR_UNSUPPORTED;   // the q/k/v maps did not merge
+  return tc_fwd(v, X, wtiles_bf16, fparams, bias, mean, rstd, nullptr, nullptr, nullptr, (cudaStream_t)stream,
+                attn_image, tokens_per_sample);
+}
+
 int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, const float* act_mask,
                      const float* wp_f32, const void* wtiles_t_bf16, const void* dy_image,
                      const float* fparams, const float* mean, const float* rstd, float* dX, float* dXn,
@@ -434,14 +451,16 @@ int kv_kan_bwd_input(const kv_kan_desc_t* d, const float* X, const float* dY, co
   int rc = check_desc(d);
   if (rc != KV_OK) return rc;
   if (d->T == 0) return KV_OK;
-  if (X == nullptr || dY == nullptr || dX == nullptr) return KV_ERR_BAD_ARG;
+  const bool tc_path = (d->flags & KV_FLAG_BF16_TC) && wtiles_t_bf16 != nullptr && dy_image != nullptr;
+  // dY may be NULL on the tensor-core path when the caller produced the bf16 dY image itself (attention backward)
+  if (X == nullptr || dX == nullptr || (dY == nullptr && !(tc_path && d->family != KV_LINEAR))) return KV_ERR_BAD_ARG;
   if ((d->flags & KV_FLAG_RELU) && act_mask == nullptr) return KV_ERR_BAD_ARG;
   if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;
   if (d->family == KV_FASTKAN && !(d->flags & KV_FLAG_NO_LAYERNORM) &&
       (mean == nullptr || rstd == nullptr || dXn == nullptr))
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
-  if ((d->flags & KV_FLAG_BF16_TC) && wtiles_t_bf16 != nullptr && dy_image != nullptr)
+  if (tc_path)
     return tc_bwd_input(tc_view(*d), X, dY, act_mask, dy_image, wtiles_t_bf16, fparams, mean, rstd, dX, dXn, dfparams,
                         (cudaStream_t)stream);
   if (wp_f32 == nullptr) return KV_ERR_BAD_ARG;
@@ -455,13 +474,15 @@ int kv_kan_bwd_weight(const kv_kan_desc_t* d, const float* X, const float* dY, c
   int rc = check_desc(d);
   if (rc != KV_OK) return rc;
   if (d->T == 0) return KV_OK;
-  if (X == nullptr || dY == nullptr || dWp == nullptr) return KV_ERR_BAD_ARG;
+  const bool tc_w = (d->flags & KV_FLAG_BF16_TC) && dy_image != nullptr && tc_bwd_weight_available(tc_view(*d));
+  // dY may be NULL on the tensor-core path (the caller made the image) as long as no bias gradient is wanted
+  if (X == nullptr || dWp == nullptr || (dY == nullptr && !(tc_w && dbias == nullptr))) return KV_ERR_BAD_ARG;
   if ((d->flags & KV_FLAG_RELU) && act_mask == nullptr) return KV_ERR_BAD_ARG;
   if (fparam_count(*d) > 0 && fparams == nullptr) return KV_ERR_BAD_ARG;
   if (d->family == KV_FASTKAN && !(d->flags & KV_FLAG_NO_LAYERNORM) && (mean == nullptr || rstd == nullptr))
     return KV_ERR_BAD_ARG;
   if (d->T == 0) return KV_OK;
-  if ((d->flags & KV_FLAG_BF16_TC) && dy_image != nullptr && tc_bwd_weight_available(tc_view(*d))) {
+  if (tc_w) {
     rc = tc_bwd_weight(tc_view(*d), X, dy_image, fparams, mean, rstd, dWp, (cudaStream_t)stream);
     if (rc != KV_OK) return rc;
     if (dbias == nullptr) return KV_OK;

@@ -276,3 +276,48 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) attn5_fwd_kernel(const FwdPara
     ptx::tmem_dealloc(tmem_base, 512);
   }
 }
+
+}  // namespace at5
+
+// shape verdict shared by the launchers (callers probe with B = 0)
+static int attn5_check(int B, int N, int H, int dh) {
+  if (B < 0 || N <= 0 || H <= 0 || dh <= 0) return KV_ERR_BAD_ARG;
+  if (N > 256 || dh > 64 || (dh % 8) != 0) return KV_ERR_UNSUPPORTED;   // two 128-row tiles; 16-byte d chunks
+  return KV_OK;
+}
+
+}  // namespace kv
+
+using namespace kv;
+
+extern "C" size_t kv_attn_image_bytes(int B, int N, int H, int d_head) {
+  if (B <= 0 || N <= 0 || H <= 0 || d_head <= 0) return 0;
+  return (size_t)B * H * 3 * at5::npad_of(N) * at5::dhp_of(d_head) * 2;
+}
+
+extern "C" int kv_attn_image_fwd(const void* image, const float* residual, float* out, float* lse, int B, int N,
+                                 int H, int d_head, void* stream) {
+  const int rc = attn5_check(B, N, H, d_head);
+  if (rc != KV_OK) return rc;
+  if (B == 0) return KV_OK;
+  if (image == nullptr || out == nullptr) return KV_ERR_BAD_ARG;
+  if ((reinterpret_cast<uintptr_t>(image) & 15) || (reinterpret_cast<uintptr_t>(out) & 15) ||
+      (residual && (reinterpret_cast<uintptr_t>(residual) & 15)))
+    return KV_ERR_ALIGNMENT;
+  const at5::FwdSmem L = at5::fwd_smem(N, d_head);
+  KV_SMEM_OPT_IN(at5::attn5_fwd_kernel, L.total, "attn5_fwd smem attribute");
+  at5::FwdParams p;
+  p.img = reinterpret_cast<const __nv_bfloat16*>(image);
+  p.residual = residual;
+  p.out = out;
+  p.lse = lse;
+  p.B = B; p.N = N; p.H = H; p.dh = d_head;
+  p.n_heads_total = B * H;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = p.n_heads_total < sms ? p.n_heads_total : sms;
+  at5::attn5_fwd_kernel<<<grid, at5::FWD_THREADS, L.total, (cudaStream_t)stream>>>(p);
+  KV_CHECK_LAUNCH("attn5_fwd_kernel");
+  return KV_OK;
+}

@@ -26,9 +26,10 @@ bool tc_bwd_weight_available(const kv_kan_desc_t& d);
 // layer (api.cu tc_view), d0 = the caller's descriptor that indexes the pointer table
 int tc_pack(const kv_kan_desc_t& d, const kv_kan_desc_t& d0, const uint64_t* ptr_table, const float* fparams,
             void* wtiles, void* wtiles_t, cudaStream_t st);
+// attn_image != nullptr: the epilogue writes the bf16 attention image of attn_tc5.cu instead of Y (q/k/v layer of MSA)
 int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const float* fparams,
            const float* bias, const float* mean, const float* rstd, const float* residual,
-           const float* pos, float* Y, cudaStream_t st);
+           const float* pos, float* Y, cudaStream_t st, void* attn_image = nullptr, int attn_tokens = 0);
 size_t tc_dy_image_bytes(const kv_kan_desc_t& d);  // bf16 copy of dY shared by the gradient kernels (0 = n/a)
 int tc_dy_image(const kv_kan_desc_t& d, const float* dY, const float* act_mask, void* image, cudaStream_t st);
 int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const float* act_mask, const void* dy_image,

@@ -268,6 +268,10 @@ struct FwdParams {
   float* Y;
   Geom gm;
   const float* in_mask;  // Linear only, nullable: the input is X * (in_mask > 0), same addressing as X
+  // q/k/v layer of MSA (attention.py:196-197), merged view (group = head, out = 3 * d_head): instead of fp32 Y the
+  // epilogue writes the bf16 attention image of attn_tc5.cu, img[b][h][part][n8][d8][n%8][d%8], zero padding included
+  __nv_bfloat16* attn_img;
+  int attn_N;            // tokens per sample (rows t = b * attn_N + n)
 };
 
 // 8 consecutive features of one row (zero beyond `in` / beyond T)
@@ -567,54 +571,58 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
     __syncwarp();
   } else if (warp == 1) {
     if (rank == 0) {
-      // ================= MMA issuer (leader CTA): the whole warp walks the loop, one elected lane issues ===
-      const int n1 = BN > 256 ? 256 : BN;
-      const int n2 = BN - n1;
-      const uint32_t idesc1 = ptx::make_idesc_bf16(2 * BM, n1);
-      const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(2 * BM, n2) : 0u;
-      const uint32_t sbo = 128;
-      // descriptors differ only in the 14-bit start-address field: add (bytes >> 4) per step
-      const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), (BM / 8) * 128, sbo);
-      const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)n1 * 8, sbo);
-      const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 16, (uint32_t)n2 * 8, sbo);
-      const uint32_t a_slot_step = (uint32_t)(gm.Mp * A_UNIT_BYTES) >> 4, b_unit_step = b_unit_bytes >> 4;
-      int sc = 0, sb = 0, ub = 0, u = 0;
-      uint32_t phA = 0, phB = 0;
-      for (int ch = 0; ch < gm.n_chunks; ++ch) {
-        for (int m0 = 0; m0 < M; m0 += gm.Mp) {     // one ring slot per part of the chunk
-        const int m1 = min(M, m0 + gm.Mp);
-        if (!(d.reserved & 2)) ptx::mbar_wait(fullA(sc), phA);
-        uint64_t da = da0 + (uint64_t)(sc * a_slot_step);
-        for (int q = m0; q < m1; ++q, ++u) {
-          if (ub == 0) {
-            stamp(0, u, 0);
-            if (!(d.reserved & 64)) ptx::mbar_wait(fullB(sb), phB);
-            stamp(0, u, 1);
-          }
-          ptx::tc_fence_after();
-          const uint32_t boff = (uint32_t)(sb * S + ub) * b_unit_step;
-          const bool last_of_stage = (ub + 1 == S) || (u + 1 == n_units);
-          if (ptx::elect_one()) {
-            if (!(d.reserved & 4)) {
-              ptx::mma2_bf16_ss(tmem_base, da, db1_0 + boff, idesc1, u > 0);
-              if (n2 && !(d.reserved & 128)) ptx::mma2_bf16_ss(tmem_base + 256, da, db2_0 + boff, idesc2, u > 0);
+      // ================= MMA issuer (leader CTA) =================
+      // ONE thread runs the whole issue loop.  Measured (scripts/mma_pace.cu, profiles/r02_mma_pace.txt): a warp-wide
+      // loop with an election, a warp sync and a tcgen05 fence per K=16 unit cannot issue faster than ~300 cycles
+      // per unit, while the tensor pipe retires a 256 x 512 x 16 unit in 256; a single-thread loop that fences only
+      // after its barrier waits reaches that rate, and a commit every few units costs nothing.
+      if (lane == 0) {
+        const int n1 = BN > 256 ? 256 : BN;
+        const int n2 = BN - n1;
+        const uint32_t idesc1 = ptx::make_idesc_bf16(2 * BM, n1);
+        const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(2 * BM, n2) : 0u;
+        const uint32_t sbo = 128;
+        // descriptors differ only in the 14-bit start-address field: add (bytes >> 4) per step
+        const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), (BM / 8) * 128, sbo);
+        const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)n1 * 8, sbo);
+        const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 16, (uint32_t)n2 * 8, sbo);
+        const uint32_t a_slot_step = (uint32_t)(gm.Mp * A_UNIT_BYTES) >> 4, b_unit_step = b_unit_bytes >> 4;
+        const int Mp = gm.Mp;
+        int sc = 0, sb = 0, ub = 0, u = 0;
+        uint32_t phA = 0, phB = 0;
+        uint64_t db1 = db1_0, db2 = db2_0;   // B descriptors of the current unit
+        for (int ch = 0; ch < gm.n_chunks; ++ch) {
+          for (int m0 = 0; m0 < M; m0 += Mp) {     // one ring slot per part of the chunk
+            const int m1 = min(M, m0 + Mp);
+            ptx::mbar_wait(fullA(sc), phA);
+            ptx::tc_fence_after();
+            uint64_t da = da0 + (uint64_t)(sc * a_slot_step);
+            for (int q = m0; q < m1; ++q, ++u) {
+              if (ub == 0) {
+                ptx::mbar_wait(fullB(sb), phB);
+                ptx::tc_fence_after();
+              }
+              ptx::mma2_bf16_ss(tmem_base, da, db1, idesc1, u > 0);
+              if (n2) ptx::mma2_bf16_ss(tmem_base + 256, da, db2, idesc2, u > 0);
+              da += A_UNIT_BYTES >> 4;
+              const bool last_of_stage = (ub + 1 == S) || (u + 1 == n_units);
+              if (last_of_stage) {
+                ptx::tc_commit2(emptyB(sb));
+                ub = 0;
+                if (++sb == NB) { sb = 0; phB ^= 1; }
+                db1 = db1_0 + (uint64_t)(sb * S) * b_unit_step;
+                db2 = db2_0 + (uint64_t)(sb * S) * b_unit_step;
+              } else {
+                ++ub;
+                db1 += b_unit_step;
+                db2 += b_unit_step;
+              }
             }
-            if (last_of_stage) ptx::tc_commit2(emptyB(sb));
-            if (q == m1 - 1) ptx::tc_commit2(emptyA(sc));
-            if (u + 1 == n_units) ptx::tc_commit2(tmem_full);
-          }
-          __syncwarp();
-          stamp(0, u, 3);
-          da += A_UNIT_BYTES >> 4;
-          if (last_of_stage) {
-            ub = 0;
-            if (++sb == NB) { sb = 0; phB ^= 1; }
-          } else {
-            ++ub;
+            ptx::tc_commit2(emptyA(sc));
+            if (++sc == NCH) { sc = 0; phA ^= 1; }
           }
         }
-        if (++sc == NCH) { sc = 0; phA ^= 1; }
-        }
+        ptx::tc_commit2(tmem_full);
       }
     } else if (lane == 0) {
       // ================= peer CTA: tell the leader when our half of each B stage has landed ===========
@@ -763,6 +771,47 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
                        (!p.residual || (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0) &&
                        (!p.pos || (reinterpret_cast<uintptr_t>(p.pos) & 15) == 0) &&
                        (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
+    if (p.attn_img != nullptr) {
+      // ---- attention-image epilogue: thread = token row (TMEM lane), 16-byte chunks of 8 consecutive d
+      const int te = t0 + q4 * 32 + lane;
+      const bool ok = te < d.T;
+      const int Ntok = p.attn_N, dh = out / 3;
+      const int NPAD = (Ntok + 15) / 16 * 16, DHP = (dh + 15) / 16 * 16;
+      const int bs = ok ? te / Ntok : 0, n = ok ? te - bs * Ntok : 0;
+      const size_t part_elems = (size_t)NPAD * DHP;
+      __nv_bfloat16* hb = p.attn_img + ((size_t)bs * d.n_groups + g) * 3 * part_elems;
+      auto chunk_at = [&](int part, int nn, int dd) {
+        return reinterpret_cast<uint4*>(hb + part * part_elems + ((size_t)(nn >> 3) * (DHP >> 3) + (dd >> 3)) * 64 + (nn & 7) * 8);
+      };
+      const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+      for (int cb = half; cb * 32 < BN; cb += NPW / 4) {
+        uint32_t rr[32];
+        ptx::tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + cb * 32, rr);
+        ptx::tmem_ld_wait();
+        if (!ok) continue;
+#pragma unroll
+        for (int k8 = 0; k8 < 4; ++k8) {
+          const int o = n_tile * BN + cb * 32 + 8 * k8;   // first output of the chunk (out % 8 == 0, d_head % 8 == 0)
+          if (cb * 32 + 8 * k8 >= BN || o >= out) continue;
+          float v[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(rr[8 * k8 + e]) + (p.bias ? p.bias[g * out + o + e] : 0.0f);
+          const int part = o / dh, dd = o - part * dh;
+          *chunk_at(part, n, dd) = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                                              pack_bf16(v[6], v[7]));
+          const bool last_d = (dd + 8 == dh);
+          if (last_d)
+            for (int dp = dh; dp < DHP; dp += 8) *chunk_at(part, n, dp) = zero4;          // d padding of this row
+          if (n == Ntok - 1) {                                                            // row padding of the sample
+            for (int nn = Ntok; nn < NPAD; ++nn) {
+              *chunk_at(part, nn, dd) = zero4;
+              if (last_d)
+                for (int dp = dh; dp < DHP; dp += 8) *chunk_at(part, nn, dp) = zero4;
+            }
+          }
+        }
+      }
+    } else
     for (int cb = half; cb * 32 < BN; cb += NPW / 4) {
       uint32_t rr[32];
       ptx::tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + cb * 32, rr);
@@ -828,8 +877,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
 
 template <int F>
 static int launch_fwd(const FwdParams& p, cudaStream_t st) {
-  // effkan: 16 producer warps (4 features per thread); every other family: 8 (the octet producers)
-  constexpr int NPW = (F == KV_EFFKAN) ? 16 : 8;
+  // 16 producer warps (4 features per thread) were measured SLOWER than 8 on the MLP shapes (768->3072: 966 vs
+  // 1012 TFLOP/s): the producers are not the pacing stage, and their stores compete with the MMA operand reads
+  constexpr int NPW = 8;
   KV_SMEM_OPT_IN((kan_tc_fwd_kernel<F, NPW>), SMEM_BYTES, "tc_fwd smem attribute");
   const int n_pairs = ceil_div(p.d.T, 2 * BM);
   if ((long long)n_pairs * p.gm.n_tiles > 65535 || p.d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
@@ -862,7 +912,12 @@ struct BwdGeom {
   int n_stages;  // contraction stages of 64 outputs
   int T8, O8;    // dY image extents in core matrices (T padded to 256, out padded to 64)
   int n_chunks;
-  int W1;        // M > 16 (SW > 256, n_sub = 1): the chunk is two MMAs of 256 and W1 = SW - 256 columns; else 0
+  // The tile's n_sub * SW columns are contiguous in TMEM and are issued as ONE MMA (<= 256 columns) or TWO
+  // (256 + W1): few wide instructions instead of n_sub narrow ones (a 144-column instruction runs at ~60 % of the
+  // rate of a 256-column one, scripts/mma_pace.cu)
+  int W1;        // columns of the second MMA, 0 = one MMA
+  __host__ __device__ int tile_cols() const { return n_sub * SW; }
+  __host__ __device__ int W0() const { return n_sub * SW > 256 ? 256 : n_sub * SW; }
 };
 
 __host__ __device__ inline BwdGeom make_bwd_geom(const kv_kan_desc_t& d) {
@@ -870,8 +925,10 @@ __host__ __device__ inline BwdGeom make_bwd_geom(const kv_kan_desc_t& d) {
   b.n_chunks = (d.in_features + KU - 1) / KU;
   b.SW = KU * d.M;
   b.n_sub = 512 / b.SW;
+  if (b.n_sub < 1) b.n_sub = 1;  // M > 32: no tensor-core input gradient (tc_bwd_ok); the dY image geometry still applies
   if (b.n_sub > b.n_chunks) b.n_sub = b.n_chunks;
   if (b.n_sub * b.SW * 64 > BI_B_STAGE) b.n_sub = BI_B_STAGE / (b.SW * 64);
+  if (b.n_sub < 1) b.n_sub = 1;
   b.n_tiles = (b.n_chunks + b.n_sub - 1) / b.n_sub;
   b.n_stages = (d.out_features + 63) / 64;
   {
@@ -880,7 +937,7 @@ __host__ __device__ inline BwdGeom make_bwd_geom(const kv_kan_desc_t& d) {
     b.O8 = (cover > b.n_stages * 64 ? (cover + 7) / 8 : b.n_stages * 8);
   }
   b.T8 = (d.T + 255) / 256 * 32;
-  b.W1 = b.SW > 256 ? b.SW - 256 : 0;
+  b.W1 = b.n_sub * b.SW > 256 ? b.n_sub * b.SW - 256 : 0;
   return b;
 }
 
@@ -922,33 +979,24 @@ __global__ void dy_image_kernel(const kv_kan_desc_t d, const float* __restrict__
 // SiLU branch) x 8 outputs, read as 8 x 32 contiguous bytes and written as 128 contiguous bytes.
 __global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, const uint64_t* __restrict__ tbl,
                                  __nv_bfloat16* __restrict__ wtt, BwdGeom b, int layout) {
-  const int half = b.SW / 2;
   const int xs = d.n_groups == d0.n_groups ? 1 : d0.x_share;
-  const size_t total64 = (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * b.n_sub * half;  // core matrices
+  const size_t total64 = (size_t)d.n_groups * b.n_tiles * b.n_stages * b.tile_cols();  // core matrices
   for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total64;
        idx += (size_t)gridDim.x * blockDim.x) {
     size_t r = idx;
-    int n8, o8, j, cc;
-    if (b.W1 == 0) {
-      n8 = r % (half / 8); r /= (half / 8);
-      o8 = r % 8; r /= 8;
-      j = r % b.n_sub; r /= b.n_sub;
-    } else {
-      // split chunk: [MMA 0: o8 (8)][n8 (16)] then [MMA 1: o8 (8)][n8 (W1 / 16)]
-      int q = (int)(r % half); r /= half;
-      j = 0;
-      if (q < 128) { n8 = q % 16; o8 = q / 16; }
-      else { q -= 128; n8 = q % (b.W1 / 16); o8 = q / (b.W1 / 16); n8 += 1 << 20; }
-    }
+    // per (stage, CTA rank): [MMA 0: o8 (8)][n8 (W0 / 16)] then [MMA 1: o8 (8)][n8 (W1 / 16)] core matrices; CTA `rank`
+    // stages rows [rank * W / 2, (rank + 1) * W / 2) of each MMA's W columns
+    const int W0 = b.W0(), W1 = b.W1, per = (W0 + W1) / 2;
+    int qi = (int)(r % per); r /= per;
     const int rank = r % 2; r /= 2;
     const int st = r % b.n_stages; r /= b.n_stages;
     const int tile = r % b.n_tiles; r /= b.n_tiles;
     const int g = (int)r;
+    int n8, o8, C;   // C = first tile column of this core matrix
+    if (qi < W0 / 2) { n8 = qi % (W0 / 16); o8 = qi / (W0 / 16); C = rank * (W0 / 2) + n8 * 8; }
+    else { qi -= W0 / 2; n8 = qi % (W1 / 16); o8 = qi / (W1 / 16); C = W0 + rank * (W1 / 2) + n8 * 8; }
+    const int j = C / b.SW, cc = C - j * b.SW;
     const int c = tile * b.n_sub + j;
-    // first column of this core matrix inside the chunk
-    if (b.W1 == 0) cc = rank * half + n8 * 8;
-    else if (n8 < (1 << 20)) cc = rank * 128 + n8 * 8;
-    else cc = 256 + rank * (b.W1 / 2) + (n8 - (1 << 20)) * 8;
     const int q = cc / 16, h = (cc / 8) & 1;
     uint32_t w[8][4];  // [column r8][4 output pairs]
     float v[8][8];     // [output oe][column r8]
@@ -1060,12 +1108,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
     __syncwarp();
   } else if (warp == 1) {
     if (rank == 0) {
-      // ---- MMA issuer: S[256 rows, n_sub x SW] += dY[256, 16] . Wt[SW, 16]^T
-      const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, SW);
+      if (lane == 0) {   // one thread runs the issue loop (see kan_tc_fwd_kernel)
+      // ---- MMA issuer: S[256 rows, n_sub x SW] += dY[256, 16] . Wt^T, the tile's columns as one or two wide MMAs
+      const int W0 = b.W0();
+      const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, W0);
+      const uint32_t idesc1 = b.W1 ? ptx::make_idesc_bf16(2 * BM, b.W1) : 0u;
       const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), 128, 1024);
-      const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)SW * 8, 128);
-      const uint32_t b_sub_step = (uint32_t)(SW * 64) >> 4;    // next sub-MMA's rows
-      const uint32_t b_k_step = (uint32_t)(2 * SW * 8) >> 4;   // next K=16 step: two 8-wide core columns
+      const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)W0 * 8, 128);
+      const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + W0 * 64, (uint32_t)b.W1 * 8, 128);
+      const uint32_t b_k_step = (uint32_t)(2 * W0 * 8) >> 4;   // next K=16 step: two 8-wide core columns
+      const uint32_t b_k_step1 = (uint32_t)(2 * b.W1 * 8) >> 4;
       int s = 0;
       uint32_t ph = 0;
       for (int tile = tile0; tile < tile1; ++tile) {
@@ -1076,20 +1128,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
       for (int st = 0; st < b.n_stages; ++st) {
         if (!(d.reserved & 256)) ptx::mbar_wait(full(s), ph);
         ptx::tc_fence_after();
-        if (ptx::elect_one()) {
+        {
           const uint64_t da = da0 + (uint64_t)((s * BI_A_STAGE) >> 4);
           const uint64_t db = db0 + (uint64_t)((s * BI_B_STAGE) >> 4);
+          const uint64_t db1 = db1_0 + (uint64_t)((s * BI_B_STAGE) >> 4);
 #pragma unroll
           for (int ks = 0; ks < BI_KS; ++ks) {
-            for (int j = 0; j < ((d.reserved & 1024) ? 1 : n_sub); ++j)
-              ptx::mma2_bf16_ss(tmem_base + j * SW, da + (uint64_t)(ks * 16), db + (uint64_t)(j * b_sub_step + ks * b_k_step),
-                                idesc, (st | ks) > 0);
+            ptx::mma2_bf16_ss(tmem_base, da + (uint64_t)(ks * 16), db + (uint64_t)(ks * b_k_step), idesc, (st | ks) > 0);
+            if (b.W1)
+              ptx::mma2_bf16_ss(tmem_base + 256, da + (uint64_t)(ks * 16), db1 + (uint64_t)(ks * b_k_step1), idesc1,
+                                (st | ks) > 0);
           }
           ptx::tc_commit2(empty(s));
           if (st + 1 == b.n_stages) ptx::tc_commit2(tmem_full);
         }
-        __syncwarp();
         if (++s == BI_STAGES) { s = 0; ph ^= 1; }
+      }
       }
       }
     } else if (lane == 0) {
@@ -1292,10 +1346,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     __syncwarp();
   } else if (warp == 1) {
     if (rank == 0) {
+      if (lane == 0) {   // one thread runs the issue loop (see kan_tc_fwd_kernel)
       // ---- MMA issuer: S[256 rows, n_sub x SW] += dY[256, 16] . Wt[SW, 16]^T
       // M <= 16: n_sub chunks of SW columns, one MMA each.  M > 16: one chunk, two MMAs of W0 = 256 and W1 columns
       // (each CTA stages W/2 rows of each, the second block behind the first)
-      const int W0 = b.W1 ? 256 : SW;
+      const int W0 = b.W0();
       const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, W0);
       const uint32_t idesc1 = b.W1 ? ptx::make_idesc_bf16(2 * BM, b.W1) : 0u;
       const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), 128, 1024);
@@ -1309,27 +1364,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       for (int st = 0; st < b.n_stages; ++st) {
         if (!(d.reserved & 256)) ptx::mbar_wait(full(s), ph);
         ptx::tc_fence_after();
-        if (ptx::elect_one()) {
+        {
           const uint64_t da = da0 + (uint64_t)((s * BI_A_STAGE) >> 4);
           const uint64_t db = db0 + (uint64_t)((s * BI_B_STAGE) >> 4);
           const uint64_t db1 = db1_0 + (uint64_t)((s * BI_B_STAGE) >> 4);
 #pragma unroll
           for (int ks = 0; ks < BI_KS; ++ks) {
-            if (b.W1) {
-              ptx::mma2_bf16_ss(tmem_base, da + (uint64_t)(ks * 16), db + (uint64_t)(ks * b_k_step), idesc, (st | ks) > 0);
+            ptx::mma2_bf16_ss(tmem_base, da + (uint64_t)(ks * 16), db + (uint64_t)(ks * b_k_step), idesc, (st | ks) > 0);
+            if (b.W1)
               ptx::mma2_bf16_ss(tmem_base + 256, da + (uint64_t)(ks * 16), db1 + (uint64_t)(ks * b_k_step1), idesc1,
                                 (st | ks) > 0);
-            } else {
-              for (int j = 0; j < ((d.reserved & 1024) ? 1 : n_sub); ++j)
-                ptx::mma2_bf16_ss(tmem_base + j * SW, da + (uint64_t)(ks * 16), db + (uint64_t)(j * b_sub_step + ks * b_k_step),
-                                  idesc, (st | ks) > 0);
-            }
           }
           ptx::tc_commit2(empty(s));
           if (st + 1 == b.n_stages) ptx::tc_commit2(tmem_full);
         }
-        __syncwarp();
         if (++s == BI_STAGES) { s = 0; ph ^= 1; }
+      }
       }
     } else if (lane == 0) {
       int s = 0;
@@ -1575,6 +1625,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     __syncwarp();
   } else if (warp == 1) {
     if (rank == 0) {
+      if (lane == 0) {   // one thread runs the issue loop (see kan_tc_fwd_kernel)
       // ---- MMA issuer: D[256 K', BN] += Phi^T[256, 16 t] . dY^T[BN, 16 t]^T, both operands MN-major
       const uint32_t idesc1 = ptx::make_idesc_bf16(2 * BM, n1, 1, 1);
       const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(2 * BM, n2, 1, 1) : 0u;
@@ -1589,7 +1640,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         ptx::mbar_wait(fullA(sa), pha);
         ptx::mbar_wait(fullB(sb), phb);
         ptx::tc_fence_after();
-        if (ptx::elect_one()) {
+        {
           const uint64_t da = da0 + (uint64_t)((sa * BW_A_STAGE) >> 4);
           const uint64_t db1 = db1_0 + (uint64_t)((sb * BW_B_STAGE) >> 4);
           const uint64_t db2 = db2_0 + (uint64_t)((sb * BW_B_STAGE) >> 4);
@@ -1605,9 +1656,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
           ptx::tc_commit2(emptyB(sb));
           if (st + 1 == n_stages) ptx::tc_commit2(tmem_full);
         }
-        __syncwarp();
         if (++sa == BW_NA) { sa = 0; pha ^= 1; }
         if (++sb == BW_NB) { sb = 0; phb ^= 1; }
+      }
       }
     } else if (lane == 0) {
       int s = 0;
@@ -1896,8 +1947,14 @@ int tc_dy_image(const kv_kan_desc_t& d, const float* dY, const float* act_mask, 
 
 int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const float* fparams,
            const float* bias, const float* mean, const float* rstd, const float* residual,
-           const float* pos, float* Y, cudaStream_t st) {
+           const float* pos, float* Y, cudaStream_t st, void* attn_image, int attn_tokens) {
   if (tc_supported(d) != KV_OK) return KV_ERR_UNSUPPORTED;
+  if (attn_image != nullptr) {
+    // image epilogue: merged q/k/v view (one group per head, 3 * d_head outputs), d_head a multiple of 8
+    if (attn_tokens <= 0 || d.T % attn_tokens != 0 || d.out_features % 24 != 0 || d.x_share != 1 || d.rows_in != 0 ||
+        (d.flags & KV_FLAG_RELU) || residual != nullptr || pos != nullptr)
+      return KV_ERR_UNSUPPORTED;
+  }
   tc::FwdParams p;
   p.d = d;
   p.X = X;
@@ -1911,6 +1968,8 @@ int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const flo
   p.Y = Y;
   p.gm = tc::make_geom(d);
   p.in_mask = nullptr;
+  p.attn_img = reinterpret_cast<__nv_bfloat16*>(attn_image);
+  p.attn_N = attn_tokens;
   switch (d.family) {
     case KV_LINEAR: return tc::launch_fwd<KV_LINEAR>(p, st);
     case KV_EFFKAN: return tc::launch_fwd<KV_EFFKAN>(p, st);
@@ -1944,6 +2003,8 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
     q.Y = dX;
     q.gm = tc::make_geom(q.d);
     q.in_mask = (d.flags & KV_FLAG_RELU) ? act_mask : nullptr;
+    q.attn_img = nullptr;
+    q.attn_N = 0;
     return tc::launch_fwd<KV_LINEAR>(q, st);
   }
   KV_SMEM_OPT_IN(tc::effkan8_bwd_input_kernel, tc::BI_SMEM_E8, "tc_bwd_input smem attribute");

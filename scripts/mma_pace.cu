@@ -19,6 +19,9 @@ struct Cfg {
   int writers;       // 8 extra warps writing 16-byte vectors into the A region
   int lbo, sbo;      // descriptor strides (bytes)
   int a_rot;         // rotate the A start address over this many 4 KB slots (1 = fixed)
+  int ckind;         // 0 = multicast commit (both CTAs), 1 = commit to the leader's barrier only, 2 = two multicast commits
+  int wwork;         // writers: dependent FMAs between two 16-byte stores (0 = back-to-back stores)
+  int lean;          // 1 = single-thread issue loop without per-iteration election / division
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) pace_kernel(Cfg c, unsigned long long* out) {
@@ -30,6 +33,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) pace_kernel(
   if (threadIdx.x == 0) {
     ptx::mbar_init(ptx::smem_u32(&bars[0]), 1);
     ptx::mbar_init(ptx::smem_u32(&bars[1]), 1);
+    ptx::mbar_init(ptx::smem_u32(&bars[2]), 1);
     ptx::fence_mbar_init();
   }
   for (int i = threadIdx.x * 16; i < 200 * 1024; i += 320 * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
@@ -52,16 +56,58 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) pace_kernel(
     const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(smem), c.lbo, c.sbo) | lt;
     const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(smem) + 112 * 1024, c.lbo, c.sbo) | lt;
     long long t0 = clock64();
+    if (c.lean) {
+      // one thread, no per-iteration election / warp sync / division: the tensor pipe (and the commits) set the pace
+      if (lane == 0) {
+        int rot = 0, cc = 0, bq = 0;
+        for (int u = 0; u < c.units; ++u) {
+          const uint64_t da = da0 + (uint64_t)(rot * 256);
+          const uint64_t db = db0 + (uint64_t)(bq * 1024);
+          if (c.two_cta) {
+            if (c.n1) ptx::mma2_bf16_ss(tmem, da, db, id1, u > 0);
+            if (c.n2) ptx::mma2_bf16_ss(tmem + 256, da, db + (8192 >> 4), id2, u > 0);
+          } else {
+            if (c.n1) ptx::mma_bf16_ss(tmem, da, db, id1, u > 0);
+            if (c.n2) ptx::mma_bf16_ss(tmem + 256, da, db + (8192 >> 4), id2, u > 0);
+          }
+          if (++cc == c.commit_every) {
+            cc = 0;
+            if (c.two_cta) {
+              if (c.ckind == 1) {
+                asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                 ptx::smem_u32(&bars[1])) : "memory");
+              } else {
+                ptx::tc_commit2(ptx::smem_u32(&bars[1]));
+                if (c.ckind == 2) ptx::tc_commit2(ptx::smem_u32(&bars[2]));
+              }
+            } else {
+              ptx::tc_commit(ptx::smem_u32(&bars[1]));
+            }
+          }
+          if (++rot == c.a_rot) rot = 0;
+          bq = (bq + 1) & 3;
+        }
+      }
+      __syncwarp();
+    } else
     for (int u = 0; u < c.units; ++u) {
       if (ptx::elect_one()) {
         const uint64_t da = da0 + (uint64_t)(((u % c.a_rot) * 4096) >> 4);
         const uint64_t db = db0 + (uint64_t)(((u & 3) * 16384) >> 4);
         if (c.two_cta) {
-          ptx::mma2_bf16_ss(tmem, da, db, id1, u > 0);
+          if (c.n1) ptx::mma2_bf16_ss(tmem, da, db, id1, u > 0);
           if (c.n2) ptx::mma2_bf16_ss(tmem + 256, da, db + (8192 >> 4), id2, u > 0);
-          if (c.commit_every && (u % c.commit_every) == c.commit_every - 1) ptx::tc_commit2(ptx::smem_u32(&bars[1]));
+          if (c.commit_every && (u % c.commit_every) == c.commit_every - 1) {
+            if (c.ckind == 1) {
+              asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                               ptx::smem_u32(&bars[1])) : "memory");
+            } else {
+              ptx::tc_commit2(ptx::smem_u32(&bars[1]));
+              if (c.ckind == 2) ptx::tc_commit2(ptx::smem_u32(&bars[2]));
+            }
+          }
         } else {
-          ptx::mma_bf16_ss(tmem, da, db, id1, u > 0);
+          if (c.n1) ptx::mma_bf16_ss(tmem, da, db, id1, u > 0);
           if (c.n2) ptx::mma_bf16_ss(tmem + 256, da, db + (8192 >> 4), id2, u > 0);
           if (c.commit_every && (u % c.commit_every) == c.commit_every - 1) ptx::tc_commit(ptx::smem_u32(&bars[1]));
         }
@@ -81,10 +127,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) pace_kernel(
     // producer-like traffic: every thread stores 16-byte vectors, conflict-free, into the A region
     uint8_t* base = smem + ((threadIdx.x - 64) & 127) * 16 + ((threadIdx.x - 64) >> 7) * 2048;
     int k = 0;
+    float f = (float)threadIdx.x;
     while (!stop) {
-#pragma unroll
-      for (int q = 0; q < 9; ++q)
-        *reinterpret_cast<uint4*>(base + ((k + q) % 24) * 4096) = make_uint4(k, q, k, q);
+#pragma unroll 1
+      for (int q = 0; q < 9; ++q) {
+        for (int w = 0; w < c.wwork; ++w) f = fmaf(f, 1.0001f, 0.5f);
+        *reinterpret_cast<uint4*>(base + ((k + q) % 24) * 4096) = make_uint4(k, q, __float_as_uint(f), q);
+      }
       ptx::fence_proxy_async_smem();
       ++k;
     }
@@ -108,25 +157,34 @@ int main() {
   struct Named { const char* name; Cfg c; };
   const int U = 4000;
   Named runs[] = {
-      {"2cta N=256+256 noswz (fwd 768->3072)", {256, 256, U, 0, 0, 1, 0, 2048, 128, 1}},
-      {"2cta N=256+128 noswz (fwd 3072->768)", {256, 128, U, 0, 0, 1, 0, 2048, 128, 1}},
-      {"2cta N=256 only", {256, 0, U, 0, 0, 1, 0, 2048, 128, 1}},
-      {"2cta N=128 only", {128, 0, U, 0, 0, 1, 0, 2048, 128, 1}},
-      {"2cta N=256+256 commit/1", {256, 256, U, 1, 0, 1, 0, 2048, 128, 1}},
-      {"2cta N=256+256 commit/3", {256, 256, U, 3, 0, 1, 0, 2048, 128, 1}},
-      {"2cta N=256+256 A rotates 27 slots", {256, 256, U, 0, 0, 1, 0, 2048, 128, 27}},
-      {"2cta N=256+256 + 8 writer warps", {256, 256, U, 0, 0, 1, 1, 2048, 128, 27}},
-      {"2cta N=256+256 + writers + commit/3", {256, 256, U, 3, 0, 1, 1, 2048, 128, 27}},
-      {"2cta N=256+256 swizzle128 desc (lbo 16, sbo 1024)", {256, 256, U, 0, 2, 1, 0, 16, 1024, 1}},
-      {"2cta N=256 swizzle128 desc", {256, 0, U, 0, 2, 1, 0, 16, 1024, 1}},
-      {"2cta N=256+256 noswz lbo128 sbo1024 (image layout)", {256, 256, U, 0, 0, 1, 0, 128, 1024, 1}},
-      {"1cta N=256 noswz", {256, 0, U, 0, 0, 0, 0, 2048, 128, 1}},
-      {"1cta N=256+256 noswz", {256, 256, U, 0, 0, 0, 0, 2048, 128, 1}},
-      {"1cta N=208 noswz lbo128 sbo1024 (attention S)", {208, 0, U, 0, 0, 0, 0, 128, 1024, 1}},
-      {"1cta N=64 noswz (attention PV)", {64, 0, U, 0, 0, 0, 0, 2048, 128, 1}},
+      {"warp loop floor (elect+syncwarp+div, no MMA)", {0, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 0}},
+      {"lean loop floor (no MMA)", {0, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=256+256", {256, 256, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=256+128", {256, 128, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=256", {256, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=128", {128, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=64", {64, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=256+256 A rot 27", {256, 256, U, 0, 0, 1, 0, 2048, 128, 27, 0, 0, 1}},
+      {"lean 2cta N=256+256 commit/1", {256, 256, U, 1, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=256+256 commit/3", {256, 256, U, 3, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=256+256 commit/9", {256, 256, U, 9, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=256+256 commit/9 x2", {256, 256, U, 9, 0, 1, 0, 2048, 128, 1, 2, 0, 1}},
+      {"lean 2cta N=256+256 commit/3 leader-only", {256, 256, U, 3, 0, 1, 0, 2048, 128, 1, 1, 0, 1}},
+      {"lean 2cta N=256+256 swizzle128 desc", {256, 256, U, 0, 2, 1, 0, 16, 1024, 1, 0, 0, 1}},
+      {"lean 2cta N=256+256 image layout lbo128 sbo1024", {256, 256, U, 0, 0, 1, 0, 128, 1024, 1, 0, 0, 1}},
+      {"lean 2cta N=256+256 writers wwork=0", {256, 256, U, 0, 0, 1, 1, 2048, 128, 27, 0, 0, 1}},
+      {"lean 2cta N=256+256 writers wwork=16", {256, 256, U, 0, 0, 1, 1, 2048, 128, 27, 0, 16, 1}},
+      {"lean 2cta N=256+256 writers wwork=16 commit/3", {256, 256, U, 3, 0, 1, 1, 2048, 128, 27, 0, 16, 1}},
+      {"lean 2cta N=256+256 writers wwork=16 commit/9", {256, 256, U, 9, 0, 1, 1, 2048, 128, 27, 0, 16, 1}},
+      {"lean 1cta N=256+256", {256, 256, U, 0, 0, 0, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 1cta N=256", {256, 0, U, 0, 0, 0, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 1cta N=208 image layout", {208, 0, U, 0, 0, 0, 0, 128, 1024, 1, 0, 0, 1}},
+      {"lean 1cta N=64", {64, 0, U, 0, 0, 0, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 1cta N=256+256 commit/3", {256, 256, U, 3, 0, 0, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=144 x2 commit/6", {144, 144, U, 6, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
   };
   for (auto& r : runs) {
-    for (int grid = 1; grid <= 74; grid += 73) {
+    for (int grid = 74; grid <= 74; grid += 73) {
       cudaMemset(d, 0, 16);
       cudaEvent_t e0, e1;
       cudaEventCreate(&e0);
