@@ -134,6 +134,34 @@ int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles
 int kv_kan_dy_image(const kv_kan_desc_t* d, const float* dY, const float* act_mask, void* dy_image,
                     void* stream);
 
+/* Extents of that image: [n_groups][t8_groups][o8_groups][8 rows][8 outputs] bf16, zero padded (the tensor-core view of
+ * the layer: the merged q/k/v maps of one head count as one group with 3 * d_head outputs).  For callers that write the
+ * image themselves (kv_attn_image_bwd). */
+int kv_kan_dy_image_geom(const kv_kan_desc_t* d, int* t8_groups, int* o8_groups);
+
+/* ---- MSA on the tensor cores (attention.py:181-202): q/k/v GEMM -> bf16 attention image -> tcgen05 attention ----
+ * Attention image: img[b][h][part (q, k, v)][n8][d8][n % 8][d % 8] bf16, n < roundup(N, 16), d < roundup(d_head, 16),
+ * zero padded: every 8 x 8 block is one core matrix of the tcgen05 shared-memory descriptors, so a part is one
+ * bulk copy and serves as K-major or MN-major operand alike. */
+size_t kv_attn_image_bytes(int B, int N, int H, int d_head);
+
+/* Forward of the grouped per-head q/k/v maps (the layer of kv_kan_fwd with x_share = 3, bf16 tensor-core path) whose
+ * epilogue writes the attention image instead of an fp32 Y.  T = B * tokens_per_sample rows. */
+int kv_kan_fwd_attn_image(const kv_kan_desc_t* d, const float* X, const void* wtiles_bf16, const float* fparams,
+                          const float* bias, const float* mean, const float* rstd, void* attn_image,
+                          int tokens_per_sample, void* stream);
+
+/* softmax(q k^T / sqrt(d_head)) v per (sample, head) from the image (attention.py:199-200): S and O accumulate in
+ * TMEM (tcgen05.mma), out [B*N][H*d_head] fp32 (+ residual, model.py:34), lse [B][H][N] (utils.py:222).
+ * N <= 256, d_head <= 64, d_head % 8 == 0; B = 0 probes the shape. */
+int kv_attn_image_fwd(const void* attn_image, const float* residual, float* out, float* lse, int B, int N, int H,
+                      int d_head, void* stream);
+
+/* Backward (recompute scheme of utils.py:229-295).  The gradients w.r.t. q, k, v leave as the bf16 dY image of the
+ * q/k/v layer (geometry from kv_kan_dy_image_geom), ready for kv_kan_bwd_input / kv_kan_bwd_weight with dY = NULL. */
+int kv_attn_image_bwd(const void* attn_image, const float* dout, const float* lse, void* dy_image, int B, int N, int H,
+                      int d_head, int t8_groups, int o8_groups, void* stream);
+
 /* Per-(row, slice) mean and 1/sqrt(var+eps) over `width` consecutive columns:
  * the LayerNorm statistics of FastKANLayer.layernorm (models/fastkan.py:57,68).
  * mean/rstd: [T][n_slices]. */

@@ -63,6 +63,10 @@ _SIGNATURES = {
     "kv_attn_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "kv_attn_fwd_bf16": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "kv_attn_bwd_bf16": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
+    "kv_kan_fwd_attn_image": [_DP] + [_P] * 7 + [_I, _P],
+    "kv_kan_dy_image_geom": [_DP, C.POINTER(C.c_int), C.POINTER(C.c_int)],
+    "kv_attn_image_fwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
+    "kv_attn_image_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
     "kv_attn_general_fwd": [C.POINTER(AttnGeneral)] + [_P] * 7,
     "kv_attn_general_bwd": [C.POINTER(AttnGeneral)] + [_P] * 11,
     "kv_layernorm_fwd": [_P, _P, _P, _P, _P, _P, _I, _I, _I, C.c_float, _P],
@@ -79,7 +83,8 @@ _SIGNATURES = {
     "kv_adam_step": [_P, _P, _P, _P, C.c_longlong, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _I,
                      _P, _P],
 }
-EXPORTS = ["kv_version", "kv_status_string", "kv_last_cuda_error", "kv_launch_count"] + list(_SIGNATURES)
+EXPORTS = ["kv_version", "kv_status_string", "kv_last_cuda_error", "kv_launch_count", "kv_attn_image_bytes"] + \
+    list(_SIGNATURES)
 
 _lib = None
 
@@ -110,6 +115,8 @@ def load():
         fn = getattr(lib, name)
         fn.restype = C.c_int
         fn.argtypes = args
+    lib.kv_attn_image_bytes.restype = C.c_size_t
+    lib.kv_attn_image_bytes.argtypes = [C.c_int] * 4
     _lib = lib
     return lib
 

@@ -118,7 +118,11 @@ class MSA(torch.nn.Module):
         mods = self._groups()
         if self._spec is None:
             self._spec = make_spec(mods, x_share=3)
-        qkv = ops.kan_apply(x2d, self._spec, [slots_of(m) for m in mods])
+        slots = [slots_of(m) for m in mods]
+        if ops.qkv_attention_fused_ok(self._spec, slots, N, self.n_heads, self.d_head):
+            # bf16 tensor-core route: q/k/v GEMM -> bf16 attention image -> tcgen05 attention, one autograd node
+            return ops.qkv_attention(x2d, self._spec, slots, B, N, self.n_heads, self.d_head, residual=residual)
+        qkv = ops.kan_apply(x2d, self._spec, slots)
         return ops.attention(qkv, B, N, self.n_heads, self.d_head, residual=residual)
 
     def forward(self, sequences):

@@ -384,6 +384,16 @@ int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles
   return KV_OK;
 }
 
+int kv_kan_dy_image_geom(const kv_kan_desc_t* d, int* t8_groups, int* o8_groups) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  if (t8_groups == nullptr || o8_groups == nullptr) return KV_ERR_BAD_ARG;
+  const kv_kan_desc_t v = tc_view(*d);
+  if (tc_dy_image_bytes(v) == 0) return KV_ERR_UNSUPPORTED;
+  tc_dy_image_geom(v, t8_groups, o8_groups);
+  return KV_OK;
+}
+
 int kv_kan_dy_image(const kv_kan_desc_t* d, const float* dY, const float* act_mask, void* dy_image, void* stream) {
   int rc = check_desc(d);
   if (rc != KV_OK) return rc;

@@ -30,6 +30,7 @@ int tc_pack(const kv_kan_desc_t& d, const kv_kan_desc_t& d0, const uint64_t* ptr
 int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const float* fparams,
            const float* bias, const float* mean, const float* rstd, const float* residual,
            const float* pos, float* Y, cudaStream_t st, void* attn_image = nullptr, int attn_tokens = 0);
+void tc_dy_image_geom(const kv_kan_desc_t& d, int* t8, int* o8);  // extents of the dY image in 8-row / 8-column groups
 size_t tc_dy_image_bytes(const kv_kan_desc_t& d);  // bf16 copy of dY shared by the gradient kernels (0 = n/a)
 int tc_dy_image(const kv_kan_desc_t& d, const float* dY, const float* act_mask, void* image, cudaStream_t st);
 int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const float* act_mask, const void* dy_image,

@@ -561,9 +561,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         const int nu = min(S, n_units - st * S);
         ptx::mbar_wait(emptyB(s), ph);
         stamp(1, st, 0);
-        ptx::mbar_arrive_expect_tx(fullB(s), nu * b_unit_bytes);
-        ptx::bulk_g2s(ptx::smem_u32(sB) + s * S * b_unit_bytes, src + (size_t)st * S * b_unit_bytes,
-                      nu * b_unit_bytes, fullB(s));
+        if (d.reserved & 16) {           // timing experiments: no weight traffic
+          ptx::mbar_arrive(fullB(s));
+        } else {
+          ptx::mbar_arrive_expect_tx(fullB(s), nu * b_unit_bytes);
+          ptx::bulk_g2s(ptx::smem_u32(sB) + s * S * b_unit_bytes, src + (size_t)st * S * b_unit_bytes,
+                        nu * b_unit_bytes, fullB(s));
+        }
         stamp(1, st, 1);
         if (++s == NB) { s = 0; ph ^= 1; }
       }
@@ -602,8 +606,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
                 ptx::mbar_wait(fullB(sb), phB);
                 ptx::tc_fence_after();
               }
-              ptx::mma2_bf16_ss(tmem_base, da, db1, idesc1, u > 0);
-              if (n2) ptx::mma2_bf16_ss(tmem_base + 256, da, db2, idesc2, u > 0);
+              if (!(d.reserved & 4)) {
+                ptx::mma2_bf16_ss(tmem_base, da, db1, idesc1, u > 0);
+                if (n2) ptx::mma2_bf16_ss(tmem_base + 256, da, db2, idesc2, u > 0);
+              }
               da += A_UNIT_BYTES >> 4;
               const bool last_of_stage = (ub + 1 == S) || (u + 1 == n_units);
               if (last_of_stage) {
@@ -709,6 +715,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       ptx::mbar_wait(emptyA(sc), ((slot_i / NCH) & 1) ^ 1);
       if (ptid == 0) stamp(2, ch, 0);
       uint8_t* base = sA + sc * gm.Mp * A_UNIT_BYTES + row_off;
+      if (d.reserved & 8) {              // timing experiments: no basis evaluation
+      } else
       if constexpr (F == KV_EFFKAN) {
         if (layout == LAYOUT_EFFKAN8) {            // M = 9: one part
           if constexpr (FPT == 8) effkan8_chunk(base, wg, cur, gt0, ginv_h);
@@ -1894,6 +1902,11 @@ size_t tc_wtiles_t_bytes(const kv_kan_desc_t& d) {
   if (d.family == KV_LINEAR) return tc_wtiles_bytes(linear_transposed(d));
   const tc::BwdGeom b = tc::make_bwd_geom(d);
   return (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * b.n_sub * b.SW * 64;
+}
+void tc_dy_image_geom(const kv_kan_desc_t& d, int* t8, int* o8) {
+  const tc::BwdGeom b = tc::make_bwd_geom(d);
+  *t8 = b.T8;
+  *o8 = b.O8;
 }
 size_t tc_dy_image_bytes(const kv_kan_desc_t& d) {
   if (!tc_bwd_w_ok(d)) return 0;

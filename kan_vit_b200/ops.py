@@ -212,6 +212,45 @@ class KanSpec:
         return off_t, meta, total
 
 
+def _kan_param_grads(spec, flat, d, pk, x, dy, ymask, dyimg, mean, rstd, dfp):
+    """Weight-gradient GEMM + product-rule scatter back to the module tensors.  Returns the list of gradients for
+    autograd (None where ops.GRAD_SINK took them).  dy may be None when only the bf16 dY image exists."""
+    lib = L.load()
+    dev = x.device
+    T = x.shape[0]
+    g, o, K = spec.n_groups, spec.out_features, spec.in_features * spec.M
+    st = _stream()
+    grads: List[Optional[torch.Tensor]] = [None] * len(flat)
+    dwp = torch.zeros((g, o, K), dtype=torch.float32, device=dev)
+    dbias = torch.zeros((g, o), dtype=torch.float32, device=dev) if pk["bias"] is not None else None
+    _call("kv_kan_bwd_weight", lib.kv_kan_bwd_weight, C.byref(d), x.data_ptr(), L.ptr(dy), L.ptr(ymask),
+          L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean), L.ptr(rstd), dwp.data_ptr(),
+          L.ptr(dbias), st, work=_kan_flops(spec, T), tag=_kan_tag(spec, T))
+    off_t, meta, total = spec.grad_layout(flat, dev)
+    sink = GRAD_SINK
+    wanted = [idx for idx, m in enumerate(meta) if m is not None and flat[idx].requires_grad]
+    targets = {idx: sink.target(flat[idx]) for idx in wanted} if sink is not None else {}
+    if sink is not None and all(t is not None and t.is_contiguous() for t in targets.values()):
+        ptrs = tuple(targets[idx].data_ptr() if idx in targets else 0 for idx in range(len(flat)))
+        if spec._sink_tbl is None or spec._sink_tbl[0] != ptrs:
+            spec._sink_tbl = (ptrs, torch.tensor(ptrs, dtype=torch.int64).to(dev))
+        d2 = L.KanDesc.from_buffer_copy(d)
+        d2.flags |= L.KV_FLAG_ACCUM_GRADS
+        _call("kv_kan_unpack_grads", lib.kv_kan_unpack_grads, C.byref(d2), dwp.data_ptr(), L.ptr(dfp),
+              L.ptr(dbias), pk["tbl"].data_ptr(), spec._sink_tbl[1].data_ptr(), st)
+        for idx in wanted:
+            sink.done(flat[idx])
+    else:
+        gflat = torch.empty((total,), dtype=torch.float32, device=dev)
+        gtbl = torch.where(off_t >= 0, off_t + gflat.data_ptr(), torch.zeros_like(off_t))
+        _call("kv_kan_unpack_grads", lib.kv_kan_unpack_grads, C.byref(d), dwp.data_ptr(), L.ptr(dfp),
+              L.ptr(dbias), pk["tbl"].data_ptr(), gtbl.data_ptr(), st)
+        for idx, m in enumerate(meta):
+            if m is not None and flat[idx].requires_grad:
+                grads[idx] = gflat[m[0]:m[0] + m[1]].view(m[2])
+    return grads
+
+
 class _KanFn(torch.autograd.Function):
     """Y = KAN(x) (+bias) (+pos) [relu] (+residual); optional class-token rows."""
 
@@ -308,33 +347,7 @@ class _KanFn(torch.autograd.Function):
                                               mean.data_ptr(), rstd.data_ptr(), dx_tmp.data_ptr(),
                                               dfp.data_ptr(), st)
         if need_w:
-            dwp = torch.zeros((g, o, K), dtype=torch.float32, device=dev)
-            dbias = torch.zeros((g, o), dtype=torch.float32, device=dev) if pk["bias"] is not None else None
-            _call("kv_kan_bwd_weight", lib.kv_kan_bwd_weight, C.byref(d), x.data_ptr(), dy.data_ptr(), L.ptr(ymask),
-                                          L.ptr(dyimg), L.ptr(pk["fp"]), L.ptr(mean), L.ptr(rstd), dwp.data_ptr(),
-                                          L.ptr(dbias), st, work=_kan_flops(spec, T), tag=_kan_tag(spec, T))
-            off_t, meta, total = spec.grad_layout(flat, dev)
-            sink = GRAD_SINK
-            wanted = [idx for idx, m in enumerate(meta) if m is not None and flat[idx].requires_grad]
-            targets = {idx: sink.target(flat[idx]) for idx in wanted} if sink is not None else {}
-            if sink is not None and all(t is not None and t.is_contiguous() for t in targets.values()):
-                ptrs = tuple(targets[idx].data_ptr() if idx in targets else 0 for idx in range(len(flat)))
-                if spec._sink_tbl is None or spec._sink_tbl[0] != ptrs:
-                    spec._sink_tbl = (ptrs, torch.tensor(ptrs, dtype=torch.int64).to(dev))
-                d2 = L.KanDesc.from_buffer_copy(d)
-                d2.flags |= L.KV_FLAG_ACCUM_GRADS
-                _call("kv_kan_unpack_grads", lib.kv_kan_unpack_grads, C.byref(d2), dwp.data_ptr(), L.ptr(dfp),
-                      L.ptr(dbias), pk["tbl"].data_ptr(), spec._sink_tbl[1].data_ptr(), st)
-                for idx in wanted:
-                    sink.done(flat[idx])
-            else:
-                gflat = torch.empty((total,), dtype=torch.float32, device=dev)
-                gtbl = torch.where(off_t >= 0, off_t + gflat.data_ptr(), torch.zeros_like(off_t))
-                _call("kv_kan_unpack_grads", lib.kv_kan_unpack_grads, C.byref(d), dwp.data_ptr(), L.ptr(dfp),
-                      L.ptr(dbias), pk["tbl"].data_ptr(), gtbl.data_ptr(), st)
-                for idx, m in enumerate(meta):
-                    if m is not None and flat[idx].requires_grad:
-                        grads[idx] = gflat[m[0]:m[0] + m[1]].view(m[2])
+            grads = _kan_param_grads(spec, flat, d, pk, x, dy, ymask, dyimg, mean, rstd, dfp)
         dres = dy if ctx.has_res else None
         dcls = None
         if ctx.has_cls:
@@ -393,6 +406,90 @@ class _AttnFn(torch.autograd.Function):
         _call(name, fn, qkv.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
               B, N, H, dh, _stream(), work=8.0 * B * H * N * N * dh)
         return dqkv, (dout if ctx.has_res else None), None, None, None, None
+
+
+class _QkvAttnFn(torch.autograd.Function):
+    """MSA.forward (attention.py:181-202) in bf16 mode as ONE autograd node: the grouped q/k/v KAN layer writes the
+    bf16 attention image (tensor-core operand layout) straight from its GEMM epilogue, the tcgen05 attention kernels
+    read it with bulk copies, and the attention backward emits the bf16 dY image the layer's gradient kernels read.
+    Neither an fp32 qkv / dqkv tensor nor a dy_image pass exists on this route."""
+
+    @staticmethod
+    def forward(ctx, x, residual, spec: KanSpec, dims, *flat):
+        lib = L.load()
+        B, N, H, dh = dims
+        _require_cuda(x, residual, *flat)
+        assert x.dim() == 2 and x.dtype == torch.float32 and x.is_contiguous()
+        T = x.shape[0]
+        n_in = spec.n_slices * spec.in_features
+        n_out = spec.n_groups * spec.out_features
+        extra = L.KV_FLAG_BF16_TC | (spec.dyn_flags() if spec.dyn_flags is not None else 0)
+        d = spec.desc(T, n_in, n_out, 0, 0, 0, extra)
+        tc_sizes = spec.tc_sizes(d)
+        pk = spec.packed(flat, x.device, tc_sizes, d.flags & (L.KV_FLAG_UNIFORM_GRID | L.KV_FLAG_BF16_TC))
+        pk["tc_sizes"] = tc_sizes
+        image = torch.empty((lib.kv_attn_image_bytes(B, N, H, dh),), dtype=torch.uint8, device=x.device)
+        _call("kv_kan_fwd", lib.kv_kan_fwd_attn_image, C.byref(d), x.data_ptr(), pk["wt"].data_ptr(), L.ptr(pk["fp"]),
+              L.ptr(pk["bias"]), None, None, image.data_ptr(), N, _stream(), work=_kan_flops(spec, T), tag=_kan_tag(spec, T))
+        out = torch.empty((T, H * dh), dtype=torch.float32, device=x.device)
+        lse = torch.empty((B, H, N), dtype=torch.float32, device=x.device)
+        _call("kv_attn_fwd_bf16", lib.kv_attn_image_fwd, image.data_ptr(), L.ptr(residual), out.data_ptr(), lse.data_ptr(),
+              B, N, H, dh, _stream(), work=4.0 * B * H * N * N * dh)
+        ctx.spec, ctx.flat, ctx.pk, ctx.d, ctx.dims = spec, flat, pk, d, dims
+        ctx.has_res = residual is not None
+        ctx.save_for_backward(x, image, lse)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = L.load()
+        spec, flat, pk, d = ctx.spec, ctx.flat, ctx.pk, ctx.d
+        B, N, H, dh = ctx.dims
+        x, image, lse = ctx.saved_tensors
+        dout = dout.contiguous()
+        dev, T, st = x.device, x.shape[0], _stream()
+        t8, o8 = C.c_int(0), C.c_int(0)
+        L.check(lib.kv_kan_dy_image_geom(C.byref(d), C.byref(t8), C.byref(o8)), "kv_kan_dy_image_geom")
+        dyimg = torch.empty((pk["tc_sizes"][2],), dtype=torch.uint8, device=dev)
+        _call("kv_attn_bwd_bf16", lib.kv_attn_image_bwd, image.data_ptr(), dout.data_ptr(), lse.data_ptr(), dyimg.data_ptr(),
+              B, N, H, dh, t8.value, o8.value, st, work=8.0 * B * H * N * N * dh)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            _call("kv_kan_bwd_input", lib.kv_kan_bwd_input, C.byref(d), x.data_ptr(), None, None, None,
+                  pk["wtt"].data_ptr(), dyimg.data_ptr(), L.ptr(pk["fp"]), None, None, dx.data_ptr(), None, None, st,
+                  work=_kan_flops(spec, T), tag=_kan_tag(spec, T))
+        grads = [None] * len(flat)
+        if any(t is not None and t.requires_grad for t in flat):
+            grads = _kan_param_grads(spec, flat, d, pk, x, None, None, dyimg, None, None, None)
+        return (dx, dout if ctx.has_res else None, None, None) + tuple(grads)
+
+
+def qkv_attention_fused_ok(spec: KanSpec, flat, N, H, dh) -> bool:
+    """True when MSA can take the fused image route: bf16 mode, q/k/v maps that merge into one layer per head
+    (efficient-kan on its uniform grid, ChebyKAN) without bias, both gradients on the tensor cores, and a head shape
+    the tcgen05 attention kernels serve (N <= 256, d_head <= 64, d_head % 8 == 0)."""
+    if _PRECISION != "bf16" or spec.x_share != 3 or spec.family not in (L.KV_EFFKAN, L.KV_CHEBY):
+        return False
+    if spec.out_features != dh or spec.n_groups != 3 * H:
+        return False
+    lib = L.load()
+    if lib.kv_attn_image_fwd(None, None, None, None, 0, N, H, dh, None) != 0:
+        return False
+    extra = L.KV_FLAG_BF16_TC | (spec.dyn_flags() if spec.dyn_flags is not None else 0)
+    if spec.family == L.KV_EFFKAN and not (extra & L.KV_FLAG_UNIFORM_GRID):
+        return False
+    d = spec.desc(8, spec.n_slices * spec.in_features, spec.n_groups * spec.out_features, 0, 0, 0, extra)
+    sz = spec.tc_sizes(d)
+    return sz is not None and sz[1] > 0 and sz[2] > 0
+
+
+def qkv_attention(x2d, spec: KanSpec, group_slots, B, N, H, dh, residual=None):
+    """x2d [B*N, H*dh] -> softmax(q k^T / sqrt(dh)) v (+ residual) with q, k, v = the per-head maps of ``spec``."""
+    flat = []
+    for slots in group_slots:
+        flat.extend(list(slots) + [None] * (L.KV_PTRS_PER_GROUP - len(slots)))
+    return _QkvAttnFn.apply(x2d.contiguous(), residual, spec, (B, N, H, dh), *flat)
 
 
 def attention_tc_ok(N, H, dh) -> bool:
