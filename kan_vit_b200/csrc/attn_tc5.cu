@@ -305,7 +305,8 @@ extern "C" int kv_attn_image_fwd(const void* image, const float* residual, float
       (residual && (reinterpret_cast<uintptr_t>(residual) & 15)))
     return KV_ERR_ALIGNMENT;
   const at5::FwdSmem L = at5::fwd_smem(N, d_head);
-  KV_SMEM_OPT_IN(at5::attn5_fwd_kernel, L.total, "attn5_fwd smem attribute");
+  if (L.total > 227 * 1024) return KV_ERR_BAD_SHAPE;
+  KV_SMEM_OPT_IN(at5::attn5_fwd_kernel, 227 * 1024, "attn5_fwd smem attribute");
   at5::FwdParams p;
   p.img = reinterpret_cast<const __nv_bfloat16*>(image);
   p.residual = residual;
@@ -731,7 +732,8 @@ extern "C" int kv_attn_image_bwd(const void* image, const float* dout, const flo
               "attn5_bwd zero dY image tail");
   }
   const at5::BwdSmem L = at5::bwd_smem(N, d_head);
-  KV_SMEM_OPT_IN(at5::attn5_bwd_kernel, L.total, "attn5_bwd smem attribute");
+  if (L.total > 227 * 1024) return KV_ERR_BAD_SHAPE;
+  KV_SMEM_OPT_IN(at5::attn5_bwd_kernel, 227 * 1024, "attn5_bwd smem attribute");
   at5::BwdParams p;
   p.img = reinterpret_cast<const __nv_bfloat16*>(image);
   p.dout = dout;

@@ -22,6 +22,7 @@ struct Cfg {
   int ckind;         // 0 = multicast commit (both CTAs), 1 = commit to the leader's barrier only, 2 = two multicast commits
   int wwork;         // writers: dependent FMAs between two 16-byte stores (0 = back-to-back stores)
   int lean;          // 1 = single-thread issue loop without per-iteration election / division
+  int data;          // operands: 0 = zeros, 1 = pseudo-random bf16 values in (-2, 2)
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) pace_kernel(Cfg c, unsigned long long* out) {
@@ -36,7 +37,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) pace_kernel(
     ptx::mbar_init(ptx::smem_u32(&bars[2]), 1);
     ptx::fence_mbar_init();
   }
-  for (int i = threadIdx.x * 16; i < 200 * 1024; i += 320 * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x * 16; i < 200 * 1024; i += 320 * 16) {
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (c.data) {   // bf16 pairs: sign and mantissa from a hash, exponent 126 / 127 (|x| in [0.5, 2))
+      uint32_t h = (uint32_t)i * 2654435761u + blockIdx.y * 40503u + rank * 977u;
+      uint32_t w[4];
+      for (int k = 0; k < 4; ++k) {
+        h = h * 1664525u + 1013904223u;
+        const uint32_t lo = ((h >> 3) & 0x80ffu) | (0x3f00u + ((h >> 20) & 0x80u));
+        h = h * 1664525u + 1013904223u;
+        const uint32_t hi = ((h >> 3) & 0x80ffu) | (0x3f00u + ((h >> 20) & 0x80u));
+        w[k] = lo | (hi << 16);
+      }
+      v = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    *reinterpret_cast<uint4*>(smem + i) = v;
+  }
   if (warp == 0) {
     if (c.two_cta) { ptx::tmem_alloc2(ptx::smem_u32(&tmem_slot), 512); ptx::tmem_relinquish2(); }
     else { ptx::tmem_alloc(ptx::smem_u32(&tmem_slot), 512); ptx::tmem_relinquish(); }
@@ -155,36 +171,17 @@ int main() {
   cudaMalloc(&d, 16);
   cudaFuncSetAttribute(pace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   struct Named { const char* name; Cfg c; };
-  const int U = 4000;
+  const int U = 40000;   // ~5 ms per launch: long enough for the power management to react
   Named runs[] = {
-      {"warp loop floor (elect+syncwarp+div, no MMA)", {0, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 0}},
-      {"lean loop floor (no MMA)", {0, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=256+256", {256, 256, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=256+128", {256, 128, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=256", {256, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=128", {128, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=64", {64, 0, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=256+256 A rot 27", {256, 256, U, 0, 0, 1, 0, 2048, 128, 27, 0, 0, 1}},
-      {"lean 2cta N=256+256 commit/1", {256, 256, U, 1, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=256+256 commit/3", {256, 256, U, 3, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=256+256 commit/9", {256, 256, U, 9, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=256+256 commit/9 x2", {256, 256, U, 9, 0, 1, 0, 2048, 128, 1, 2, 0, 1}},
-      {"lean 2cta N=256+256 commit/3 leader-only", {256, 256, U, 3, 0, 1, 0, 2048, 128, 1, 1, 0, 1}},
-      {"lean 2cta N=256+256 swizzle128 desc", {256, 256, U, 0, 2, 1, 0, 16, 1024, 1, 0, 0, 1}},
-      {"lean 2cta N=256+256 image layout lbo128 sbo1024", {256, 256, U, 0, 0, 1, 0, 128, 1024, 1, 0, 0, 1}},
-      {"lean 2cta N=256+256 writers wwork=0", {256, 256, U, 0, 0, 1, 1, 2048, 128, 27, 0, 0, 1}},
-      {"lean 2cta N=256+256 writers wwork=16", {256, 256, U, 0, 0, 1, 1, 2048, 128, 27, 0, 16, 1}},
-      {"lean 2cta N=256+256 writers wwork=16 commit/3", {256, 256, U, 3, 0, 1, 1, 2048, 128, 27, 0, 16, 1}},
-      {"lean 2cta N=256+256 writers wwork=16 commit/9", {256, 256, U, 9, 0, 1, 1, 2048, 128, 27, 0, 16, 1}},
-      {"lean 1cta N=256+256", {256, 256, U, 0, 0, 0, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 1cta N=256", {256, 0, U, 0, 0, 0, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 1cta N=208 image layout", {208, 0, U, 0, 0, 0, 0, 128, 1024, 1, 0, 0, 1}},
-      {"lean 1cta N=64", {64, 0, U, 0, 0, 0, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 1cta N=256+256 commit/3", {256, 256, U, 3, 0, 0, 0, 2048, 128, 1, 0, 0, 1}},
-      {"lean 2cta N=144 x2 commit/6", {144, 144, U, 6, 0, 1, 0, 2048, 128, 1, 0, 0, 1}},
+      {"lean 2cta N=256+256 zeros", {256, 256, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1, 0}},
+      {"lean 2cta N=256+256 random data", {256, 256, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1, 1}},
+      {"lean 2cta N=256+256 random data A rot 27 commit/3", {256, 256, U, 3, 0, 1, 0, 2048, 128, 27, 0, 0, 1, 1}},
+      {"lean 2cta N=256+128 random data", {256, 128, U, 0, 0, 1, 0, 2048, 128, 1, 0, 0, 1, 1}},
+      {"lean 2cta N=256+256 random data + writers wwork=16", {256, 256, U, 0, 0, 1, 1, 2048, 128, 27, 0, 16, 1, 1}},
+      {"lean 1cta N=256+256 random data", {256, 256, U, 0, 0, 0, 0, 2048, 128, 1, 0, 0, 1, 1}},
   };
   for (auto& r : runs) {
-    for (int grid = 74; grid <= 74; grid += 73) {
+    for (int grid : {1, 16, 74}) {
       cudaMemset(d, 0, 16);
       cudaEvent_t e0, e1;
       cudaEventCreate(&e0);

@@ -43,8 +43,7 @@ def test_attention_image_forward_backward(B, N, H, dh):
     lib = L.load()
     dev = torch.device("cuda:0")
     g = torch.Generator().manual_seed(B * 1000 + N)
-    q, k, v = (torch.randn((B, H, N, dh), generator=g).to(torch.bfloat16).float().to(dev) for _ in range(3))
-    q = q * 1.5
+    q, k, v = ((torch.randn((B, H, N, dh), generator=g) * sc).to(torch.bfloat16).float().to(dev) for sc in (1.5, 1.0, 1.0))
     res = torch.randn((B * N, H * dh), generator=g).to(dev)
     dout = torch.randn((B * N, H * dh), generator=g).to(dev)
     img = _pack_image(q, k, v)
