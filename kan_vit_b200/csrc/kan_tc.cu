@@ -66,12 +66,14 @@ __host__ __device__ inline Geom make_geom(const kv_kan_desc_t& d) {
   g.n_tiles = (out16 + 511) / 512;
   g.BN = ((out16 + g.n_tiles - 1) / g.n_tiles + 15) / 16 * 16;
   const int half_unit = g.BN * KU;  // bytes; each CTA of the pair stages half of a unit: BN/2 rows
-  g.S = 24576 / half_unit;
-  g.S = g.S < 1 ? 1 : (g.S > 8 ? 8 : g.S);
-  int nb = B_RING_BYTES / (g.S * half_unit);
-  g.NB = nb > NB_MAX ? NB_MAX : nb;
   g.npart = (d.M + 8) / 9;
   g.Mp = (d.M + g.npart - 1) / g.npart;
+  g.S = 24576 / half_unit;
+  g.S = g.S < 1 ? 1 : (g.S > 8 ? 8 : g.S);
+  // parts of equal size that split into whole stages of 3 units: the MMA thread's unrolled issue loop applies
+  if (d.M % g.Mp == 0 && g.Mp % 3 == 0 && g.S >= 3) g.S = 3;
+  int nb = B_RING_BYTES / (g.S * half_unit);
+  g.NB = nb > NB_MAX ? NB_MAX : nb;
   g.NCH = A_UNITS / g.Mp;
   g.effkan8 = (d.family == KV_EFFKAN && d.spline_order == 3 && d.grid_size == 5 &&
                (d.flags & KV_FLAG_UNIFORM_GRID)) ? 1 : 0;
@@ -595,21 +597,59 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         int sc = 0, sb = 0, ub = 0, u = 0;
         uint32_t phA = 0, phB = 0;
         uint64_t db1 = db1_0, db2 = db2_0;   // B descriptors of the current unit
+        const bool fast = !dbg && S == 3 && (M % Mp) == 0 && (Mp % 3) == 0 && !(d.reserved & 4);
+        if (fast) {
+          // Every part is Mp / 3 whole B stages of 3 units: one wait and one commit per stage, the six MMAs of a stage
+          // unrolled with 32-bit descriptor arithmetic.  (The generic loop below spends ~300 cycles of instruction
+          // latency per unit in this single thread -- more than the 256 cycles the tensor pipe needs for the unit.)
+          const uint32_t a_hi = (uint32_t)(da0 >> 32), b1_hi = (uint32_t)(db1_0 >> 32), b2_hi = (uint32_t)(db2_0 >> 32);
+          const uint32_t a_lo0 = (uint32_t)da0, b1_lo0 = (uint32_t)db1_0, b2_lo0 = (uint32_t)db2_0;
+          const uint32_t a_unit = A_UNIT_BYTES >> 4, stage_step = 3u * b_unit_step;
+          const int stages_per_part = Mp / 3;
+          const int n_parts_total = gm.n_chunks * (M / Mp);
+          uint32_t acc = 0;
+          for (int part = 0; part < n_parts_total; ++part) {
+            ptx::mbar_wait(fullA(sc), phA);
+            ptx::tc_fence_after();
+            uint32_t a_lo = a_lo0 + (uint32_t)sc * a_slot_step;
+            for (int st = 0; st < stages_per_part; ++st) {
+              ptx::mbar_wait(fullB(sb), phB);
+              ptx::tc_fence_after();
+              const uint32_t b1 = b1_lo0 + (uint32_t)sb * stage_step, b2 = b2_lo0 + (uint32_t)sb * stage_step;
+#pragma unroll
+              for (int k = 0; k < 3; ++k) {
+                ptx::mma2_bf16_ss_lohi(tmem_base, a_lo + k * a_unit, a_hi, b1 + k * b_unit_step, b1_hi, idesc1, acc);
+                if (n2)
+                  ptx::mma2_bf16_ss_lohi(tmem_base + 256, a_lo + k * a_unit, a_hi, b2 + k * b_unit_step, b2_hi, idesc2, acc);
+                acc = 1;
+              }
+              ptx::tc_commit2(emptyB(sb));
+              if (++sb == NB) { sb = 0; phB ^= 1; }
+              a_lo += 3 * a_unit;
+            }
+            ptx::tc_commit2(emptyA(sc));
+            if (++sc == NCH) { sc = 0; phA ^= 1; }
+          }
+        } else
         for (int ch = 0; ch < gm.n_chunks; ++ch) {
           for (int m0 = 0; m0 < M; m0 += Mp) {     // one ring slot per part of the chunk
             const int m1 = min(M, m0 + Mp);
+            if (dbg) stamp(0, u, 2);
             ptx::mbar_wait(fullA(sc), phA);
             ptx::tc_fence_after();
             uint64_t da = da0 + (uint64_t)(sc * a_slot_step);
             for (int q = m0; q < m1; ++q, ++u) {
               if (ub == 0) {
+                if (dbg) stamp(0, u, 0);
                 ptx::mbar_wait(fullB(sb), phB);
                 ptx::tc_fence_after();
+                if (dbg) stamp(0, u, 1);
               }
               if (!(d.reserved & 4)) {
                 ptx::mma2_bf16_ss(tmem_base, da, db1, idesc1, u > 0);
                 if (n2) ptx::mma2_bf16_ss(tmem_base + 256, da, db2, idesc2, u > 0);
               }
+              if (dbg) stamp(0, u, 3);
               da += A_UNIT_BYTES >> 4;
               const bool last_of_stage = (ub + 1 == S) || (u + 1 == n_units);
               if (last_of_stage) {

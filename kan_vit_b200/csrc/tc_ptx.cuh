@@ -161,6 +161,19 @@ __device__ __forceinline__ void mma2_bf16_ss(uint32_t tmem_d, uint64_t desc_a, u
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// The same with the descriptors as (lo, hi) 32-bit halves: an issue loop then advances `lo` with 32-bit adds only
+// (hi holds LBO / SBO / version and never changes).
+__device__ __forceinline__ void mma2_bf16_ss_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                  uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n\t}" ::"r"(tmem_d),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // arrive on the mbarrier at this offset in BOTH CTAs once all prior tcgen05 ops of this thread completed
 __device__ __forceinline__ void tc_commit2(uint32_t bar) {
   asm volatile(

@@ -52,6 +52,7 @@ GRAD_SINK = None
 # stay fp32 in HBM in both modes.
 _PRECISION = "fp32"
 _DEBUG_BITS = int(__import__("os").environ.get("KV_DEBUG_BITS", "0"))  # kernel timing experiments only
+_NO_FUSED_ATTN = __import__("os").environ.get("KV_NO_FUSED_ATTN") == "1"  # A/B experiments: mma.sync attention route
 
 
 def set_precision(mode: str):
@@ -469,7 +470,7 @@ def qkv_attention_fused_ok(spec: KanSpec, flat, N, H, dh) -> bool:
     """True when MSA can take the fused image route: bf16 mode, q/k/v maps that merge into one layer per head
     (efficient-kan on its uniform grid, ChebyKAN) without bias, both gradients on the tensor cores, and a head shape
     the tcgen05 attention kernels serve (N <= 256, d_head <= 64, d_head % 8 == 0)."""
-    if _PRECISION != "bf16" or spec.x_share != 3 or spec.family not in (L.KV_EFFKAN, L.KV_CHEBY):
+    if _PRECISION != "bf16" or spec.x_share != 3 or spec.family not in (L.KV_EFFKAN, L.KV_CHEBY) or _NO_FUSED_ATTN:
         return False
     if spec.out_features != dh or spec.n_groups != 3 * H:
         return False

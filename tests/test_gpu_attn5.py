@@ -69,7 +69,7 @@ def test_attention_image_forward_backward(B, N, H, dh):
             "bwd")
     torch.cuda.synchronize()
     dq, dk, dv, pad = _unpack_dy(dy, B, N, H, dh, T8, O8)
-    assert pad.abs().max().item() == 0.0
+    assert pad.numel() == 0 or pad.abs().max().item() == 0.0
     assert relerr(dv, vr.grad) < TOL
     assert relerr(dq, qr.grad) < TOL
     assert relerr(dk, kr.grad) < TOL
