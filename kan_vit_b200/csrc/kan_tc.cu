@@ -578,59 +578,62 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
   } else if (warp == 1) {
     if (rank == 0) {
       // ================= MMA issuer (leader CTA) =================
-      // ONE thread runs the whole issue loop.  Measured (scripts/mma_pace.cu, profiles/r02_mma_pace.txt): a warp-wide
-      // loop with an election, a warp sync and a tcgen05 fence per K=16 unit cannot issue faster than ~300 cycles
-      // per unit, while the tensor pipe retires a 256 x 512 x 16 unit in 256; a single-thread loop that fences only
-      // after its barrier waits reaches that rate, and a commit every few units costs nothing.
-      if (lane == 0) {
-        const int n1 = BN > 256 ? 256 : BN;
-        const int n2 = BN - n1;
-        const uint32_t idesc1 = ptx::make_idesc_bf16(2 * BM, n1);
-        const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(2 * BM, n2) : 0u;
-        const uint32_t sbo = 128;
-        // descriptors differ only in the 14-bit start-address field: add (bytes >> 4) per step
-        const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), (BM / 8) * 128, sbo);
-        const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)n1 * 8, sbo);
-        const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 16, (uint32_t)n2 * 8, sbo);
-        const uint32_t a_slot_step = (uint32_t)(gm.Mp * A_UNIT_BYTES) >> 4, b_unit_step = b_unit_bytes >> 4;
-        const int Mp = gm.Mp;
+      // Measured (scripts/mma_pace.cu, profiles/r02_mma_pace.txt, and clock stamps inside this kernel): the tensor
+      // pipe retires a 256 x 512 x 16 unit in 256 cycles, but an issue loop that spends ~60 instructions per unit in
+      // ONE thread (election, warp sync, fence, 64-bit descriptor arithmetic, per-unit branches) cannot issue faster
+      // than ~450 cycles per unit: the issuing thread, not the tensor pipe, paced the round-1 kernels.  The fast path
+      // below is walked by the whole converged warp with warp-uniform operands and elects inside the asm blocks, so
+      // it compiles to straight-line uniform-datapath code: ~7 instructions per MMA, one wait and one commit per
+      // stage of 3 units.
+      const int n1 = BN > 256 ? 256 : BN;
+      const int n2 = BN - n1;
+      const uint32_t idesc1 = ptx::make_idesc_bf16(2 * BM, n1);
+      const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(2 * BM, n2) : 0u;
+      const uint32_t sbo = 128;
+      // descriptors differ only in the 14-bit start-address field: add (bytes >> 4) per step
+      const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), (BM / 8) * 128, sbo);
+      const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)n1 * 8, sbo);
+      const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 16, (uint32_t)n2 * 8, sbo);
+      const uint32_t a_slot_step = (uint32_t)(gm.Mp * A_UNIT_BYTES) >> 4, b_unit_step = b_unit_bytes >> 4;
+      const int Mp = gm.Mp;
+      const bool fast = !dbg && S == 3 && (M % Mp) == 0 && (Mp % 3) == 0 && !(d.reserved & 4);
+      if (fast) {
+        const uint32_t a_hi = (uint32_t)(da0 >> 32), b1_hi = (uint32_t)(db1_0 >> 32), b2_hi = (uint32_t)(db2_0 >> 32);
+        const uint32_t a_lo0 = (uint32_t)da0, b1_lo0 = (uint32_t)db1_0, b2_lo0 = (uint32_t)db2_0;
+        const uint32_t a_unit = A_UNIT_BYTES >> 4, stage_step = 3u * b_unit_step;
+        const int stages_per_part = Mp / 3;
+        const int n_parts_total = gm.n_chunks * (M / Mp);
+        int sc = 0, sb = 0;
+        uint32_t phA = 0, phB = 0, acc = 0;
+        for (int part = 0; part < n_parts_total; ++part) {
+          ptx::mbar_wait(fullA(sc), phA);
+          ptx::tc_fence_after();
+          uint32_t a_lo = a_lo0 + (uint32_t)sc * a_slot_step;
+          for (int st = 0; st < stages_per_part; ++st) {
+            ptx::mbar_wait(fullB(sb), phB);
+            ptx::tc_fence_after();
+            const uint32_t b1 = b1_lo0 + (uint32_t)sb * stage_step, b2 = b2_lo0 + (uint32_t)sb * stage_step;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+              ptx::mma2_bf16_ss_lohi_elect(tmem_base, a_lo + k * a_unit, a_hi, b1 + k * b_unit_step, b1_hi, idesc1, acc);
+              if (n2)
+                ptx::mma2_bf16_ss_lohi_elect(tmem_base + 256, a_lo + k * a_unit, a_hi, b2 + k * b_unit_step, b2_hi, idesc2,
+                                             acc);
+              acc = 1;
+            }
+            ptx::tc_commit2_elect(emptyB(sb));
+            if (++sb == NB) { sb = 0; phB ^= 1; }
+            a_lo += 3 * a_unit;
+          }
+          ptx::tc_commit2_elect(emptyA(sc));
+          if (++sc == NCH) { sc = 0; phA ^= 1; }
+        }
+        ptx::tc_commit2_elect(tmem_full);
+      } else if (lane == 0) {
+        // generic loop (parts that do not split into whole stages, timing experiments): one thread
         int sc = 0, sb = 0, ub = 0, u = 0;
         uint32_t phA = 0, phB = 0;
         uint64_t db1 = db1_0, db2 = db2_0;   // B descriptors of the current unit
-        const bool fast = !dbg && S == 3 && (M % Mp) == 0 && (Mp % 3) == 0 && !(d.reserved & 4);
-        if (fast) {
-          // Every part is Mp / 3 whole B stages of 3 units: one wait and one commit per stage, the six MMAs of a stage
-          // unrolled with 32-bit descriptor arithmetic.  (The generic loop below spends ~300 cycles of instruction
-          // latency per unit in this single thread -- more than the 256 cycles the tensor pipe needs for the unit.)
-          const uint32_t a_hi = (uint32_t)(da0 >> 32), b1_hi = (uint32_t)(db1_0 >> 32), b2_hi = (uint32_t)(db2_0 >> 32);
-          const uint32_t a_lo0 = (uint32_t)da0, b1_lo0 = (uint32_t)db1_0, b2_lo0 = (uint32_t)db2_0;
-          const uint32_t a_unit = A_UNIT_BYTES >> 4, stage_step = 3u * b_unit_step;
-          const int stages_per_part = Mp / 3;
-          const int n_parts_total = gm.n_chunks * (M / Mp);
-          uint32_t acc = 0;
-          for (int part = 0; part < n_parts_total; ++part) {
-            ptx::mbar_wait(fullA(sc), phA);
-            ptx::tc_fence_after();
-            uint32_t a_lo = a_lo0 + (uint32_t)sc * a_slot_step;
-            for (int st = 0; st < stages_per_part; ++st) {
-              ptx::mbar_wait(fullB(sb), phB);
-              ptx::tc_fence_after();
-              const uint32_t b1 = b1_lo0 + (uint32_t)sb * stage_step, b2 = b2_lo0 + (uint32_t)sb * stage_step;
-#pragma unroll
-              for (int k = 0; k < 3; ++k) {
-                ptx::mma2_bf16_ss_lohi(tmem_base, a_lo + k * a_unit, a_hi, b1 + k * b_unit_step, b1_hi, idesc1, acc);
-                if (n2)
-                  ptx::mma2_bf16_ss_lohi(tmem_base + 256, a_lo + k * a_unit, a_hi, b2 + k * b_unit_step, b2_hi, idesc2, acc);
-                acc = 1;
-              }
-              ptx::tc_commit2(emptyB(sb));
-              if (++sb == NB) { sb = 0; phB ^= 1; }
-              a_lo += 3 * a_unit;
-            }
-            ptx::tc_commit2(emptyA(sc));
-            if (++sc == NCH) { sc = 0; phA ^= 1; }
-          }
-        } else
         for (int ch = 0; ch < gm.n_chunks; ++ch) {
           for (int m0 = 0; m0 < M; m0 += Mp) {     // one ring slot per part of the chunk
             const int m1 = min(M, m0 + Mp);
@@ -1156,7 +1159,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
     __syncwarp();
   } else if (warp == 1) {
     if (rank == 0) {
-      if (lane == 0) {   // one thread runs the issue loop (see kan_tc_fwd_kernel)
+      {   // the whole converged warp walks the issue loop, election inside the asm blocks (see kan_tc_fwd_kernel)
       // ---- MMA issuer: S[256 rows, n_sub x SW] += dY[256, 16] . Wt^T, the tile's columns as one or two wide MMAs
       const int W0 = b.W0();
       const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, W0);
@@ -1164,8 +1167,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
       const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), 128, 1024);
       const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)W0 * 8, 128);
       const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + W0 * 64, (uint32_t)b.W1 * 8, 128);
+      const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b1_hi = (uint32_t)(db1_0 >> 32);
+      const uint32_t a_lo0 = (uint32_t)da0, b_lo0 = (uint32_t)db0, b1_lo0 = (uint32_t)db1_0;
       const uint32_t b_k_step = (uint32_t)(2 * W0 * 8) >> 4;   // next K=16 step: two 8-wide core columns
       const uint32_t b_k_step1 = (uint32_t)(2 * b.W1 * 8) >> 4;
+      const bool two = b.W1 != 0;
       int s = 0;
       uint32_t ph = 0;
       for (int tile = tile0; tile < tile1; ++tile) {
@@ -1173,23 +1179,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
         ptx::mbar_wait_cluster(tmem_empty, (uint32_t)((tile - tile0 - 1) & 1));
         ptx::tc_fence_after();
       }
+      uint32_t acc = 0;
       for (int st = 0; st < b.n_stages; ++st) {
-        if (!(d.reserved & 256)) ptx::mbar_wait(full(s), ph);
+        ptx::mbar_wait(full(s), ph);
         ptx::tc_fence_after();
-        {
-          const uint64_t da = da0 + (uint64_t)((s * BI_A_STAGE) >> 4);
-          const uint64_t db = db0 + (uint64_t)((s * BI_B_STAGE) >> 4);
-          const uint64_t db1 = db1_0 + (uint64_t)((s * BI_B_STAGE) >> 4);
+        const uint32_t a_lo = a_lo0 + (uint32_t)((s * BI_A_STAGE) >> 4);
+        const uint32_t b_lo = b_lo0 + (uint32_t)((s * BI_B_STAGE) >> 4);
+        const uint32_t b1_lo = b1_lo0 + (uint32_t)((s * BI_B_STAGE) >> 4);
 #pragma unroll
-          for (int ks = 0; ks < BI_KS; ++ks) {
-            ptx::mma2_bf16_ss(tmem_base, da + (uint64_t)(ks * 16), db + (uint64_t)(ks * b_k_step), idesc, (st | ks) > 0);
-            if (b.W1)
-              ptx::mma2_bf16_ss(tmem_base + 256, da + (uint64_t)(ks * 16), db1 + (uint64_t)(ks * b_k_step1), idesc1,
-                                (st | ks) > 0);
-          }
-          ptx::tc_commit2(empty(s));
-          if (st + 1 == b.n_stages) ptx::tc_commit2(tmem_full);
+        for (int ks = 0; ks < BI_KS; ++ks) {
+          ptx::mma2_bf16_ss_lohi_elect(tmem_base, a_lo + ks * 16, a_hi, b_lo + ks * b_k_step, b_hi, idesc, acc);
+          if (two) ptx::mma2_bf16_ss_lohi_elect(tmem_base + 256, a_lo + ks * 16, a_hi, b1_lo + ks * b_k_step1, b1_hi, idesc1, acc);
+          acc = 1;
         }
+        ptx::tc_commit2_elect(empty(s));
+        if (st + 1 == b.n_stages) ptx::tc_commit2_elect(tmem_full);
         if (++s == BI_STAGES) { s = 0; ph ^= 1; }
       }
       }
@@ -1394,38 +1398,35 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     __syncwarp();
   } else if (warp == 1) {
     if (rank == 0) {
-      if (lane == 0) {   // one thread runs the issue loop (see kan_tc_fwd_kernel)
-      // ---- MMA issuer: S[256 rows, n_sub x SW] += dY[256, 16] . Wt[SW, 16]^T
-      // M <= 16: n_sub chunks of SW columns, one MMA each.  M > 16: one chunk, two MMAs of W0 = 256 and W1 columns
-      // (each CTA stages W/2 rows of each, the second block behind the first)
+      {   // the whole converged warp walks the issue loop, election inside the asm blocks (see kan_tc_fwd_kernel)
+      // ---- MMA issuer: S[256 rows, tile columns] += dY[256, 16] . Wt^T, the tile's columns as one or two wide MMAs
       const int W0 = b.W0();
       const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, W0);
       const uint32_t idesc1 = b.W1 ? ptx::make_idesc_bf16(2 * BM, b.W1) : 0u;
       const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), 128, 1024);
       const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)W0 * 8, 128);
       const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + W0 * 64, (uint32_t)b.W1 * 8, 128);
-      const uint32_t b_sub_step = (uint32_t)(SW * 64) >> 4;    // next sub-MMA's rows
+      const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b1_hi = (uint32_t)(db1_0 >> 32);
+      const uint32_t a_lo0 = (uint32_t)da0, b_lo0 = (uint32_t)db0, b1_lo0 = (uint32_t)db1_0;
       const uint32_t b_k_step = (uint32_t)(2 * W0 * 8) >> 4;   // next K=16 step: two 8-wide core columns
       const uint32_t b_k_step1 = (uint32_t)(2 * b.W1 * 8) >> 4;
+      const bool two = b.W1 != 0;
       int s = 0;
-      uint32_t ph = 0;
+      uint32_t ph = 0, acc = 0;
       for (int st = 0; st < b.n_stages; ++st) {
-        if (!(d.reserved & 256)) ptx::mbar_wait(full(s), ph);
+        ptx::mbar_wait(full(s), ph);
         ptx::tc_fence_after();
-        {
-          const uint64_t da = da0 + (uint64_t)((s * BI_A_STAGE) >> 4);
-          const uint64_t db = db0 + (uint64_t)((s * BI_B_STAGE) >> 4);
-          const uint64_t db1 = db1_0 + (uint64_t)((s * BI_B_STAGE) >> 4);
+        const uint32_t a_lo = a_lo0 + (uint32_t)((s * BI_A_STAGE) >> 4);
+        const uint32_t b_lo = b_lo0 + (uint32_t)((s * BI_B_STAGE) >> 4);
+        const uint32_t b1_lo = b1_lo0 + (uint32_t)((s * BI_B_STAGE) >> 4);
 #pragma unroll
-          for (int ks = 0; ks < BI_KS; ++ks) {
-            ptx::mma2_bf16_ss(tmem_base, da + (uint64_t)(ks * 16), db + (uint64_t)(ks * b_k_step), idesc, (st | ks) > 0);
-            if (b.W1)
-              ptx::mma2_bf16_ss(tmem_base + 256, da + (uint64_t)(ks * 16), db1 + (uint64_t)(ks * b_k_step1), idesc1,
-                                (st | ks) > 0);
-          }
-          ptx::tc_commit2(empty(s));
-          if (st + 1 == b.n_stages) ptx::tc_commit2(tmem_full);
+        for (int ks = 0; ks < BI_KS; ++ks) {
+          ptx::mma2_bf16_ss_lohi_elect(tmem_base, a_lo + ks * 16, a_hi, b_lo + ks * b_k_step, b_hi, idesc, acc);
+          if (two) ptx::mma2_bf16_ss_lohi_elect(tmem_base + 256, a_lo + ks * 16, a_hi, b1_lo + ks * b_k_step1, b1_hi, idesc1, acc);
+          acc = 1;
         }
+        ptx::tc_commit2_elect(empty(s));
+        if (st + 1 == b.n_stages) ptx::tc_commit2_elect(tmem_full);
         if (++s == BI_STAGES) { s = 0; ph ^= 1; }
       }
       }
@@ -1673,7 +1674,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     __syncwarp();
   } else if (warp == 1) {
     if (rank == 0) {
-      if (lane == 0) {   // one thread runs the issue loop (see kan_tc_fwd_kernel)
+      {   // the whole converged warp walks the issue loop, election inside the asm blocks (see kan_tc_fwd_kernel)
       // ---- MMA issuer: D[256 K', BN] += Phi^T[256, 16 t] . dY^T[BN, 16 t]^T, both operands MN-major
       const uint32_t idesc1 = ptx::make_idesc_bf16(2 * BM, n1, 1, 1);
       const uint32_t idesc2 = n2 ? ptx::make_idesc_bf16(2 * BM, n2, 1, 1) : 0u;
@@ -1682,28 +1683,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       // B sub-tile: [t8 (8)][o8 (nj/16)][t%8][16 B]: LBO = nj*8, SBO = 128
       const uint64_t db1_0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)n1 * 8, 128);
       const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 64, (uint32_t)n2 * 8, 128);
+      const uint32_t a_hi = (uint32_t)(da0 >> 32), b1_hi = (uint32_t)(db1_0 >> 32), b2_hi = (uint32_t)(db2_0 >> 32);
+      const uint32_t a_lo0 = (uint32_t)da0, b1_lo0 = (uint32_t)db1_0, b2_lo0 = (uint32_t)db2_0;
+      const uint32_t k1 = (uint32_t)(2 * n1 * 8) >> 4, k2 = (uint32_t)(2 * n2 * 8) >> 4;   // next K=16 step of B
+      const bool two = n2 != 0;
       int sa = 0, sb = 0;
-      uint32_t pha = 0, phb = 0;
+      uint32_t pha = 0, phb = 0, acc = 0;
       for (int st = 0; st < n_stages; ++st) {
         ptx::mbar_wait(fullA(sa), pha);
         ptx::mbar_wait(fullB(sb), phb);
         ptx::tc_fence_after();
-        {
-          const uint64_t da = da0 + (uint64_t)((sa * BW_A_STAGE) >> 4);
-          const uint64_t db1 = db1_0 + (uint64_t)((sb * BW_B_STAGE) >> 4);
-          const uint64_t db2 = db2_0 + (uint64_t)((sb * BW_B_STAGE) >> 4);
+        const uint32_t a_lo = a_lo0 + (uint32_t)((sa * BW_A_STAGE) >> 4);
+        const uint32_t b1 = b1_lo0 + (uint32_t)((sb * BW_B_STAGE) >> 4), b2 = b2_lo0 + (uint32_t)((sb * BW_B_STAGE) >> 4);
 #pragma unroll
-          for (int ks = 0; ks < 4; ++ks) {
-            ptx::mma2_bf16_ss(tmem_base, da + (uint64_t)(ks * 256), db1 + (uint64_t)((ks * 2 * n1 * 8) >> 4), idesc1,
-                              (st | ks) > 0);
-            if (n2)
-              ptx::mma2_bf16_ss(tmem_base + 256, da + (uint64_t)(ks * 256), db2 + (uint64_t)((ks * 2 * n2 * 8) >> 4),
-                                idesc2, (st | ks) > 0);
-          }
-          ptx::tc_commit2(emptyA(sa));
-          ptx::tc_commit2(emptyB(sb));
-          if (st + 1 == n_stages) ptx::tc_commit2(tmem_full);
+        for (int ks = 0; ks < 4; ++ks) {
+          ptx::mma2_bf16_ss_lohi_elect(tmem_base, a_lo + ks * 256, a_hi, b1 + ks * k1, b1_hi, idesc1, acc);
+          if (two) ptx::mma2_bf16_ss_lohi_elect(tmem_base + 256, a_lo + ks * 256, a_hi, b2 + ks * k2, b2_hi, idesc2, acc);
+          acc = 1;
         }
+        ptx::tc_commit2_elect(emptyA(sa));
+        ptx::tc_commit2_elect(emptyB(sb));
+        if (st + 1 == n_stages) ptx::tc_commit2_elect(tmem_full);
         if (++sa == BW_NA) { sa = 0; pha ^= 1; }
         if (++sb == BW_NB) { sb = 0; phb ^= 1; }
       }

@@ -174,6 +174,28 @@ __device__ __forceinline__ void mma2_bf16_ss_lohi(uint32_t tmem_d, uint32_t a_lo
       "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Variants for an issue loop that the WHOLE (converged) warp walks with warp-uniform operands: the election happens
+// inside the asm block, so the compiler sees straight-line uniform code (no per-instruction divergence handling).
+__device__ __forceinline__ void mma2_bf16_ss_lohi_elect(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                        uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n\t}" ::"r"(tmem_d),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit2_elect(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}" ::"r"(bar),
+      "h"((uint16_t)3)
+      : "memory");
+}
 // arrive on the mbarrier at this offset in BOTH CTAs once all prior tcgen05 ops of this thread completed
 __device__ __forceinline__ void tc_commit2(uint32_t bar) {
   asm volatile(
