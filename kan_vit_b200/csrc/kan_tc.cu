@@ -15,7 +15,9 @@
 //
 // Warp roles (320 threads): warp 0 = TMEM allocator + B loader, warp 1 = barrier init + MMA issuer,
 //   warps 2..9 = A producers (basis prologue), then epilogue.
+#include <cstdio>
 #include <cstdlib>
+#include <cuda.h>   // CUtensorMap and the encode entry point's types (the function itself is fetched at run time)
 #include "basis.cuh"
 #include "internal.cuh"
 #include "tc_ptx.cuh"
@@ -1072,6 +1074,7 @@ __global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, 
 }
 
 struct BwdInParams {
+  CUtensorMap tm_dy;     // dY image, box {32 words, 8 o8 (one 64-output stage), 16 t8 (this CTA's 128 rows)}
   kv_kan_desc_t d;
   const float* X;
   const __nv_bfloat16* dyimg;
@@ -1087,7 +1090,7 @@ struct BwdInParams {
   int tpc;  // effkan8 kernel: column tiles per CTA pair
 };
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8_bwd_input_kernel(const BwdInParams p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8_bwd_input_kernel(const __grid_constant__ BwdInParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + BI_STAGES * BI_A_STAGE;
@@ -1136,8 +1139,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
   if (warp == 0) {
     if (lane == 0) {
       // ---- loader: per stage 16 x 1 KB of the dY image (this CTA's 128 rows) + one copy of the weight image
-      const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.dyimg) +
-                            ((size_t)g * b.T8 + (size_t)m_tile * 16) * b.O8 * 128;
       int s = 0;
       uint32_t ph = 1;
       for (int tile = tile0; tile < tile1; ++tile) {
@@ -1147,9 +1148,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
         ptx::mbar_wait(empty(s), ph);
         ptx::mbar_arrive_expect_tx(full(s), BI_A_STAGE + b_stage_bytes);
         const uint32_t adst = ptx::smem_u32(sA) + s * BI_A_STAGE;
-#pragma unroll 4
-        for (int t8 = 0; t8 < 16; ++t8)
-          ptx::bulk_g2s(adst + t8 * 1024, asrc + ((size_t)t8 * b.O8 + (size_t)st * 8) * 128, 1024, full(s));
+        ptx::tma_load_3d(adst, &p.tm_dy, 0, st * 8, g * b.T8 + m_tile * 16, full(s));
         ptx::bulk_g2s(ptx::smem_u32(sB) + s * BI_B_STAGE, bsrc + (size_t)st * 2 * b_stage_bytes, b_stage_bytes,
                       full(s));
         if (++s == BI_STAGES) { s = 0; ph ^= 1; }
@@ -1333,7 +1332,7 @@ struct StridedFastkanDotSink {  // RBF part (m < G) and SiLU part (m == G) kept 
 };
 
 template <int F>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_bwd_input_generic_kernel(const BwdInParams p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_bwd_input_generic_kernel(const __grid_constant__ BwdInParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + BI_STAGES * BI_A_STAGE;
@@ -1377,8 +1376,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
   if (warp == 0) {
     if (lane == 0) {
       // ---- loader: per stage 16 x 1 KB of the dY image (this CTA's 128 rows) + one copy of the weight image
-      const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.dyimg) +
-                            ((size_t)g * b.T8 + (size_t)m_tile * 16) * b.O8 * 128;
       const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.wtt) +
                             (((size_t)g * b.n_tiles + tile) * b.n_stages * 2 + rank) * (size_t)b_stage_bytes;
       int s = 0;
@@ -1387,9 +1384,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         ptx::mbar_wait(empty(s), ph);
         ptx::mbar_arrive_expect_tx(full(s), BI_A_STAGE + b_stage_bytes);
         const uint32_t adst = ptx::smem_u32(sA) + s * BI_A_STAGE;
-#pragma unroll 4
-        for (int t8 = 0; t8 < 16; ++t8)
-          ptx::bulk_g2s(adst + t8 * 1024, asrc + ((size_t)t8 * b.O8 + (size_t)st * 8) * 128, 1024, full(s));
+        ptx::tma_load_3d(adst, &p.tm_dy, 0, st * 8, g * b.T8 + m_tile * 16, full(s));
         ptx::bulk_g2s(ptx::smem_u32(sB) + s * BI_B_STAGE, bsrc + (size_t)st * 2 * b_stage_bytes, b_stage_bytes,
                       full(s));
         if (++s == BI_STAGES) { s = 0; ph ^= 1; }
@@ -1574,6 +1569,7 @@ constexpr int BW_NA = 3, BW_NB = 4;
 constexpr int BW_SMEM = BW_NA * BW_A_STAGE + BW_NB * BW_B_STAGE + BAR_BYTES;
 
 struct BwdWParams {
+  CUtensorMap tm_dy1, tm_dy2;   // dY image boxes {32 words, n1/16 | n2/16 o8 (this CTA's half of a sub-MMA), 8 t8 (64 rows)}
   kv_kan_desc_t d;
   const float* X;
   const __nv_bfloat16* dyimg;
@@ -1592,7 +1588,7 @@ struct BwdWParams {
 };
 
 template <int F>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_bwd_weight_kernel(const BwdWParams p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_bwd_weight_kernel(const __grid_constant__ BwdWParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + BW_NA * BW_A_STAGE;
@@ -1653,7 +1649,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
   if (warp == 0) {
     if (lane == 0) {
       // ---- loader: this CTA's half of the dY rows of each sub-MMA, 8 row blocks per stage
-      const uint8_t* img = reinterpret_cast<const uint8_t*>(p.dyimg) + (size_t)g * b.T8 * b.O8 * 128;
       const int o8_1 = (n_tile * BN + (int)rank * (n1 / 2)) / 8;
       const int o8_2 = (n_tile * BN + n1 + (int)rank * (n2 / 2)) / 8;
       int s = 0;
@@ -1662,12 +1657,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         ptx::mbar_wait(emptyB(s), ph);
         ptx::mbar_arrive_expect_tx(fullB(s), b_stage_bytes);
         const uint32_t dst = ptx::smem_u32(sB) + s * BW_B_STAGE;
-        const int t8g = (row0 + st * 64) / 8;
-        for (int t8 = 0; t8 < 8; ++t8) {
-          const uint8_t* rowp = img + (size_t)(t8g + t8) * b.O8 * 128;
-          ptx::bulk_g2s(dst + t8 * (n1 * 8), rowp + (size_t)o8_1 * 128, n1 * 8, fullB(s));
-          if (n2) ptx::bulk_g2s(dst + n1 * 64 + t8 * (n2 * 8), rowp + (size_t)o8_2 * 128, n2 * 8, fullB(s));
-        }
+        const int t8g = g * b.T8 + (row0 + st * 64) / 8;
+        ptx::tma_load_3d(dst, &p.tm_dy1, 0, o8_1, t8g, fullB(s));
+        if (n2) ptx::tma_load_3d(dst + n1 * 64, &p.tm_dy2, 0, o8_2, t8g, fullB(s));
         if (++s == BW_NB) { s = 0; ph ^= 1; }
       }
     }
@@ -1899,6 +1891,38 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
 
 }  // namespace tc
 
+// ---- TMA tensor map of the bf16 dY image ---------------------------------------------------------------------------
+// The image [g][t8][o8][8 rows][8 outputs] is a 3-D tensor of 32-bit words: dim0 = one 128-byte core matrix (32 words),
+// dim1 = o8, dim2 = g * T8 + t8.  A box {32, n_o8, n_t8} lands in shared memory as [t8][o8][128 B] -- the operand
+// layout both gradient kernels read -- with ONE cp.async.bulk.tensor instead of n_t8 (x2) bulk copies: the loader
+// thread issued 16-17 copies per stage before and was the pacing stage of both kernels (scripts/bulk_pace.cu:
+// ~60 cycles per extra copy on top of ~500 per stage).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int encode_dy_image_map(CUtensorMap* map, const void* image, int n_groups, int T8, int O8, int box_o8, int box_t8) {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    KV_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres), "cuTensorMapEncodeTiled lookup");
+    if (qres != cudaDriverEntryPointSuccess || sym == nullptr) return KV_ERR_CUDA;
+    fn = reinterpret_cast<EncodeTiledFn>(sym);
+  }
+  const cuuint64_t dims[3] = {32, (cuuint64_t)O8, (cuuint64_t)n_groups * T8};
+  const cuuint64_t strides[2] = {128, (cuuint64_t)O8 * 128};   // bytes, dims 1 and 2
+  const cuuint32_t box[3] = {32, (cuuint32_t)box_o8, (cuuint32_t)box_t8};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void*>(image), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return KV_ERR_CUDA;
+  }
+  return KV_OK;
+}
+
 int tc_supported(const kv_kan_desc_t& d) {
   if (d.M > tc::MAX_M_TC) return KV_ERR_UNSUPPORTED;
   return KV_OK;
@@ -2073,6 +2097,10 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
   p.dXn = dXn;
   p.dfparams = dfparams;
   p.b = tc::make_bwd_geom(d);
+  {
+    const int rc = encode_dy_image_map(&p.tm_dy, dy_image, d.n_groups, p.b.T8, p.b.O8, 8, 16);
+    if (rc != KV_OK) return rc;
+  }
   const int n_pairs = ceil_div(d.T, 2 * tc::BM);
   if ((long long)n_pairs * p.b.n_tiles > 65535 || d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
   dim3 grid(2, n_pairs * p.b.n_tiles, d.n_groups);
@@ -2127,6 +2155,12 @@ int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, 
   p.dWp = dWp;
   p.b = tc::make_bwd_geom(d);
   p.gm = tc::make_geom(d);
+  {
+    const int n1 = p.gm.BN > 256 ? 256 : p.gm.BN, n2 = p.gm.BN - n1;
+    int rc = encode_dy_image_map(&p.tm_dy1, dy_image, d.n_groups, p.b.T8, p.b.O8, n1 / 16, 8);
+    if (rc == KV_OK) rc = encode_dy_image_map(&p.tm_dy2, dy_image, d.n_groups, p.b.T8, p.b.O8, n2 ? n2 / 16 : 1, 8);
+    if (rc != KV_OK) return rc;
+  }
   // K' tiles of 128 basis columns: effkan = one per 16-feature chunk (8 splines each) + one per 128 features
   // (SiLU column); Linear = one per 128 features
   p.mean = mean;
