@@ -28,15 +28,17 @@ namespace tc {
 constexpr int BM = 128;              // rows per CTA tile (UMMA M)
 constexpr int KU = 16;               // K per unit (UMMA K for bf16)
 constexpr int A_UNIT_BYTES = BM * KU * 2;
-constexpr int A_UNITS = 27;          // A ring capacity in units; holds A_UNITS / M whole chunks
+constexpr int A_UNITS = 18;          // A ring capacity in units: two default-effkan chunks (the producers need ~1/3 of a
+                                     // chunk's MMA time, so two slots keep the tensor pipe fed); the memory goes to B
 constexpr int A_RING_BYTES = A_UNITS * A_UNIT_BYTES;
-constexpr int B_RING_BYTES = 96 * 1024;
+constexpr int B_RING_BYTES = 144 * 1024;   // 6 stages of 3 units at BN = 512: the weight stream's round trip
+                                           // (commit -> loader -> L2 -> peer relay) needs more than 4 stages in flight
 constexpr int NB_MAX = 16;
 constexpr int NCH_MAX = A_UNITS;
 constexpr int N_PRODUCER_WARPS = 8;
 constexpr int NTHREADS = 32 * (2 + N_PRODUCER_WARPS);
 constexpr int BAR_BYTES = 1024;
-constexpr int DBG_BYTES = 16 * 1024;  // clock stamps of timing experiments (d.reserved & 32)
+constexpr int DBG_BYTES = 4 * 1024;   // clock stamps of timing experiments (d.reserved & 32): 4 roles x 64 entries x 4 words
 constexpr int SMEM_BYTES = A_RING_BYTES + B_RING_BYTES + BAR_BYTES + DBG_BYTES;
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_M_TC = KV_MAX_M;  // forward / weight gradient: any M (chunks are walked in parts of <= 9 bases)
@@ -68,7 +70,7 @@ __host__ __device__ inline Geom make_geom(const kv_kan_desc_t& d) {
   g.n_tiles = (out16 + 511) / 512;
   g.BN = ((out16 + g.n_tiles - 1) / g.n_tiles + 15) / 16 * 16;
   const int half_unit = g.BN * KU;  // bytes; each CTA of the pair stages half of a unit: BN/2 rows
-  g.npart = (d.M + 8) / 9;
+  g.npart = (d.M + 8) / 9;   // parts of <= 9 bases: at least two ring slots
   g.Mp = (d.M + g.npart - 1) / g.npart;
   g.S = 24576 / half_unit;
   g.S = g.S < 1 ? 1 : (g.S > 8 ? 8 : g.S);
@@ -549,7 +551,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
   const bool dbg = (d.reserved & 32) && blockIdx.y == 0 && blockIdx.z == 0;
   uint32_t* dbuf = reinterpret_cast<uint32_t*>(smem + A_RING_BYTES + B_RING_BYTES + BAR_BYTES);
   auto stamp = [&](int role, int u, int k) {
-    if (dbg && u < 256) dbuf[(role * 256 + u) * 4 + k] = (uint32_t)clock64();
+    if (dbg && u < 64) dbuf[(role * 64 + u) * 4 + k] = (uint32_t)clock64();
   };
 
   const int S = gm.S;
@@ -919,7 +921,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
   }
   ptx::cluster_sync_all();  // the peer's smem / TMEM stay alive until every MMA and epilogue is done
   if (dbg) {
-    for (int i = threadIdx.x; i < 4096; i += NTH)
+    for (int i = threadIdx.x; i < 1024; i += NTH)
       reinterpret_cast<uint32_t*>(p.Y)[(size_t)(rank * 128 + i / 512) * d.ldy + (i % 512)] = dbuf[i];
   }
   if (warp == 0) {
@@ -1587,8 +1589,13 @@ struct BwdWParams {
   const float* rstd;
 };
 
-template <int F>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_bwd_weight_kernel(const __grid_constant__ BwdWParams p) {
+// NPW = producer / epilogue warps: 8, or 16 (twice the warps per scheduler: the producers' dependent cubic / shift /
+// pack chains, not the tensor pipe, pace this kernel -- ~2400 cycles per 64-row stage against 768-1024 of MMA work)
+template <int F, int NPW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) kan_tc_bwd_weight_kernel(const __grid_constant__ BwdWParams p) {
+  constexpr int NFB = NPW / 2;          // feature blocks: a stage's 64 rows x NFB thread columns
+  constexpr int SPF = 16 / NFB;         // spline tile: features per thread (4 | 2)
+  constexpr int SLO = 16 / NFB;         // SiLU / Linear tile: 8-feature octets per thread (4 | 2)
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + BW_NA * BW_A_STAGE;
@@ -1627,7 +1634,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < BW_NA; ++s) {
-      ptx::mbar_init(fullA(s), 2 * N_PRODUCER_WARPS);
+      ptx::mbar_init(fullA(s), 2 * NPW);
       ptx::mbar_init(emptyA(s), 1);
     }
     for (int s = 0; s < BW_NB; ++s) {
@@ -1713,7 +1720,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
   } else {
     // ---- A producers: basis values of 64 rows x this tile's features per stage
     const int ptid = threadIdx.x - 64;
-    const int tl = ptid & 63, fb = ptid >> 6;          // row inside the stage, feature block (0..3)
+    const int tl = ptid & 63, fb = ptid >> 6;          // row inside the stage, feature block (0..NFB-1)
     const int xoff = (g / d.x_share) * in;
     const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0);
     float gt0 = 0.f, ginv_h = 0.f;
@@ -1745,7 +1752,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         ptx::mbar_wait(emptyA(s), ph);
         uint8_t* base = sA + s * BW_A_STAGE + row_off;
         if (tile_live) {
-          for (int oq = fb; oq < p.no; oq += 4) {
+          for (int oq = fb; oq < p.no; oq += NFB) {
             const int i0 = (g_oc0 + oq) * 8;
             float x8[8];
             load_x8(xrow, i0, in, row_ok && i0 < in, vec, x8);
@@ -1762,7 +1769,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     // Two levels of prefetch: the stripe of stage st + PF is pulled into L2, and the registers of stage st + 1 are
     // loaded BEFORE stage st is evaluated, so the L2 round trip hides under a whole stage instead of stalling
     // every stage (the producers, not the tensor pipe, paced the out = 768 layers).
-    constexpr int XN = 32;
+    constexpr int XN = 8 * SLO;
     auto load_stage = [&](int st, float (&xv)[XN]) {
       const int t = row0 + st * 64 + tl;
       const bool row_ok = t < row1;
@@ -1771,26 +1778,29 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         constexpr int PF = 8;
         const int tp = t + PF * 64;
         if (tile_live && tp < row1) {
-          const float* pf = p.X + (size_t)tp * d.ldx + xoff + (spline_tile ? feat0 + 4 * fb : feat0 + 32 * fb);
-          if ((spline_tile ? feat0 + 4 * fb : feat0 + 32 * fb) < in) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+          const float* pf = p.X + (size_t)tp * d.ldx + xoff + (spline_tile ? feat0 + SPF * fb : feat0 + 8 * SLO * fb);
+          if ((spline_tile ? feat0 + SPF * fb : feat0 + 8 * SLO * fb) < in) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
         }
       }
       if (!tile_live) return;
       if (spline_tile) {
-        // 4 features per thread: features feat0 + 4*fb .. +3
-        const int i0 = feat0 + 4 * fb;
-        if (row_ok && vec && i0 + 4 <= in) {
+        // SPF features per thread: features feat0 + SPF*fb .. + SPF-1
+        const int i0 = feat0 + SPF * fb;
+        if (SPF == 4 && row_ok && vec && i0 + 4 <= in) {
           const float4 a = __ldg(reinterpret_cast<const float4*>(xrow + i0));
           xv[0] = a.x; xv[1] = a.y; xv[2] = a.z; xv[3] = a.w;
+        } else if (SPF == 2 && row_ok && vec && i0 + 2 <= in) {
+          const float2 a = __ldg(reinterpret_cast<const float2*>(xrow + i0));
+          xv[0] = a.x; xv[1] = a.y;
         } else {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) xv[q] = (row_ok && i0 + q < in) ? __ldg(xrow + i0 + q) : 0.0f;
+          for (int q = 0; q < SPF; ++q) xv[q] = (row_ok && i0 + q < in) ? __ldg(xrow + i0 + q) : 0.0f;
         }
       } else {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < SLO; ++k) {
           float t8v[8];
-          load_x8(xrow, feat0 + 32 * fb + 8 * k, in, row_ok, vec, t8v);
+          load_x8(xrow, feat0 + 8 * SLO * fb + 8 * k, in, row_ok, vec, t8v);
 #pragma unroll
           for (int q = 0; q < 8; ++q) xv[8 * k + q] = t8v[q];
         }
@@ -1807,7 +1817,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       if (tile_live) {
         if (spline_tile) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
+          for (int q = 0; q < SPF; ++q) {
             const float u = (xv[q] - gt0) * ginv_h;
             const float jf = floorf(u);
             const float sfr = u - jf;
@@ -1823,16 +1833,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
             const int sh = (j - 3) * 16;
             const uint64_t lo = shl64(W, sh) | shr64(W, -sh);
             const uint64_t hi = shl64(W, sh - 64) | shr64(W, 64 - sh);
-            // feature f = 4*fb + q of the chunk owns K' block f (8 splines)
-            sts128(base + (4 * fb + q) * 128, (uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+            // feature f = SPF*fb + q of the chunk owns K' block f (8 splines)
+            sts128(base + (SPF * fb + q) * 128, (uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
           }
         } else {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
+          for (int k = 0; k < SLO; ++k) {
             float v[8];
 #pragma unroll
             for (int q = 0; q < 8; ++q) v[q] = (F == KV_EFFKAN) ? fast_silu(xv[8 * k + q]) : xv[8 * k + q];
-            sts128(base + (4 * fb + k) * 128, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+            sts128(base + (SLO * fb + k) * 128, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
                    pack_bf16(v[6], v[7]));
           }
         }
@@ -1867,7 +1877,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       }
       const int M = d.M, K = in * M, out = d.out_features;
       float* dst = p.dWp + (size_t)g * out * K + (size_t)i * M + m;
-      for (int cb = half; cb * 32 < BN; cb += 2) {
+      for (int cb = half; cb * 32 < BN; cb += NPW / 4) {
         uint32_t rr[32];
         ptx::tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + cb * 32, rr);
         ptx::tmem_ld_wait();
@@ -2138,8 +2148,14 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
 
 template <int F>
 static int launch_bwd_weight(const tc::BwdWParams& p, dim3 grid, cudaStream_t st) {
-  KV_SMEM_OPT_IN(tc::kan_tc_bwd_weight_kernel<F>, tc::BW_SMEM, "tc_bwd_weight smem attribute");
-  tc::kan_tc_bwd_weight_kernel<F><<<grid, tc::NTHREADS, tc::BW_SMEM, st>>>(p);
+  // effkan default layout / Linear tiles: 16 producer warps; generic octet x basis tiles: 8
+  if (!p.generic && (F == KV_EFFKAN || F == KV_LINEAR)) {
+    KV_SMEM_OPT_IN((tc::kan_tc_bwd_weight_kernel<F, 16>), tc::BW_SMEM, "tc_bwd_weight smem attribute");
+    tc::kan_tc_bwd_weight_kernel<F, 16><<<grid, 32 * 18, tc::BW_SMEM, st>>>(p);
+  } else {
+    KV_SMEM_OPT_IN((tc::kan_tc_bwd_weight_kernel<F, 8>), tc::BW_SMEM, "tc_bwd_weight smem attribute");
+    tc::kan_tc_bwd_weight_kernel<F, 8><<<grid, 32 * 10, tc::BW_SMEM, st>>>(p);
+  }
   KV_CHECK_LAUNCH("kan_tc_bwd_weight_kernel");
   return KV_OK;
 }
