@@ -600,7 +600,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 16, (uint32_t)n2 * 8, sbo);
       const uint32_t a_slot_step = (uint32_t)(gm.Mp * A_UNIT_BYTES) >> 4, b_unit_step = b_unit_bytes >> 4;
       const int Mp = gm.Mp;
-      const bool fast = !dbg && S == 3 && (M % Mp) == 0 && (Mp % 3) == 0 && !(d.reserved & 4);
+      const bool fast = !(d.reserved & 2048) && S == 3 && (M % Mp) == 0 && (Mp % 3) == 0 && !(d.reserved & 4);
       if (fast) {
         const uint32_t a_hi = (uint32_t)(da0 >> 32), b1_hi = (uint32_t)(db1_0 >> 32), b2_hi = (uint32_t)(db2_0 >> 32);
         const uint32_t a_lo0 = (uint32_t)da0, b1_lo0 = (uint32_t)db1_0, b2_lo0 = (uint32_t)db2_0;
@@ -609,13 +609,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         const int n_parts_total = gm.n_chunks * (M / Mp);
         int sc = 0, sb = 0;
         uint32_t phA = 0, phB = 0, acc = 0;
+        int gst = 0;
         for (int part = 0; part < n_parts_total; ++part) {
+          if (dbg && lane == 0) stamp(0, gst, 2);
           ptx::mbar_wait(fullA(sc), phA);
           ptx::tc_fence_after();
           uint32_t a_lo = a_lo0 + (uint32_t)sc * a_slot_step;
-          for (int st = 0; st < stages_per_part; ++st) {
+          for (int st = 0; st < stages_per_part; ++st, ++gst) {
+            if (dbg && lane == 0) stamp(0, gst, 0);
             ptx::mbar_wait(fullB(sb), phB);
             ptx::tc_fence_after();
+            if (dbg && lane == 0) stamp(0, gst, 1);
             const uint32_t b1 = b1_lo0 + (uint32_t)sb * stage_step, b2 = b2_lo0 + (uint32_t)sb * stage_step;
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
@@ -1662,11 +1666,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       uint32_t ph = 1;
       for (int st = 0; st < n_stages; ++st) {
         ptx::mbar_wait(emptyB(s), ph);
-        ptx::mbar_arrive_expect_tx(fullB(s), b_stage_bytes);
-        const uint32_t dst = ptx::smem_u32(sB) + s * BW_B_STAGE;
-        const int t8g = g * b.T8 + (row0 + st * 64) / 8;
-        ptx::tma_load_3d(dst, &p.tm_dy1, 0, o8_1, t8g, fullB(s));
-        if (n2) ptx::tma_load_3d(dst + n1 * 64, &p.tm_dy2, 0, o8_2, t8g, fullB(s));
+        if (d.reserved & 16) {   // timing experiments: no dY traffic
+          ptx::mbar_arrive(fullB(s));
+        } else {
+          ptx::mbar_arrive_expect_tx(fullB(s), b_stage_bytes);
+          const uint32_t dst = ptx::smem_u32(sB) + s * BW_B_STAGE;
+          const int t8g = g * b.T8 + (row0 + st * 64) / 8;
+          ptx::tma_load_3d(dst, &p.tm_dy1, 0, o8_1, t8g, fullB(s));
+          if (n2) ptx::tma_load_3d(dst + n1 * 64, &p.tm_dy2, 0, o8_2, t8g, fullB(s));
+        }
         if (++s == BW_NB) { s = 0; ph ^= 1; }
       }
     }
@@ -1696,6 +1704,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         const uint32_t b1 = b1_lo0 + (uint32_t)((sb * BW_B_STAGE) >> 4), b2 = b2_lo0 + (uint32_t)((sb * BW_B_STAGE) >> 4);
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
+          if (d.reserved & 4) break;   // timing experiments: no MMAs
           ptx::mma2_bf16_ss_lohi_elect(tmem_base, a_lo + ks * 256, a_hi, b1 + ks * k1, b1_hi, idesc1, acc);
           if (two) ptx::mma2_bf16_ss_lohi_elect(tmem_base + 256, a_lo + ks * 256, a_hi, b2 + ks * k2, b2_hi, idesc2, acc);
           acc = 1;
@@ -1814,7 +1823,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       if (st + 1 < n_stages) load_stage(st + 1, xnext);
       ptx::mbar_wait(emptyA(s), ph);
       uint8_t* base = sA + s * BW_A_STAGE + row_off;
-      if (tile_live) {
+      if (tile_live && !(d.reserved & 8)) {
         if (spline_tile) {
 #pragma unroll
           for (int q = 0; q < SPF; ++q) {
@@ -1858,7 +1867,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
     // ---- epilogue: TMEM lane = basis column K', column = output; fp32 RED into dWp[g][o][i*M+m]
     ptx::mbar_wait(tmem_full, 0);
     ptx::tc_fence_after();
-    if (tile_live) {
+    if (tile_live && !(d.reserved & 64)) {
       const int pw = warp - 2;
       const int q4 = warp & 3, half = pw >> 2;
       const int l = q4 * 32 + lane;  // K' index inside the tile

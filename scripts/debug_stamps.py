@@ -18,7 +18,7 @@ for rank in range(2):
     d = y[rank * 128: rank * 128 + 2, :512].contiguous().view(torch.int32).cpu().view(4, 64, 4).long() & 0xffffffff
     t0 = int(d[1, 0, 0])
     f = lambda v: (int(v) - t0) & 0xffffffff
-    print("CTA rank", rank, "roles: 0=mma(u: before fullB wait, after, before fullA wait (chunk start), after issue) 1=loader(u: emptyB ok, issued) 2=producer(chunk: emptyA ok, arrived) 3=relay(u: fullB, arrived)")
+    print("CTA rank", rank, "roles: 0=mma(stage: before fullB wait, after, before fullA wait (part start), -) 1=loader(u: emptyB ok, issued) 2=producer(chunk: emptyA ok, arrived) 3=relay(u: fullB, arrived)")
     for u in list(range(0, 64)):
         print(u, "mma", [f(d[0, u, k]) for k in range(4)], "load", [f(d[1, u, k]) for k in range(2)],
               "prod", [f(d[2, u, k]) for k in range(2)], "relay", [f(d[3, u, k]) for k in range(2)])
