@@ -1815,12 +1815,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         }
       }
     };
-    float xv[XN], xnext[XN];
-#pragma unroll
-    for (int q = 0; q < XN; ++q) xv[q] = xnext[q] = 0.0f;
-    if (n_stages > 0) load_stage(0, xv);
-    for (int st = 0; st < n_stages; ++st) {
-      if (st + 1 < n_stages) load_stage(st + 1, xnext);
+    // Register ring of three stages: the loads of stage st + 2 are issued before stage st is evaluated.  With a
+    // distance of one stage the L2 round trip (~1000 cycles) was the per-stage floor of this kernel (the evaluation
+    // itself takes less), i.e. the producers were LATENCY-bound -- measured: the empty skeleton of the kernel ran at
+    // 70 % of the full kernel's time.
+    auto produce_stage = [&](const float (&xv)[XN]) {
       ptx::mbar_wait(emptyA(s), ph);
       uint8_t* base = sA + s * BW_A_STAGE + row_off;
       if (tile_live && !(d.reserved & 8)) {
@@ -1860,8 +1859,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(s), 0));
       if (++s == BW_NA) { s = 0; ph ^= 1; }
+    };
+    float x0[XN], x1[XN], x2[XN];
 #pragma unroll
-      for (int q = 0; q < XN; ++q) xv[q] = xnext[q];
+    for (int q = 0; q < XN; ++q) x0[q] = x1[q] = x2[q] = 0.0f;
+    if (n_stages > 0) load_stage(0, x0);
+    if (n_stages > 1) load_stage(1, x1);
+    for (int st = 0; st < n_stages; st += 3) {
+      if (st + 2 < n_stages) load_stage(st + 2, x2);
+      produce_stage(x0);
+      if (st + 1 >= n_stages) break;
+      if (st + 3 < n_stages) load_stage(st + 3, x0);
+      produce_stage(x1);
+      if (st + 2 >= n_stages) break;
+      if (st + 4 < n_stages) load_stage(st + 4, x1);
+      produce_stage(x2);
     }
     }
     // ---- epilogue: TMEM lane = basis column K', column = output; fp32 RED into dWp[g][o][i*M+m]
