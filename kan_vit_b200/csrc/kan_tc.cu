@@ -1572,10 +1572,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
 constexpr int BW_A_STAGE = 16 * 1024;   // 64 t x 128 K' x 2 B
 constexpr int BW_B_STAGE = 32 * 1024;   // 64 t x BN/2 x 2 B
 constexpr int BW_NA = 3, BW_NB = 4;
-constexpr int BW_SMEM = BW_NA * BW_A_STAGE + BW_NB * BW_B_STAGE + BAR_BYTES;
+constexpr int BW_NX = 4;                // X ring (spline tiles): TMA-staged fp32 tiles of 64 rows x 16 features
+constexpr int BW_X_STAGE = 64 * 16 * 4; // 4 KB, SWIZZLE_64B
+constexpr int BW_SMEM = BW_NA * BW_A_STAGE + BW_NB * BW_B_STAGE + BW_NX * BW_X_STAGE + BAR_BYTES;
 
 struct BwdWParams {
   CUtensorMap tm_dy1, tm_dy2;   // dY image boxes {32 words, n1/16 | n2/16 o8 (this CTA's half of a sub-MMA), 8 t8 (64 rows)}
+  CUtensorMap tm_x;             // X [T][ldx] fp32, box {16 features, 64 rows}, SWIZZLE_64B (spline tiles; use_tma_x)
+  int use_tma_x;
   kv_kan_desc_t d;
   const float* X;
   const __nv_bfloat16* dyimg;
@@ -1603,14 +1607,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + BW_NA * BW_A_STAGE;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BW_NA * BW_A_STAGE + BW_NB * BW_B_STAGE);
+  uint8_t* sX = smem + BW_NA * BW_A_STAGE + BW_NB * BW_B_STAGE;   // 1024-byte aligned (swizzle atom = 512 B)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BW_NA * BW_A_STAGE + BW_NB * BW_B_STAGE + BW_NX * BW_X_STAGE);
   const uint32_t bar0 = ptx::smem_u32(bars);
   auto fullA = [&](int s) { return bar0 + 8u * s; };
   auto emptyA = [&](int s) { return bar0 + 8u * (BW_NA + s); };
   auto fullB = [&](int s) { return bar0 + 8u * (2 * BW_NA + s); };
   auto emptyB = [&](int s) { return bar0 + 8u * (2 * BW_NA + BW_NB + s); };
   const uint32_t tmem_full = bar0 + 8u * (2 * BW_NA + 2 * BW_NB);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * BW_NA + 2 * BW_NB + 1);
+  auto fullX = [&](int s) { return bar0 + 8u * (2 * BW_NA + 2 * BW_NB + 1 + s); };
+  auto emptyX = [&](int s) { return bar0 + 8u * (2 * BW_NA + 2 * BW_NB + 1 + BW_NX + s); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * BW_NA + 2 * BW_NB + 1 + 2 * BW_NX);
 
   const kv_kan_desc_t& d = p.d;
   const BwdGeom b = p.b;
@@ -1646,6 +1653,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       ptx::mbar_init(emptyB(s), 1);
     }
     ptx::mbar_init(tmem_full, 1);
+    for (int s = 0; s < BW_NX; ++s) {
+      ptx::mbar_init(fullX(s), 1);
+      ptx::mbar_init(emptyX(s), NPW);
+    }
     ptx::fence_mbar_init();
   }
   if (warp == 0) {
@@ -1662,9 +1673,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       // ---- loader: this CTA's half of the dY rows of each sub-MMA, 8 row blocks per stage
       const int o8_1 = (n_tile * BN + (int)rank * (n1 / 2)) / 8;
       const int o8_2 = (n_tile * BN + n1 + (int)rank * (n2 / 2)) / 8;
-      int s = 0;
-      uint32_t ph = 1;
+      int s = 0, sx = 0;
+      uint32_t ph = 1, phx = 1;
+      const bool tma_x = p.use_tma_x && tile_live && spline_tile;
+      const int xcol = (g / d.x_share) * in + feat0;
       for (int st = 0; st < n_stages; ++st) {
+        if (tma_x) {   // this CTA's X tile of the stage: 64 rows x the chunk's 16 features, one tensor copy
+          ptx::mbar_wait(emptyX(sx), phx);
+          ptx::mbar_arrive_expect_tx(fullX(sx), BW_X_STAGE);
+          ptx::tma_load_2d(ptx::smem_u32(sX) + sx * BW_X_STAGE, &p.tm_x, xcol, row0 + st * 64, fullX(sx));
+          if (++sx == BW_NX) { sx = 0; phx ^= 1; }
+        }
         ptx::mbar_wait(emptyB(s), ph);
         if (d.reserved & 16) {   // timing experiments: no dY traffic
           ptx::mbar_arrive(fullB(s));
@@ -1780,6 +1799,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
     // every stage (the producers, not the tensor pipe, paced the out = 768 layers).
     constexpr int XN = 8 * SLO;
     auto load_stage = [&](int st, float (&xv)[XN]) {
+      if (d.reserved & 256) return;   // timing experiments: no X traffic
       const int t = row0 + st * 64 + tl;
       const bool row_ok = t < row1;
       const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
@@ -1815,10 +1835,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         }
       }
     };
-    // Register ring of three stages: the loads of stage st + 2 are issued before stage st is evaluated.  With a
-    // distance of one stage the L2 round trip (~1000 cycles) was the per-stage floor of this kernel (the evaluation
-    // itself takes less), i.e. the producers were LATENCY-bound -- measured: the empty skeleton of the kernel ran at
-    // 70 % of the full kernel's time.
+    // One stage of the A operand from the stage's inputs xv
     auto produce_stage = [&](const float (&xv)[XN]) {
       ptx::mbar_wait(emptyA(s), ph);
       uint8_t* base = sA + s * BW_A_STAGE + row_off;
@@ -1860,20 +1877,44 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(s), 0));
       if (++s == BW_NA) { s = 0; ph ^= 1; }
     };
-    float x0[XN], x1[XN], x2[XN];
+    float xv[XN], xnext[XN];
 #pragma unroll
-    for (int q = 0; q < XN; ++q) x0[q] = x1[q] = x2[q] = 0.0f;
-    if (n_stages > 0) load_stage(0, x0);
-    if (n_stages > 1) load_stage(1, x1);
-    for (int st = 0; st < n_stages; st += 3) {
-      if (st + 2 < n_stages) load_stage(st + 2, x2);
-      produce_stage(x0);
-      if (st + 1 >= n_stages) break;
-      if (st + 3 < n_stages) load_stage(st + 3, x0);
-      produce_stage(x1);
-      if (st + 2 >= n_stages) break;
-      if (st + 4 < n_stages) load_stage(st + 4, x1);
-      produce_stage(x2);
+    for (int q = 0; q < XN; ++q) xv[q] = xnext[q] = 0.0f;
+    // Spline tiles with a TMA-able X: the loader thread stages the stage's 64 x 16 fp32 tile in shared memory
+    // (cp.async.bulk.tensor, BW_NX stages deep) and every thread picks its SPF values from there.  The per-thread
+    // LDG route issues one 32-byte sector request per thread and stage (plus an L2 prefetch each): measured, that
+    // request stream -- not the evaluation, not the MMAs -- took 0.8 of this kernel's 2.6 ms (768 -> 3072, T = 66 192).
+    const bool tma_x = p.use_tma_x && tile_live && spline_tile;
+    int sx = 0;
+    uint32_t phx = 0;
+    // byte offset of this thread's values inside a stage: row tl, 16-byte chunk XOR-swizzled (SWIZZLE_64B)
+    const int xoff_b = tl * 64 + ((((fb * SPF * 4) >> 4) ^ ((tl >> 1) & 3)) << 4) + ((fb * SPF * 4) & 15);
+    if (n_stages > 0 && !tma_x) load_stage(0, xv);
+    for (int st = 0; st < n_stages; ++st) {
+      if (tma_x) {
+        ptx::mbar_wait(fullX(sx), phx);
+        const uint8_t* xs = sX + sx * BW_X_STAGE + xoff_b;
+        if (SPF == 4) {
+          const float4 a4 = *reinterpret_cast<const float4*>(xs);
+          xv[0] = a4.x; xv[1] = a4.y; xv[2] = a4.z; xv[3] = a4.w;
+        } else {
+          const float2 a2 = *reinterpret_cast<const float2*>(xs);
+          xv[0] = a2.x; xv[1] = a2.y;
+        }
+#pragma unroll
+        for (int q = 0; q < SPF; ++q)
+          if (feat0 + SPF * fb + q >= in) xv[q] = 0.0f;   // beyond this group's features (a neighbour's columns)
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(emptyX(sx));
+        if (++sx == BW_NX) { sx = 0; phx ^= 1; }
+      } else if (st + 1 < n_stages) {
+        load_stage(st + 1, xnext);
+      }
+      produce_stage(xv);
+      if (!tma_x) {
+#pragma unroll
+        for (int q = 0; q < XN; ++q) xv[q] = xnext[q];
+      }
     }
     }
     // ---- epilogue: TMEM lane = basis column K', column = output; fp32 RED into dWp[g][o][i*M+m]
@@ -1949,6 +1990,27 @@ static int encode_dy_image_map(CUtensorMap* map, const void* image, int n_groups
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return KV_ERR_CUDA;
+  }
+  return KV_OK;
+}
+// X [T][ldx] fp32 as a 2-D tensor, box {16 features, 64 rows} with the 64-byte swizzle (the consumer threads read one
+// row each: unswizzled, 32 lanes would hit two banks)
+static int encode_x_map(CUtensorMap* map, const float* X, int ldx, int T) {
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  KV_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres), "cuTensorMapEncodeTiled lookup");
+  if (qres != cudaDriverEntryPointSuccess || sym == nullptr) return KV_ERR_CUDA;
+  const EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(sym);
+  const cuuint64_t dims[2] = {(cuuint64_t)ldx, (cuuint64_t)T};
+  const cuuint64_t strides[1] = {(cuuint64_t)ldx * 4};
+  const cuuint32_t box[2] = {16, 64};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(X), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled (X) failed (%d)", (int)r);
     return KV_ERR_CUDA;
   }
   return KV_OK;
@@ -2197,6 +2259,12 @@ int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, 
     int rc = encode_dy_image_map(&p.tm_dy1, dy_image, d.n_groups, p.b.T8, p.b.O8, n1 / 16, 8);
     if (rc == KV_OK) rc = encode_dy_image_map(&p.tm_dy2, dy_image, d.n_groups, p.b.T8, p.b.O8, n2 ? n2 / 16 : 1, 8);
     if (rc != KV_OK) return rc;
+  }
+  p.use_tma_x = 0;
+  if (!tc_bwd_generic(d) && d.family == KV_EFFKAN && (d.ldx % 4) == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0) {
+    const int rc = encode_x_map(&p.tm_x, X, d.ldx, d.T);
+    if (rc != KV_OK) return rc;
+    p.use_tma_x = 1;
   }
   // K' tiles of 128 basis columns: effkan = one per 16-feature chunk (8 splines each) + one per 128 features
   // (SiLU column); Linear = one per 128 features
