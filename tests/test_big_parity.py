@@ -27,6 +27,10 @@ output, the input gradient and every parameter gradient:
              per-stage error while the tensor as a whole does not.  Measured on B200 (max-norm, for the record):
              block 2.6e-2; 2-block config-4 ViT y 3.0e-2, gx 8.2e-2, worst per-head gradient 1.6e-1 (the
              mma.sync route of round 1: 2.5e-2 / 6.6e-2 / 1.3e-1); 6-block config-3 ViTs 4.1e-2.
+             Calibration: the same oracle run under torch's CPU bf16 autocast (what the reference's own modules do
+             with bf16 arithmetic) is further from fp32 than this library on these cases (2-block config-4 ViT:
+             y 4.6e-2, gx 1.1e-1, worst per-head gradient 1.8e-1; the SineKAN ViT's `freq` gradients 3.3e-1), so
+             where that error exceeds the sqrt(S) bound a tensor is held to 1.25x the reference's own bf16 error.
 """
 import numpy as np
 import pytest
@@ -226,6 +230,15 @@ def _errors(y, gx, grads, ry, rgx, rgrads, fro=False):
     return out
 
 
+def _ref_bf16_errors(fwd, x, sd, dy, y32, gx32, g32):
+    """Per-tensor distance of the oracle under CPU bf16 autocast from its fp32 run (Frobenius for gradients)."""
+    def fwd16(xx, s2):
+        with torch.autocast("cpu", dtype=torch.bfloat16):
+            return fwd(xx, s2).float()
+    y16, gx16, g16 = _oracle_run(fwd16, x, sd, dy, torch.float32)
+    return _errors(y16, gx16, g16, y32, gx32, g32, fro=True)
+
+
 def _freq_factor(key):
     """SineKAN's `freq` gradient (models/sinekan.py:66-67: one 4-vector shared by every input and output of a layer) is
     a sum over all rows and features of terms of both signs that nearly cancel (test_gpu_parity.py): its bf16 error
@@ -233,13 +246,14 @@ def _freq_factor(key):
     return 2.5 if key.endswith(".freq") else 1.0
 
 
-def _check_against(tag, errs, tol_y, tol_g, report, slack=None):
+def _check_against(tag, errs, tol_y, tol_g, report, slack=None, ref16=None):
     slack = slack or {}
+    ref16 = ref16 or {}
     report[tag] = max(errs.values())
 
     def tol(k):
         base = tol_y if k == "y" else tol_g * (_freq_factor(k) if tag == "bf16" else 1.0)
-        return max(base, 3.0 * slack.get(k, 0.0))
+        return max(base, 3.0 * slack.get(k, 0.0), 1.25 * ref16.get(k, 0.0))
     bad = {k: (v, tol(k)) for k, v in errs.items() if v >= tol(k)}
     assert not bad, (tag, bad)
 
@@ -257,6 +271,11 @@ def test_cuda_matches_reference_fixture(name):
     dy = _dy_for(name, shape, seed)
     gmax = max(fx.absmax(k) for k in fx.keys() if k.startswith("g/"))
     tol_bf16_g = TOL_BF16 * _bf16_stages(name) ** 0.5
+    ref16 = {}
+    if _bf16_stages(name) > 1:
+        sd = _golden_state(m, seed)
+        y32, gx32, g32 = _oracle_run(fwd, x, sd, dy, torch.float32)
+        ref16 = _ref_bf16_errors(fwd, x, sd, dy, y32, gx32, g32)
     for mode, tol_y, tol_g in (("fp32", TOL_FP32, TOL_FP32_GRAD), ("bf16", tol_bf16_g, tol_bf16_g)):
         y, gx, grads = _gpu_run(m, x, dy, mode)
         got = {"y": y, "gx": gx, **{"g/" + k: v for k, v in grads.items()}}
@@ -266,6 +285,8 @@ def test_cuda_matches_reference_fixture(name):
             if fx.absmax(key) <= 1e-4 * gmax:     # ~0 gradient: judge against the model's largest gradient
                 e = e * fx.absmax(key) / gmax if not fro else 0.0
             tol = fx.tol(key, tol_y if key == "y" else tol_g * (_freq_factor(key) if mode == "bf16" else 1.0))
+            if mode == "bf16":
+                tol = max(tol, 1.25 * ref16.get(key, 0.0))
             assert e < tol, (mode, key, e, tol)
 
 
@@ -312,6 +333,7 @@ def test_cuda_matches_oracle_at_baseline_geometry(name):
     _check_against("fp32", _errors(y, gx, grads, y64, gx64, g64), TOL_FP32, TOL_FP32_GRAD, report, own32)
     # bf16 tensor-core kernels against the fp32 oracle (inputs and weights are bf16-representable by construction)
     y, gx, grads = _gpu_run(m, x, dy, "bf16")
+    ref16 = _ref_bf16_errors(fwd, x, sd, dy, y32, gx32, g32) if _bf16_stages(name) > 1 else None
     _check_against("bf16", _errors(y, gx, grads, y32, gx32, g32, fro=_relu_mlp(name)),
-                   TOL_BF16 * _bf16_stages(name) ** 0.5, TOL_BF16 * _bf16_stages(name) ** 0.5, report)
+                   TOL_BF16 * _bf16_stages(name) ** 0.5, TOL_BF16 * _bf16_stages(name) ** 0.5, report, ref16=ref16)
     print(name, {k: f"{v:.2e}" for k, v in report.items()})
