@@ -59,23 +59,37 @@ struct Geom {
   int npart;     // parts per chunk: the bases of a chunk are produced / consumed in npart slices of <= Mp bases,
   int Mp;        //   so that the ring always holds >= 2 slots (M > 13) and layers with M > 27 fit at all
   int effkan8;   // host-side candidate for LAYOUT_EFFKAN8 (the device-side grid probe decides)
+  int loopC;     // the K walk of the forward kernels: loopC chunk groups of loopM units, cut into npart parts of Mp.
+  int loopM;     //   KAN families: (n_chunks, M).  nn.Linear (M = 1): ONE group of n_chunks units in parts of 6
+                 //   consecutive 16-feature chunks, so a ring slot / barrier round trip carries 6 MMAs instead of 1
   __host__ __device__ size_t tile_elems() const { return (size_t)n_units * BN * KU; }
 };
 
-__host__ __device__ inline Geom make_geom(const kv_kan_desc_t& d) {
+// max_bn: 512 for the one-tile-per-CTA-pair kernels (forward KV_FWD_BN=512, weight gradient), 256 for the
+// persistent forward kernel (two accumulators in TMEM)
+__host__ __device__ inline Geom make_geom(const kv_kan_desc_t& d, int max_bn = 512) {
   Geom g;
   g.n_chunks = (d.in_features + KU - 1) / KU;
   g.n_units = g.n_chunks * d.M;
   const int out16 = (d.out_features + 15) / 16 * 16;
-  g.n_tiles = (out16 + 511) / 512;
+  g.n_tiles = (out16 + max_bn - 1) / max_bn;
   g.BN = ((out16 + g.n_tiles - 1) / g.n_tiles + 15) / 16 * 16;
   const int half_unit = g.BN * KU;  // bytes; each CTA of the pair stages half of a unit: BN/2 rows
-  g.npart = (d.M + 8) / 9;   // parts of <= 9 bases: at least two ring slots
-  g.Mp = (d.M + g.npart - 1) / g.npart;
+  if (d.family == KV_LINEAR && d.M == 1) {
+    g.loopC = 1;
+    g.loopM = g.n_chunks;
+    g.Mp = g.n_chunks < 6 ? g.n_chunks : 6;
+    g.npart = (g.n_chunks + g.Mp - 1) / g.Mp;
+  } else {
+    g.loopC = g.n_chunks;
+    g.loopM = d.M;
+    g.npart = (d.M + 8) / 9;   // parts of <= 9 bases: at least two ring slots
+    g.Mp = (d.M + g.npart - 1) / g.npart;
+  }
   g.S = 24576 / half_unit;
   g.S = g.S < 1 ? 1 : (g.S > 8 ? 8 : g.S);
   // parts of equal size that split into whole stages of 3 units: the MMA thread's unrolled issue loop applies
-  if (d.M % g.Mp == 0 && g.Mp % 3 == 0 && g.S >= 3) g.S = 3;
+  if (g.loopM % g.Mp == 0 && g.Mp % 3 == 0 && g.S >= 3) g.S = 3;
   int nb = B_RING_BYTES / (g.S * half_unit);
   g.NB = nb > NB_MAX ? NB_MAX : nb;
   g.NCH = A_UNITS / g.Mp;
@@ -497,6 +511,58 @@ __device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const f
 }
 
 // NPW = producer / epilogue warps: 8 (a thread owns 8 features of a chunk) or 16 (4 features; effkan only)
+// nn.Linear A producer of one tile (both forward kernels; 256 producer threads: row r, k-half wg): the operand is the
+// bf16 image of X itself.  A ring slot carries Mp consecutive 16-feature chunks (one 16-byte store per chunk and
+// thread); the loads of the next slot are in flight while the current one is converted.  mrow != nullptr: the ReLU
+// gate of a transposed layer (input gradient of Linear + ReLU), applied while converting.
+__device__ __forceinline__ void linear_produce_tile(const Geom& gm, const float* __restrict__ xrow, const float* __restrict__ mrow,
+                                                    bool row_ok, bool vec, bool mvec, int in, int wg, uint8_t* sA_row,
+                                                    uint32_t bar0, int NCH, int lane, int& slot_i) {
+  constexpr int LC = 6;   // >= Geom::Mp of a Linear layer
+  const int Mp = gm.Mp, n_chunks = gm.n_chunks;
+  float cur[LC][8];
+  auto load_part = [&](int c0, float (&v)[LC][8]) {
+#pragma unroll
+    for (int u = 0; u < LC; ++u) {
+      if (u < Mp && c0 + u < n_chunks) {
+        load_x8(xrow, (c0 + u) * KU + wg * 8, in, row_ok, vec, v[u]);
+        if (mrow != nullptr) {
+          float mk[8];
+          load_x8(mrow, (c0 + u) * KU + wg * 8, in, row_ok, mvec, mk);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) v[u][q] = mk[q] > 0.0f ? v[u][q] : 0.0f;
+        }
+      } else {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[u][q] = 0.0f;
+      }
+    }
+  };
+  load_part(0, cur);
+  for (int pt = 0; pt < gm.npart; ++pt, ++slot_i) {
+    float nxt[LC][8];
+    load_part((pt + 1) * Mp, nxt);    // beyond the last part: zeros, no loads
+    const int sc = slot_i % NCH;
+    const int Mt = min(Mp, n_chunks - pt * Mp);
+    ptx::mbar_wait(bar0 + 8u * (NCH_MAX + sc), ((slot_i / NCH) & 1) ^ 1);   // emptyA(sc)
+    uint8_t* base = sA_row + sc * Mp * A_UNIT_BYTES + wg * 2048;
+#pragma unroll
+    for (int u = 0; u < LC; ++u) {
+      if (u < Mt)
+        *reinterpret_cast<uint4*>(base + u * A_UNIT_BYTES) =
+            make_uint4(pack_bf16(cur[u][0], cur[u][1]), pack_bf16(cur[u][2], cur[u][3]), pack_bf16(cur[u][4], cur[u][5]),
+                       pack_bf16(cur[u][6], cur[u][7]));
+    }
+    ptx::fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(bar0 + 8u * sc, 0));  // the leader's fullA(sc)
+#pragma unroll
+    for (int u = 0; u < LC; ++u)
+#pragma unroll
+      for (int q = 0; q < 8; ++q) cur[u][q] = nxt[u][q];
+  }
+}
+
 template <int F, int NPW>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) kan_tc_fwd_kernel(const FwdParams p) {
   constexpr int NTH = 32 * (2 + NPW);
@@ -554,6 +620,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
     if (dbg && u < 64) dbuf[(role * 64 + u) * 4 + k] = (uint32_t)clock64();
   };
 
+  if (threadIdx.x == 64) stamp(2, 61, 1);
   const int S = gm.S;
   const int n_stages = (n_units + S - 1) / S;
   if (warp == 0) {
@@ -600,13 +667,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       const uint64_t db2_0 = ptx::make_smem_desc(ptx::smem_u32(sB) + n1 * 16, (uint32_t)n2 * 8, sbo);
       const uint32_t a_slot_step = (uint32_t)(gm.Mp * A_UNIT_BYTES) >> 4, b_unit_step = b_unit_bytes >> 4;
       const int Mp = gm.Mp;
-      const bool fast = !(d.reserved & 2048) && S == 3 && (M % Mp) == 0 && (Mp % 3) == 0 && !(d.reserved & 4);
+      const int LM = gm.loopM;   // units per chunk group (M; nn.Linear: all chunks of the layer)
+      const bool fast = !(d.reserved & 2048) && S == 3 && (LM % Mp) == 0 && (Mp % 3) == 0 && !(d.reserved & 4);
       if (fast) {
         const uint32_t a_hi = (uint32_t)(da0 >> 32), b1_hi = (uint32_t)(db1_0 >> 32), b2_hi = (uint32_t)(db2_0 >> 32);
         const uint32_t a_lo0 = (uint32_t)da0, b1_lo0 = (uint32_t)db1_0, b2_lo0 = (uint32_t)db2_0;
         const uint32_t a_unit = A_UNIT_BYTES >> 4, stage_step = 3u * b_unit_step;
         const int stages_per_part = Mp / 3;
-        const int n_parts_total = gm.n_chunks * (M / Mp);
+        const int n_parts_total = gm.loopC * (LM / Mp);
         int sc = 0, sb = 0;
         uint32_t phA = 0, phB = 0, acc = 0;
         int gst = 0;
@@ -642,9 +710,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         int sc = 0, sb = 0, ub = 0, u = 0;
         uint32_t phA = 0, phB = 0;
         uint64_t db1 = db1_0, db2 = db2_0;   // B descriptors of the current unit
-        for (int ch = 0; ch < gm.n_chunks; ++ch) {
-          for (int m0 = 0; m0 < M; m0 += Mp) {     // one ring slot per part of the chunk
-            const int m1 = min(M, m0 + Mp);
+        for (int ch = 0; ch < gm.loopC; ++ch) {
+          for (int m0 = 0; m0 < LM; m0 += Mp) {     // one ring slot per part of the chunk
+            const int m1 = min(LM, m0 + Mp);
             if (dbg) stamp(0, u, 2);
             ptx::mbar_wait(fullA(sc), phA);
             ptx::tc_fence_after();
@@ -746,6 +814,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         for (int q = 0; q < FPT; ++q) v[q] = mk[q] > 0.0f ? v[q] : 0.0f;
       }
     };
+    if (ptid == 0) stamp(2, 62, 0);
+    if constexpr (F == KV_LINEAR) {
+      static_assert(F != KV_LINEAR || FPT == 8, "the Linear producers own 8 features per thread");
+      int slot_i = 0;
+      linear_produce_tile(gm, xrow, mrow, row_ok, vec, mvec, in, wg, sA + row_off, bar0, NCH, lane, slot_i);
+    } else {
     float cur[FPT];
     load_xf(xrow, vec, wg * FPT, cur);
     gate(wg * FPT, cur);
@@ -798,9 +872,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
 #pragma unroll
       for (int q = 0; q < FPT; ++q) cur[q] = nxt[q];
     }
+    }
     // ================= epilogue: TMEM -> registers -> smem transpose -> coalesced global stores =========
+    if (ptid == 0) stamp(2, 62, 1);
     ptx::mbar_wait(tmem_full, 0);
     ptx::tc_fence_after();
+    if (ptid == 0) stamp(2, 62, 2);
     const int pw = warp - 2;
     const int q4 = warp & 3;            // TMEM lane quadrant this warp may read
     const int half = pw >> 2;           // NPW / 4 warps per quadrant split the column blocks
@@ -922,9 +999,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       __syncwarp();
     }
     ptx::tc_fence_before();
+    if (ptid == 0) stamp(2, 62, 3);
   }
   ptx::cluster_sync_all();  // the peer's smem / TMEM stay alive until every MMA and epilogue is done
   if (dbg) {
+    if (threadIdx.x == 64) stamp(2, 61, 2);
+    __syncthreads();
     for (int i = threadIdx.x; i < 1024; i += NTH)
       reinterpret_cast<uint32_t*>(p.Y)[(size_t)(rank * 128 + i / 512) * d.ldy + (i % 512)] = dbuf[i];
   }
@@ -934,11 +1014,480 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
   }
 }
 
+
+// =========================================================================================
+// Persistent forward kernel (BN <= 256): one CTA pair per SM pair walks the (group, row block, output tile) list.
+//   * the accumulator is double-buffered in TMEM (2 x 256 columns): four dedicated epilogue warps drain tile i while
+//     the tensor pipe works on tile i + 1, so the epilogue (TMEM -> registers -> coalesced stores, the HBM write
+//     burst of every CTA at once) and the per-tile set-up (TMEM allocation, barrier init, cluster sync, first
+//     operand fetch: ~6000 cycles) no longer sit between two main loops -- in the one-tile-per-CTA kernel they took
+//     ~30 % of a 768 -> 3072 tile and most of a 64 -> 192 (q/k/v) tile;
+//   * the operand rings simply keep running across tiles (loader and producers run ahead into the next tile).
+// Warps: 0 loader, 1 MMA issuer (leader) / B relay (peer), 2-9 basis producers, 10-13 epilogue.
+// =========================================================================================
+constexpr int P_NPW = 8;                       // producer warps
+constexpr int P_NEW = 4;                       // epilogue warps (one per TMEM lane quadrant)
+constexpr int P_THREADS = 32 * (2 + P_NPW + P_NEW);
+constexpr int P_B_RING = 96 * 1024;
+constexpr int P_STG_BYTES = P_NEW * 32 * 36 * 4;   // epilogue staging: 32 rows x 36 floats per warp
+constexpr int P_SMEM = A_RING_BYTES + P_B_RING + P_STG_BYTES + BAR_BYTES;
+
+template <int F>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc_fwd_persistent_kernel(const FwdParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + A_RING_BYTES;
+  float* sStg = reinterpret_cast<float*>(smem + A_RING_BYTES + P_B_RING);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A_RING_BYTES + P_B_RING + P_STG_BYTES);
+  const uint32_t bar0 = ptx::smem_u32(bars);
+  auto fullA = [&](int s) { return bar0 + 8u * s; };
+  auto emptyA = [&](int s) { return bar0 + 8u * (NCH_MAX + s); };
+  auto fullB = [&](int s) { return bar0 + 8u * (2 * NCH_MAX + s); };
+  auto emptyB = [&](int s) { return bar0 + 8u * (2 * NCH_MAX + NB_MAX + s); };
+  auto tmemFull = [&](int b) { return bar0 + 8u * (2 * NCH_MAX + 2 * NB_MAX + b); };
+  auto tmemEmpty = [&](int b) { return bar0 + 8u * (2 * NCH_MAX + 2 * NB_MAX + 2 + b); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NCH_MAX + 2 * NB_MAX + 4);
+
+  const kv_kan_desc_t& d = p.d;
+  const Geom gm = p.gm;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();  // 0 = leader of the CTA pair
+  const int M = d.M, Mp = gm.Mp;
+  const int n_units = gm.n_units;
+  const int BN = gm.BN, NCH = gm.NCH, S = gm.S;
+  const uint32_t b_unit_bytes = (uint32_t)BN * KU;  // this CTA's half of the B unit: BN/2 rows x 16 x 2 B
+  int NB = P_B_RING / (S * (int)b_unit_bytes);
+  NB = NB > NB_MAX ? NB_MAX : NB;
+  const int n_stages = (n_units + S - 1) / S;
+  // tile list: output tiles of one row block adjacent (their X tile is shared through L2 at the same time)
+  const int n_pairs = ceil_div(d.T, 2 * BM);
+  const int total_tiles = d.n_groups * n_pairs * gm.n_tiles;
+  const int n_my = (total_tiles - (int)blockIdx.y + (int)gridDim.y - 1) / (int)gridDim.y;
+  auto tile_of = [&](int it, int& g, int& mp, int& n_tile) {
+    const int tile = (int)blockIdx.y + it * (int)gridDim.y;
+    n_tile = tile % gm.n_tiles;
+    const int r = tile / gm.n_tiles;
+    mp = r % n_pairs;
+    g = r / n_pairs;
+  };
+
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < NCH_MAX; ++s) {
+      ptx::mbar_init(fullA(s), 2 * P_NPW);  // (leader) local + peer producer warps
+      ptx::mbar_init(emptyA(s), 1);
+    }
+    for (int s = 0; s < NB_MAX; ++s) {
+      ptx::mbar_init(fullB(s), rank == 0 ? 2 : 1);  // leader: own bulk copy + the peer's "my half landed"
+      ptx::mbar_init(emptyB(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(tmemFull(b), 1);
+      ptx::mbar_init(tmemEmpty(b), 2 * P_NEW);   // (leader) the epilogue warps of both CTAs
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) {
+    ptx::tmem_alloc2(ptx::smem_u32(tmem_slot), TMEM_COLS);
+    ptx::tmem_relinquish2();
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync_all();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= B loader: this CTA's half of S units per bulk copy, tile after tile =================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 1;  // a fresh barrier passes a wait on parity 1
+      for (int it = 0; it < n_my; ++it) {
+        int g, mp, n_tile;
+        tile_of(it, g, mp, n_tile);
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(p.wt) +
+                             (((size_t)g * gm.n_tiles + n_tile) * 2 + rank) * (size_t)n_units * b_unit_bytes;
+        for (int st = 0; st < n_stages; ++st) {
+          const int nu = min(S, n_units - st * S);
+          ptx::mbar_wait(emptyB(s), ph);
+          ptx::mbar_arrive_expect_tx(fullB(s), nu * b_unit_bytes);
+          ptx::bulk_g2s(ptx::smem_u32(sB) + s * S * b_unit_bytes, src + (size_t)st * S * b_unit_bytes,
+                        nu * b_unit_bytes, fullB(s));
+          if (++s == NB) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (rank == 0) {
+      // ================= MMA issuer (leader CTA): the whole converged warp, election inside the asm blocks ==========
+      const uint32_t idesc = ptx::make_idesc_bf16(2 * BM, BN);
+      const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(sA), (BM / 8) * 128, 128);
+      const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(sB), (uint32_t)BN * 8, 128);
+      const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32);
+      const uint32_t a_lo0 = (uint32_t)da0, b_lo0 = (uint32_t)db0;
+      const uint32_t a_unit = A_UNIT_BYTES >> 4, b_unit_step = b_unit_bytes >> 4;
+      const uint32_t a_slot_step = (uint32_t)(Mp * A_UNIT_BYTES) >> 4;
+      const int LM = gm.loopM;   // units per chunk group (M; nn.Linear: all chunks of the layer)
+      const bool fast = S == 3 && (LM % Mp) == 0 && (Mp % 3) == 0;
+      const int n_parts_total = gm.loopC * gm.npart;
+      int sc = 0, sb = 0;
+      uint32_t phA = 0, phB = 0;
+      for (int it = 0; it < n_my; ++it) {
+        const int buf = it & 1;
+        // the epilogue warps of both CTAs have drained this accumulator (its use two tiles ago)
+        ptx::mbar_wait_cluster(tmemEmpty(buf), (uint32_t)((it >> 1) & 1) ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t tacc = tmem_base + buf * 256;
+        uint32_t acc = 0;
+        if (fast) {
+          const int stages_per_part = Mp / 3;
+          for (int part = 0; part < n_parts_total; ++part) {
+            ptx::mbar_wait(fullA(sc), phA);
+            ptx::tc_fence_after();
+            uint32_t a_lo = a_lo0 + (uint32_t)sc * a_slot_step;
+            for (int st = 0; st < stages_per_part; ++st) {
+              ptx::mbar_wait(fullB(sb), phB);
+              ptx::tc_fence_after();
+              const uint32_t b_lo = b_lo0 + (uint32_t)sb * 3u * b_unit_step;
+#pragma unroll
+              for (int k = 0; k < 3; ++k) {
+                ptx::mma2_bf16_ss_lohi_elect(tacc, a_lo + k * a_unit, a_hi, b_lo + k * b_unit_step, b_hi, idesc, acc);
+                acc = 1;
+              }
+              ptx::tc_commit2_elect(emptyB(sb));
+              if (++sb == NB) { sb = 0; phB ^= 1; }
+              a_lo += 3 * a_unit;
+            }
+            ptx::tc_commit2_elect(emptyA(sc));
+            if (++sc == NCH) { sc = 0; phA ^= 1; }
+          }
+        } else {
+          int ub = 0, u = 0;
+          for (int ch = 0; ch < gm.loopC; ++ch) {
+            for (int m0 = 0; m0 < LM; m0 += Mp) {
+              const int m1 = min(LM, m0 + Mp);
+              ptx::mbar_wait(fullA(sc), phA);
+              ptx::tc_fence_after();
+              uint32_t a_lo = a_lo0 + (uint32_t)sc * a_slot_step;
+              for (int q = m0; q < m1; ++q, ++u) {
+                if (ub == 0) {
+                  ptx::mbar_wait(fullB(sb), phB);
+                  ptx::tc_fence_after();
+                }
+                ptx::mma2_bf16_ss_lohi_elect(tacc, a_lo, a_hi, b_lo0 + (uint32_t)(sb * S + ub) * b_unit_step, b_hi, idesc, acc);
+                acc = 1;
+                a_lo += a_unit;
+                if (ub + 1 == S || u + 1 == n_units) {
+                  ptx::tc_commit2_elect(emptyB(sb));
+                  ub = 0;
+                  if (++sb == NB) { sb = 0; phB ^= 1; }
+                } else {
+                  ++ub;
+                }
+              }
+              ptx::tc_commit2_elect(emptyA(sc));
+              if (++sc == NCH) { sc = 0; phA ^= 1; }
+            }
+          }
+        }
+        ptx::tc_commit2_elect(tmemFull(buf));
+      }
+    } else if (lane == 0) {
+      // ================= peer CTA: tell the leader when our half of each B stage has landed ===========
+      int s = 0;
+      uint32_t ph = 0;
+      for (int st = 0; st < n_stages * n_my; ++st) {
+        ptx::mbar_wait(fullB(s), ph);
+        ptx::mbar_arrive_cluster(ptx::mapa(fullB(s), 0));
+        if (++s == NB) { s = 0; ph ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp < 2 + P_NPW) {
+    // ================= A producers: basis prologue, tile after tile =================
+    const int ptid = threadIdx.x - 64;
+    const int r = ptid & (BM - 1), wg = ptid >> 7;  // row of the 128-row tile, k-half (8 features) of the chunk
+    const int n_slices = d.n_groups / d.x_share;
+    const int in = d.in_features;
+    const int row_off = (r >> 3) * 128 + (r & 7) * 16;
+    int slot_i = 0;   // running ring-slot counter (parts produced so far, all tiles)
+    for (int it = 0; it < n_my; ++it) {
+      int g, mp, n_tile;
+      tile_of(it, g, mp, n_tile);
+      const int t0 = (mp * 2 + (int)rank) * BM;
+      const int slice = g / d.x_share;
+      const int xoff = slice * in;
+      const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0);
+      const bool mvec = vec && ((reinterpret_cast<uintptr_t>(p.in_mask) & 15) == 0);
+      const int t = t0 + r;
+      const bool row_ok = t < d.T;
+      const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
+      const BasisCtx c = make_ctx(d, p.fparams, g);
+      const int layout = group_layout(d, gm, p.fparams, g);
+      float gt0 = 0.f, ginv_h = 0.f;
+      if (layout == LAYOUT_EFFKAN8) {
+        const float* probe = c.fp + (size_t)in * (d.grid_size + 2 * d.spline_order + 1);
+        gt0 = probe[1];
+        ginv_h = probe[2];
+      }
+      float mu = 0.f, rs = 1.f;
+      if (F == KV_FASTKAN && !(d.flags & KV_FLAG_NO_LAYERNORM) && row_ok) {
+        mu = p.mean[(size_t)t * n_slices + slice];
+        rs = p.rstd[(size_t)t * n_slices + slice];
+      }
+      // Linear as the input gradient of a ReLU layer: dY is gated by the layer's own forward output
+      const float* mrow = (F == KV_LINEAR && p.in_mask != nullptr)
+                              ? p.in_mask + (size_t)(row_ok ? t : 0) * d.ldx + xoff : nullptr;
+      auto gate = [&](int i0g, float (&v)[8]) {
+        if (F == KV_LINEAR && mrow != nullptr) {
+          float mk[8];
+          load_x8(mrow, i0g, in, row_ok, mvec, mk);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) v[q] = mk[q] > 0.0f ? v[q] : 0.0f;
+        }
+      };
+      if constexpr (F == KV_LINEAR) {
+        linear_produce_tile(gm, xrow, mrow, row_ok, vec, mvec, in, wg, sA + row_off, bar0, NCH, lane, slot_i);
+        continue;
+      }
+      float cur[8];
+      load_x8(xrow, wg * 8, in, row_ok, vec, cur);
+      gate(wg * 8, cur);
+      for (int ch = 0; ch < gm.n_chunks; ++ch) {
+        float nxt[8];
+        if (ch + 1 < gm.n_chunks) {
+          load_x8(xrow, (ch + 1) * KU + wg * 8, in, row_ok, vec, nxt);
+          gate((ch + 1) * KU + wg * 8, nxt);
+        } else {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) nxt[q] = 0.0f;
+        }
+        const int i0 = ch * KU + wg * 8;
+        for (int pt = 0; pt < gm.npart; ++pt, ++slot_i) {   // one ring slot per part: bases [m0, m0 + Mt) of the chunk
+          const int sc = slot_i % NCH;
+          const int m0 = pt * Mp, Mt = min(Mp, M - m0);
+          ptx::mbar_wait(emptyA(sc), ((slot_i / NCH) & 1) ^ 1);
+          uint8_t* base = sA + sc * Mp * A_UNIT_BYTES + row_off;
+          if constexpr (F == KV_EFFKAN) {
+            if (layout == LAYOUT_EFFKAN8) {            // M = 9: one part
+              effkan8_chunk(base, wg, cur, gt0, ginv_h);
+            } else {
+              // arbitrary knots: Cox-de Boor per feature, scattered 2-byte stores
+#pragma unroll 1
+              for (int q = 0; q < 8; ++q) {
+                StrideSink sink{base + wg * 2048 + q * 2, A_UNIT_BYTES, m0, Mt};
+                if (i0 + q < in) {
+                  basis_eval<F>(c, i0 + q, cur[q], cur[q], sink);
+                } else {
+                  for (int m = m0; m < m0 + Mt; ++m) sink.put(m, 0.0f);
+                }
+              }
+            }
+          } else {
+            basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, m0, Mt, cur, c, i0, mu, rs);
+          }
+          ptx::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(sc), 0));  // the leader's barrier
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) cur[q] = nxt[q];
+      }
+    }
+  } else {
+    // ================= epilogue warps: TMEM -> registers -> smem transpose -> coalesced global stores =========
+    const int q4 = warp & 3;                 // TMEM lane quadrant this warp may read
+    const int ew = warp - (2 + P_NPW);
+    constexpr int LDT = 36;                  // staging row stride in floats (conflict-free float4 access)
+    float* stg = sStg + ew * (32 * LDT);
+    const int out = d.out_features;
+    const int ncols_total = d.n_groups * out;
+    const int c4 = (lane & 7) * 4, rsub = lane >> 3;
+    for (int it = 0; it < n_my; ++it) {
+      int g, mp, n_tile;
+      tile_of(it, g, mp, n_tile);
+      const int buf = it & 1;
+      const int t0 = (mp * 2 + (int)rank) * BM;
+      ptx::mbar_wait(tmemFull(buf), (uint32_t)((it >> 1) & 1));
+      ptx::tc_fence_after();
+      const uint32_t trow = tmem_base + ((uint32_t)(q4 * 32) << 16) + buf * 256;
+      if (p.attn_img != nullptr) {
+        // ---- attention-image epilogue: thread = token row (TMEM lane), 16-byte chunks of 8 consecutive d
+        const int te = t0 + q4 * 32 + lane;
+        const bool ok = te < d.T;
+        const int Ntok = p.attn_N, dh = out / 3;
+        const int NPAD = (Ntok + 15) / 16 * 16, DHP = (dh + 15) / 16 * 16;
+        const int bs = ok ? te / Ntok : 0, n = ok ? te - bs * Ntok : 0;
+        const size_t part_elems = (size_t)NPAD * DHP;
+        __nv_bfloat16* hb = p.attn_img + ((size_t)bs * d.n_groups + g) * 3 * part_elems;
+        auto chunk_at = [&](int part, int nn, int dd) {
+          return reinterpret_cast<uint4*>(hb + part * part_elems + ((size_t)(nn >> 3) * (DHP >> 3) + (dd >> 3)) * 64 + (nn & 7) * 8);
+        };
+        const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+        for (int cb = 0; cb * 32 < BN; ++cb) {
+          uint32_t rr[32];
+          ptx::tmem_ld32(trow + cb * 32, rr);
+          ptx::tmem_ld_wait();
+          if (!ok) continue;
+#pragma unroll
+          for (int k8 = 0; k8 < 4; ++k8) {
+            const int o = n_tile * BN + cb * 32 + 8 * k8;   // first output of the chunk (out % 8 == 0, d_head % 8 == 0)
+            if (cb * 32 + 8 * k8 >= BN || o >= out) continue;
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(rr[8 * k8 + e]) + (p.bias ? p.bias[g * out + o + e] : 0.0f);
+            const int part = o / dh, dd = o - part * dh;
+            *chunk_at(part, n, dd) = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                                                pack_bf16(v[6], v[7]));
+            const bool last_d = (dd + 8 == dh);
+            if (last_d)
+              for (int dp = dh; dp < DHP; dp += 8) *chunk_at(part, n, dp) = zero4;          // d padding of this row
+            if (n == Ntok - 1) {                                                            // row padding of the sample
+              for (int nn = Ntok; nn < NPAD; ++nn) {
+                *chunk_at(part, nn, dd) = zero4;
+                if (last_d)
+                  for (int dp = dh; dp < DHP; dp += 8) *chunk_at(part, nn, dp) = zero4;
+              }
+            }
+          }
+        }
+      } else {
+        // the 8 rows this lane stores in the row-wise phase
+        long long yoff[8];
+        int posrow[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int te = t0 + q4 * 32 + k * 4 + rsub;
+          if (te < d.T) {
+            yoff[k] = (long long)map_row(te, d.rows_in, d.rows_out, d.row_shift) * d.ldy;
+            posrow[k] = d.rows_in ? (d.row_shift + te % d.rows_in) : te;
+          } else {
+            yoff[k] = -1;
+            posrow[k] = 0;
+          }
+        }
+        const int colbase = g * out + n_tile * BN;
+        const bool vec_y = ((d.ldy & 3) == 0) && ((colbase & 3) == 0) && ((ncols_total & 3) == 0) &&
+                           ((reinterpret_cast<uintptr_t>(p.Y) & 15) == 0) &&
+                           (!p.residual || (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0) &&
+                           (!p.pos || (reinterpret_cast<uintptr_t>(p.pos) & 15) == 0) &&
+                           (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
+        for (int cb = 0; cb * 32 < BN; ++cb) {
+          uint32_t rr[32];
+          ptx::tmem_ld32(trow + cb * 32, rr);
+          ptx::tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            *reinterpret_cast<uint4*>(stg + lane * LDT + 4 * k) = make_uint4(rr[4 * k], rr[4 * k + 1], rr[4 * k + 2], rr[4 * k + 3]);
+          __syncwarp();
+          const int cl = cb * 32 + c4;           // column inside the tile
+          const int o = n_tile * BN + cl;        // output feature of the group
+          const int col = colbase + cl;          // column of Y
+          float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+          const bool full4 = vec_y && (cl + 3 < BN) && (o + 3 < out);
+          if (p.bias && full4) bv = *reinterpret_cast<const float4*>(p.bias + col);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float4 a = *reinterpret_cast<const float4*>(stg + (k * 4 + rsub) * LDT + c4);
+            if (yoff[k] < 0) continue;
+            float v[4] = {a.x, a.y, a.z, a.w};
+            if (full4) {
+              v[0] += bv.x; v[1] += bv.y; v[2] += bv.z; v[3] += bv.w;
+              if (p.pos) {
+                const float4 pv = *reinterpret_cast<const float4*>(p.pos + (size_t)posrow[k] * ncols_total + col);
+                v[0] += pv.x; v[1] += pv.y; v[2] += pv.z; v[3] += pv.w;
+              }
+              if (d.flags & KV_FLAG_RELU) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) v[e] = fmaxf(v[e], 0.0f);
+              }
+              if (p.residual) {
+                const float4 rv = *reinterpret_cast<const float4*>(p.residual + yoff[k] + col);
+                v[0] += rv.x; v[1] += rv.y; v[2] += rv.z; v[3] += rv.w;
+              }
+              *reinterpret_cast<float4*>(p.Y + yoff[k] + col) = make_float4(v[0], v[1], v[2], v[3]);
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                if (cl + e < BN && o + e < out) {
+                  float w = v[e];
+                  if (p.bias) w += p.bias[col + e];
+                  if (p.pos) w += p.pos[(size_t)posrow[k] * ncols_total + col + e];
+                  if (d.flags & KV_FLAG_RELU) w = fmaxf(w, 0.0f);
+                  if (p.residual) w += p.residual[yoff[k] + col + e];
+                  p.Y[yoff[k] + col + e] = w;
+                }
+              }
+            }
+          }
+          __syncwarp();
+        }
+      }
+      // this warp has drained its lanes of the accumulator: the leader may overwrite it two tiles from now
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tmemEmpty(buf), 0));
+    }
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync_all();  // the peer's smem / TMEM stay alive until every MMA and epilogue is done
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc2(tmem_base, TMEM_COLS);
+  }
+}
+
+
+// Forward kernel choice.  Layers whose output tile fits 256 TMEM columns (q/k/v maps, heads, d <= 256 MLPs) run the
+// persistent kernel: same weight image, same tile, epilogue and set-up overlapped.  Wider layers keep the 256 x 512
+// tile of kan_tc_fwd_kernel: measured on 768 -> 3072 / 3072 -> 768 (T = 66192) the persistent kernel on 256-wide
+// tiles reaches 1127 / 1106 TFLOP/s against 1381 / 1246 -- halving BN doubles the basis work per FLOP and raises the
+// shared-memory traffic of the MMA operand reads from 64 to 96 B/cycle/SM -- while the 64 -> 192 q/k/v layer drops
+// from 0.911 to 0.574 ms.  Timing experiments: KV_FWD_BN=256 tiles every layer for the persistent kernel,
+// KV_FWD_PERSISTENT=0 turns it off.
+inline int fwd_max_bn() {
+  static const int v = [] {
+    const char* e = getenv("KV_FWD_BN");
+    return (e != nullptr && atoi(e) == 256) ? 256 : 512;
+  }();
+  return v;
+}
+inline bool fwd_persistent_enabled() {
+  static const bool v = [] {
+    const char* e = getenv("KV_FWD_PERSISTENT");
+    return !(e != nullptr && atoi(e) == 0);
+  }();
+  return v;
+}
+// nn.Linear (K = in: a 256 x 512 tile's main loop is shorter than its epilogue) is always tiled for the persistent kernel
+inline Geom fwd_geom(const kv_kan_desc_t& d) {
+  return make_geom(d, (d.family == KV_LINEAR && fwd_persistent_enabled()) ? 256 : fwd_max_bn());
+}
+
+template <int F>
+static int launch_fwd_persistent(const FwdParams& p, cudaStream_t st) {
+  KV_SMEM_OPT_IN((kan_tc_fwd_persistent_kernel<F>), P_SMEM, "tc_fwd persistent smem attribute");
+  const long long tiles = (long long)ceil_div(p.d.T, 2 * BM) * p.gm.n_tiles * p.d.n_groups;
+  if (tiles > 0x7fffffffLL) return KV_ERR_BAD_SHAPE;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  static int sm_count[64] = {0};
+  if (dev < 64) {
+    if (sm_count[dev] == 0) cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+    sms = sm_count[dev];
+  }
+  const int pairs = sms / 2;
+  dim3 grid(2, (unsigned)(tiles < pairs ? tiles : pairs), 1);  // x = CTA pair; each pair walks tiles y, y + gridDim.y, ...
+  kan_tc_fwd_persistent_kernel<F><<<grid, P_THREADS, P_SMEM, st>>>(p);
+  KV_CHECK_LAUNCH("kan_tc_fwd_persistent_kernel");
+  return KV_OK;
+}
+
 template <int F>
 static int launch_fwd(const FwdParams& p, cudaStream_t st) {
   // 16 producer warps (4 features per thread) were measured SLOWER than 8 on the MLP shapes (768->3072: 966 vs
   // 1012 TFLOP/s): the producers are not the pacing stage, and their stores compete with the MMA operand reads
   constexpr int NPW = 8;
+  if (p.gm.BN <= 256 && fwd_persistent_enabled() && !(p.d.reserved & 0xfff)) return launch_fwd_persistent<F>(p, st);
   KV_SMEM_OPT_IN((kan_tc_fwd_kernel<F, NPW>), SMEM_BYTES, "tc_fwd smem attribute");
   const int n_pairs = ceil_div(p.d.T, 2 * BM);
   if ((long long)n_pairs * p.gm.n_tiles > 65535 || p.d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
@@ -2022,7 +2571,7 @@ int tc_supported(const kv_kan_desc_t& d) {
 }
 
 size_t tc_wtiles_bytes(const kv_kan_desc_t& d) {
-  const tc::Geom gm = tc::make_geom(d);
+  const tc::Geom gm = tc::fwd_geom(d);
   return (size_t)d.n_groups * gm.n_tiles * gm.tile_elems() * 2;
 }
 
@@ -2080,7 +2629,7 @@ static int grid_for(size_t total, int threads) {
 
 int tc_pack(const kv_kan_desc_t& d, const kv_kan_desc_t& d0, const uint64_t* ptr_table, const float* fparams,
             void* wtiles, void* wtiles_t, cudaStream_t st) {
-  const tc::Geom gm = tc::make_geom(d);
+  const tc::Geom gm = tc::fwd_geom(d);
   if (wtiles != nullptr) {
     const size_t total = (size_t)d.n_groups * gm.n_tiles * gm.tile_elems() / 8;
     tc::tc_pack_kernel<<<grid_for(total, 256), 256, 0, st>>>(d, d0, ptr_table, fparams,
@@ -2090,7 +2639,7 @@ int tc_pack(const kv_kan_desc_t& d, const kv_kan_desc_t& d0, const uint64_t* ptr
   if (wtiles_t != nullptr && d.family == KV_LINEAR) {
     if (!tc_bwd_ok(d)) return KV_ERR_UNSUPPORTED;
     const kv_kan_desc_t dt = linear_transposed(d);
-    const tc::Geom gmt = tc::make_geom(dt);
+    const tc::Geom gmt = tc::fwd_geom(dt);
     const size_t total = (size_t)dt.n_groups * gmt.n_tiles * gmt.tile_elems() / 8;
     tc::tc_pack_linear_t_kernel<<<grid_for(total, 256), 256, 0, st>>>(dt, d, d0, ptr_table,
                                                                       reinterpret_cast<__nv_bfloat16*>(wtiles_t), gmt);
@@ -2136,7 +2685,7 @@ int tc_fwd(const kv_kan_desc_t& d, const float* X, const void* wtiles, const flo
   p.residual = residual;
   p.pos = pos;
   p.Y = Y;
-  p.gm = tc::make_geom(d);
+  p.gm = tc::fwd_geom(d);
   p.in_mask = nullptr;
   p.attn_img = reinterpret_cast<__nv_bfloat16*>(attn_image);
   p.attn_N = attn_tokens;
@@ -2171,7 +2720,7 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
     q.fparams = nullptr;
     q.bias = q.mean = q.rstd = q.residual = q.pos = nullptr;
     q.Y = dX;
-    q.gm = tc::make_geom(q.d);
+    q.gm = tc::fwd_geom(q.d);
     q.in_mask = (d.flags & KV_FLAG_RELU) ? act_mask : nullptr;
     q.attn_img = nullptr;
     q.attn_N = 0;
