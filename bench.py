@@ -419,10 +419,12 @@ def run_gpu_arm(args):
         achieved = work_call / (ms_call * 1e-3) / 1e9
         peak, unit, bound = peaks["hbm_gbs"], "GB/s", "hbm"
     traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(tpath):
-        with open(tpath) as f:
-            traffic = json.load(f).get(top_name)  # DRAM bytes of that launch, one ncu --set full capture
+    for tname in ("r02_traffic.json", "r01_traffic.json"):
+        tpath = os.path.join(ROOT, "profiles", tname)
+        if os.path.exists(tpath):
+            with open(tpath) as f:
+                traffic = json.load(f).get(top_name)  # DRAM bytes of that launch, one ncu --set full capture
+            break
     roofline = {"bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
                 "traffic": traffic, "kernel": top_name, "kernel_ms_per_call": ms_call,
                 "kernel_calls_per_step": calls, "kernel_share_of_step": ms_call * calls / kernel_ms,
@@ -469,6 +471,260 @@ def run_gpu_arm(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------
+# --config cfg5: the "KANLinear fused TFLOP/s vs peak" half of BASELINE.json's metric.
+# A step = forward + backward (input and coefficient gradients) of the two headline layers of configs[3]/[4]:
+# KANLinear 768 -> 3072 and 3072 -> 768 (efficient-kan, grid 5, order 3, M = 9) on T = 65 536 token rows, chained the
+# way the KAN MLP chains them, bf16 tensor-core arithmetic.  Algorithmic FLOPs 6 T in out M per layer.
+# ---------------------------------------------------------------------------------------------
+LAYER_T = 65536
+LAYER_SHAPES = ((768, 3072), (3072, 768))
+LAYER_M = 9
+LAYER_CPU_T = 4096
+LAYER_METRIC, LAYER_UNIT = "kan_linear_fwd_bwd_tflops", "TFLOP/s"
+
+
+def layer_flops(T):
+    return sum(6.0 * T * i * o * LAYER_M for i, o in LAYER_SHAPES)
+
+
+def layer_workload(T):
+    return (f"cfg5 headline layers: KANLinear 768->3072 -> KANLinear 3072->768 (efficient-kan grid 5 order 3), "
+            f"T={T} token rows, step = forward + backward (dX and dW) of both layers")
+
+
+def time_layer_cpu(T, steps, budget_s):
+    """The reference algorithm of the two layers (oracle port: b_splines + two F.linear per layer, autograd backward)
+    on the host cores.  TEST-INFRASTRUCTURE oracle used as the reported CPU baseline."""
+    from oracle import kan_oracle as O
+    g = torch.Generator().manual_seed(0)
+    ws = []
+    for i, o in LAYER_SHAPES:
+        ws.append(((torch.randn(o, i, generator=g) * i ** -0.5).requires_grad_(),
+                   (torch.randn(o, i, 8, generator=g) * 0.05).requires_grad_(),
+                   torch.ones(o, i).requires_grad_(), O.effkan_default_grid(i)))
+    x = torch.randn(T, LAYER_SHAPES[0][0], generator=g).requires_grad_()
+    dy = torch.randn(T, LAYER_SHAPES[-1][1], generator=g)
+
+    def step():
+        h = x
+        for bw, sw, sc, grid in ws:
+            h = O.effkan_forward(h, bw, sw, sc, grid, 3)
+        for t in [x] + [w for tup in ws for w in tup[:3]]:
+            t.grad = None
+        h.backward(dy)
+
+    step()
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        step()
+        ts.append(time.perf_counter() - t0)
+        if sum(ts) > budget_s:
+            break
+    mean = sum(ts) / len(ts)
+    return layer_flops(T) / mean / 1e12, mean * 1e3, len(ts)
+
+
+SWEEP_SHAPES = ((192, 192), (384, 384), (768, 768), (1536, 1536), (3072, 3072), (768, 3072), (3072, 768))
+
+
+def cpu_layer_sweep(args):
+    """CPU column of the config-5 sweep (--impl reference --config cfg5 --sweep-cpu): forward + backward of ONE layer of
+    each family (grid 5) on the host cores through the oracle port, T = 4096 rows (Fourier: 512, as the reference's
+    own [T, out, in, G] intermediate would demand; the port uses the contraction form).  One JSON line per point."""
+    from oracle import kan_oracle as O
+    cores = host_threads()
+    g = torch.Generator().manual_seed(0)
+    rn = lambda *sh: (torch.randn(*sh, generator=g) * 0.05).requires_grad_()
+    G = 5
+    for fam in ("effkan", "cheby", "fastkan", "sine", "fourier"):
+        for i, o in SWEEP_SHAPES:
+            T = 512 if fam == "fourier" else 4096
+            if fam == "effkan":
+                ws = [rn(o, i), rn(o, i, G + 3), rn(o, i)]
+                grid = O.effkan_default_grid(i, G, 3)
+                f = lambda x: O.effkan_forward(x, ws[0], ws[1], ws[2], grid, 3)
+                M = G + 4
+            elif fam == "cheby":
+                ws = [rn(i, o, G + 1)]
+                f = lambda x: O.cheby_forward(x, ws[0])
+                M = G + 1
+            elif fam == "fastkan":
+                ws = [torch.ones(i).requires_grad_(), torch.zeros(i).requires_grad_(), rn(o, i * G), rn(o, i), rn(o)]
+                rg = torch.linspace(-2.0, 2.0, G)
+                f = lambda x: O.fastkan_forward(x, ws[0], ws[1], rg, ws[2], ws[3], ws[4])
+                M = G + 1
+            elif fam == "sine":
+                ws = [rn(o, i, G), O.sinekan_default_freq(G).requires_grad_(), rn(1, o)]
+                ph = O.sinekan_phase(i, G)
+                f = lambda x: O.sinekan_forward(x, ws[0], ws[1], ph, ws[2])
+                M = G
+            else:
+                ws = [rn(2, o, i, G), rn(1, o)]
+                f = lambda x: O.fourier_forward(x, ws[0], ws[1])
+                M = 2 * G
+            x = torch.randn(T, i, generator=g).requires_grad_()
+            dy = torch.randn(T, o, generator=g)
+
+            def step():
+                for t in [x] + ws:
+                    t.grad = None
+                f(x).backward(dy)
+
+            step()
+            t0 = time.perf_counter()
+            step()
+            dt = time.perf_counter() - t0
+            print(json.dumps({"family": fam, "T": T, "in": i, "out": o, "grid": G, "M": M, "impl": "cpu port (oracle)",
+                              "cores": cores, "fwdbwd_ms": round(dt * 1e3, 2),
+                              "fwdbwd_tflops": round(6.0 * T * i * o * M / dt / 1e12, 4)}), file=_OUT, flush=True)
+
+
+def run_layer_reference_arm(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = host_threads()
+    val, ms, done = time_layer_cpu(LAYER_CPU_T, args.steps, CPU_TIME_BUDGET_S)
+    sample = (f"{done} steps at T={LAYER_CPU_T} rows (oracle/kan_oracle.py effkan_forward, torch CPU fp32, autograd; "
+              f"{ms:.0f} ms/step)")
+    line = {"metric": LAYER_METRIC, "value": val, "unit": LAYER_UNIT, "n_gpus": args.gpus, "steps": done, "warmup": 1,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "impl": "reference",
+            "config": {"workload": layer_workload(LAYER_T), "reference_sample": sample},
+            "cpu_baseline": {"value": val, "unit": LAYER_UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": LAYER_UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), file=_OUT, flush=True)
+
+
+def run_layer_arm(args):
+    import torch.distributed as dist
+    import kan_vit_b200 as K
+    from kan_vit_b200 import _lib as L
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the GPU arm has no CPU fallback; use --impl reference)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)   # replicas only: the barrier and the max over ranks
+    lib = L.load()
+    K.set_precision("bf16")
+    T = args.batch or LAYER_T
+    torch.manual_seed(0)
+    layers = [K.KANLinear(i, o).to(dev) for i, o in LAYER_SHAPES]
+    g = torch.Generator().manual_seed(1000 + rank)
+    n_host = 2
+    host_x = [torch.randn(T, LAYER_SHAPES[0][0], generator=g).pin_memory() for _ in range(n_host)]
+    host_dy = [torch.randn(T, LAYER_SHAPES[-1][1], generator=g).pin_memory() for _ in range(n_host)]
+    dev_x = [t.to(dev).requires_grad_() for t in host_x]
+    dev_dy = [t.to(dev) for t in host_dy]
+    params = [p for m in layers for p in m.parameters()]
+
+    def fwd_bwd(x, dy):
+        for p in params:
+            p.grad = None
+        x.grad = None
+        h = x
+        for m in layers:
+            h = m(h)
+        h.backward(dy)
+        return h
+
+    def resident_step(i):
+        fwd_bwd(dev_x[i % n_host], dev_dy[i % n_host])
+
+    stage_x = torch.empty_like(dev_x[0]).requires_grad_()
+    stage_dy = torch.empty_like(dev_dy[0])
+    host_y = torch.empty(T, LAYER_SHAPES[-1][1]).pin_memory()
+    host_dx = torch.empty(T, LAYER_SHAPES[0][0]).pin_memory()
+
+    def e2e_step(i):
+        # host rows in (x and dy from pinned memory), the layer output and the input gradient back out to the host
+        with torch.no_grad():
+            stage_x.copy_(host_x[i % n_host], non_blocking=True)
+            stage_dy.copy_(host_dy[i % n_host], non_blocking=True)
+        y = fwd_bwd(stage_x, stage_dy)
+        host_y.copy_(y.detach(), non_blocking=True)
+        host_dx.copy_(stage_x.grad, non_blocking=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for i in range(max(args.warmup, 3)):
+        resident_step(i)
+    torch.cuda.synchronize()
+    clocks = ClockSampler(local)
+    clocks.start()
+    l0 = lib.kv_launch_count()
+    ms_total = timed(resident_step, args.steps)
+    launches = lib.kv_launch_count() - l0
+    ms_e2e = timed(e2e_step, args.steps)
+    clk = clocks.stop()
+
+    prof = profile_kernels(lambda: resident_step(0), 3)
+    by_shape = prof.pop("_by_shape")
+    peaks = load_peaks()
+    gemm = {k: v for k, v in by_shape.items() if k.split(" ")[0] in FLOP_KERNELS}
+    top = max(gemm, key=lambda k: gemm[k]["ms_per_call"] * gemm[k]["calls"])
+    kernel_ms = sum(v["ms_per_step"] for v in prof.values())
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(top.replace(f"T{T} ", "T66192 "))  # the same launch inside the cfg4 step
+    roofline = {"bound": "tensor", "achieved": gemm[top]["tflops"], "peak": peaks["bf16_tflops_sustained"],
+                "unit": "TFLOP/s", "frac": gemm[top]["tflops"] / peaks["bf16_tflops_sustained"], "traffic": traffic,
+                "kernel": top, "kernel_ms_per_call": gemm[top]["ms_per_call"],
+                "kernel_share_of_step": gemm[top]["ms_per_call"] * gemm[top]["calls"] / kernel_ms,
+                "peak_source": peaks["source"] + " (sustained bf16 dense); burst " + str(peaks["bf16_tflops"]),
+                "by_shape": {k: {"calls": v["calls"], "ms_per_call": round(v["ms_per_call"], 4), "tflops": round(v["tflops"], 1)}
+                             for k, v in sorted(by_shape.items(), key=lambda kv: -kv[1]["ms_per_call"] * kv[1]["calls"])}}
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = host_threads()
+        cval, cms, n_done = time_layer_cpu(LAYER_CPU_T, 3, 30.0)
+        cpu_baseline = {"value": cval, "unit": LAYER_UNIT, "cores": cores, "kind": "port",
+                        "sample": f"{n_done} steps at T={LAYER_CPU_T} rows of the same two layers "
+                                  f"(oracle/kan_oracle.py, torch CPU fp32, {cms:.0f} ms/step)"}
+    if rank == 0:
+        ms_step = ms_total / args.steps
+        h2d = sum(t.numel() * t.element_size() for t in (host_x[0], host_dy[0]))
+        d2h = sum(t.numel() * t.element_size() for t in (host_y, host_dx))
+        line = {"metric": LAYER_METRIC, "value": world * layer_flops(T) / (ms_step * 1e-3) / 1e12, "unit": LAYER_UNIT,
+                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": layer_workload(T), "parallelism": f"replicas x{world}",
+                           "l2": f"no flush: one step touches {4e-6 * T * (768 * 3 + 3072 * 3):.0f} MB of activations and "
+                                 "gradients > 126 MB L2",
+                           "frac_of_sustained_peak": (layer_flops(T) / (ms_step * 1e-3) / 1e12) / peaks["bf16_tflops_sustained"],
+                           "frac_of_burst_peak": (layer_flops(T) / (ms_step * 1e-3) / 1e12) / peaks["bf16_tflops"]},
+                "e2e": {"value": world * layer_flops(T) / (ms_e2e / args.steps * 1e-3) / 1e12, "unit": LAYER_UNIT,
+                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu_baseline}
+        print(json.dumps(line), file=_OUT, flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 _OUT = sys.stdout
 
 
@@ -484,7 +740,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--config", default="cfg4", choices=sorted(CONFIGS))
+    ap.add_argument("--config", default="cfg4", choices=sorted(CONFIGS) + ["cfg5"])
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the config's)")
     ap.add_argument("--precision", default=None, choices=["fp32", "bf16"],
                     help="bf16 = tcgen05 / tensor-core kernels with fp32 accumulation, fp32 = exact SIMT kernels "
@@ -493,7 +749,16 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cuda-graph", action="store_true",
                     help="single GPU: capture the whole iteration in a CUDA graph (launch-bound small configs)")
+    ap.add_argument("--sweep-cpu", action="store_true",
+                    help="with --config cfg5: the CPU column of the layer sweep (oracle port), one JSON line per point")
     args = ap.parse_args()
+    if args.config == "cfg5" and args.sweep_cpu:
+        if int(os.environ.get("RANK", "0")) == 0:
+            cpu_layer_sweep(args)
+        return
+    if args.config == "cfg5":
+        (run_layer_reference_arm if args.impl == "reference" else run_layer_arm)(args)
+        return
     if args.precision is None:
         args.precision = "bf16" if args.bf16 else DEFAULT_PRECISION[args.config]
     if args.impl == "reference":

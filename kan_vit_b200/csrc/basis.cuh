@@ -17,6 +17,10 @@ struct BasisCtx {
   int M;            // basis count incl. base branch
   float rbf_denom;  // fastkan denominator
   uint32_t flags;
+  // effkan, tensor-core kernels only (make_ctx_tc): every feature shares one uniform knot vector t0 + j h, so the span
+  // index and the de Boor triangle need no knot loads.  The exact fp32 kernels keep uniform = 0 (stored knots).
+  int uniform;
+  float t0, inv_h;
 };
 
 __device__ __forceinline__ BasisCtx make_ctx(const kv_kan_desc_t& d, const float* fparams, int g) {
@@ -28,6 +32,21 @@ __device__ __forceinline__ BasisCtx make_ctx(const kv_kan_desc_t& d, const float
   c.M = d.M;
   c.rbf_denom = d.rbf_denom;
   c.flags = d.flags;
+  c.uniform = 0;
+  c.t0 = 0.0f;
+  c.inv_h = 0.0f;
+  return c;
+}
+
+// tensor-core kernels: as make_ctx, plus the uniform-grid probe kv_kan_pack wrote behind the knots of an effkan group
+__device__ __forceinline__ BasisCtx make_ctx_tc(const kv_kan_desc_t& d, const float* fparams, int g) {
+  BasisCtx c = make_ctx(d, fparams, g);
+  if (d.family == KV_EFFKAN && c.fp != nullptr) {
+    const float* probe = c.fp + (size_t)d.in_features * (d.grid_size + 2 * d.spline_order + 1);
+    c.uniform = probe[0] == 1.0f ? 1 : 0;
+    c.t0 = probe[1];
+    c.inv_h = probe[2];
+  }
   return c;
 }
 
@@ -52,9 +71,14 @@ __device__ __forceinline__ float fastkan_xn(const BasisCtx& c, int i, float x, f
 // N[r], r = 0..level, holds B_{j-level+r, level}.
 // ---------------------------------------------------------------------------------
 __device__ __forceinline__ int bspline_find_span(const float* __restrict__ t, int nknots, float x) {
-  if (!(x >= t[0]) || !(x < t[nknots - 1])) return -1;
-  int j = 0;
-  for (int q = 1; q < nknots - 1; ++q) j += (x >= t[q]) ? 1 : 0;
+  const float t0 = t[0], tl = t[nknots - 1];
+  if (!(x >= t0) || !(x < tl)) return -1;
+  // the largest j <= nknots - 2 with t[j] <= x: a guess from the grid ends (exact on a uniform grid up to rounding),
+  // then a walk -- a few steps on the quantile grids of update_grid, instead of one comparison per knot
+  int j = (int)((x - t0) * (float)(nknots - 1) / (tl - t0));
+  j = j < 0 ? 0 : (j > nknots - 2 ? nknots - 2 : j);
+  while (j > 0 && x < t[j]) --j;
+  while (j < nknots - 2 && x >= t[j + 1]) ++j;
   return j;
 }
 
@@ -114,6 +138,44 @@ __device__ __forceinline__ void effkan_deriv(const BasisCtx& c, int i, float x, 
   const int nb = c.G + c.k;
   if (Sink::kDense) {
     for (int m = 0; m < nb; ++m) s.put(m, 0.0f);
+  }
+  if (c.uniform && c.k >= 1) {
+    // uniform knots (tensor-core kernels): span and triangle in units of h, no knot loads;
+    // B'_{a,k} = (B_{a,k-1} - B_{a+1,k-1}) / h
+    const float sx = (x - c.t0) * c.inv_h;
+    if (sx >= 0.0f && sx < (float)(nknots - 1)) {
+      const int j = min((int)sx, nknots - 2);
+      const float u = sx - (float)j;
+      float N[KV_MAX_SPLINE_ORDER + 1];
+#pragma unroll
+      for (int r = 0; r <= KV_MAX_SPLINE_ORDER; ++r) N[r] = 0.0f;
+      N[0] = 1.0f;
+#pragma unroll
+      for (int p = 1; p <= KV_MAX_SPLINE_ORDER; ++p) {
+        if (p <= c.k - 1) {
+          float saved = 0.0f;
+          const float ip = 1.0f / (float)p;
+#pragma unroll
+          for (int r = 0; r < p; ++r) {
+            const float temp = N[r] * ip;
+            N[r] = saved + ((float)(r + 1) - u) * temp;
+            saved = (u + (float)(p - r - 1)) * temp;
+          }
+          N[p] = saved;
+        }
+      }
+#pragma unroll
+      for (int r = 0; r <= KV_MAX_SPLINE_ORDER; ++r) {
+        const int a = j - c.k + r;
+        if (r <= c.k && a >= 0 && a < nb) {
+          const float lo = (r >= 1) ? N[r >= 1 ? r - 1 : 0] : 0.0f;
+          const float hi = (r <= c.k - 1) ? N[r] : 0.0f;
+          s.put(a, (lo - hi) * c.inv_h);
+        }
+      }
+    }
+    s.put(nb, silu_grad_f(x));
+    return;
   }
   int j = bspline_find_span(t, nknots, x);
   if (j >= 0 && c.k >= 1) {

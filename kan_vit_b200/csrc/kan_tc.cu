@@ -17,6 +17,7 @@
 //   warps 2..9 = A producers (basis prologue), then epilogue.
 #include <cstdio>
 #include <cstdlib>
+#include <type_traits>
 #include <cuda.h>   // CUtensorMap and the encode entry point's types (the function itself is fetched at run time)
 #include "basis.cuh"
 #include "internal.cuh"
@@ -374,6 +375,60 @@ __device__ __forceinline__ void effkan8_chunk4(uint8_t* base, int qg, const floa
       make_uint2(pack_bf16(sv[0], sv[1]), pack_bf16(sv[2], sv[3]));
 }
 
+// The k + 1 B-splines that are non-zero at x for feature i: N[r] = B_{jb + r, k}(x), jb = j - k for the knot span j that
+// holds x (far negative, N = 0, when x lies outside [t_0, t_last) or i is beyond the layer's features).
+//   c.uniform: one uniform knot vector t0 + j h (any grid_size) -- span and triangle in units of h, no knot loads;
+//   otherwise: span search on the feature's own knots (a guess from the grid ends, corrected by a short walk), the 2k
+//   knots around the span, and the triangular de Boor scheme with k (k + 1) / 2 divisions -- every term the
+//   reference's full recursion (models/effkan.py:99-132) forms for a non-zero basis, none of the zero ones.
+__device__ __forceinline__ void effkan_local_basis(const BasisCtx& c, int i, float xv, float (&N)[KV_MAX_SPLINE_ORDER + 1],
+                                                   int& jb) {
+  constexpr int KMAX = KV_MAX_SPLINE_ORDER;
+  const int k = c.k, nk = c.G + 2 * c.k + 1;
+#pragma unroll
+  for (int r = 0; r <= KMAX; ++r) N[r] = 0.0f;
+  jb = -(1 << 20);
+  if (i >= c.in) return;
+  float left[KMAX + 1], right[KMAX + 1];
+  int j;
+  if (c.uniform) {
+    const float sx = (xv - c.t0) * c.inv_h;
+    if (!(sx >= 0.0f) || !(sx < (float)(nk - 1))) return;
+    j = min((int)sx, nk - 2);
+    const float u = sx - (float)j;
+#pragma unroll
+    for (int pp = 1; pp <= KMAX; ++pp) {
+      left[pp] = u + (float)(pp - 1);
+      right[pp] = (float)pp - u;
+    }
+  } else {
+    const float* t = c.fp + (size_t)i * nk;
+    j = bspline_find_span(t, nk, xv);
+    if (j < 0) return;
+#pragma unroll
+    for (int pp = 1; pp <= KMAX; ++pp) {
+      left[pp] = xv - t[max(j + 1 - pp, 0)];
+      right[pp] = t[min(j + pp, nk - 1)] - xv;
+    }
+  }
+  N[0] = 1.0f;
+#pragma unroll
+  for (int pp = 1; pp <= KMAX; ++pp) {
+    if (pp <= k) {
+      float saved = 0.0f;
+#pragma unroll
+      for (int r = 0; r < pp; ++r) {
+        const float den = right[r + 1] + left[pp - r];      // uniform: exactly pp
+        const float temp = den != 0.0f ? __fdividef(N[r], den) : 0.0f;
+        N[r] = saved + right[r + 1] * temp;
+        saved = left[pp - r] * temp;
+      }
+      N[pp] = saved;
+    }
+  }
+  jb = j - k;
+}
+
 // Basis-major layout, basis index outermost: 8 features x one m = one 16-byte store.
 // basis_octet: the values of 8 consecutive features (one 16-byte vector per basis function m) for the bases
 // m0 <= m < m0 + Mt, written at dst + (m - m0) * stride.
@@ -397,14 +452,33 @@ __device__ __forceinline__ void basis_octet(uint8_t* dst, int stride, int m0, in
              pack_bf16(v[6], v[7]));
   };
   if (F == KV_EFFKAN) {
-#pragma unroll 1
-    for (int q = 0; q < 8; ++q) {
-      StrideSink sink{dst + q * 2, stride, m0, Mt};
-      if (i0 + q < c.in) {
-        basis_eval<F>(c, i0 + q, x[q], x[q], sink);
-      } else {
-        for (int m = 0; m < M; ++m) sink.put(m, 0.0f);
+    // B-splines on arbitrary per-feature knots (grid_size != 5, or any grid after update_grid), models/effkan.py:99-132.
+    // At most k + 1 bases are non-zero at x: those of the knot span j that holds it.  Per feature: find the span (a
+    // guess from the grid ends, corrected by a short walk), load the 2k knots around it and run the triangular
+    // de Boor scheme (k (k + 1) / 2 divisions) -- every term the reference's full recursion forms for a non-zero
+    // basis, none of the zero ones.  Then one 16-byte row per basis index: for feature q the value is N[q][m - jb[q]]
+    // inside the span's window and 0 elsewhere.
+    constexpr int KMAX = KV_MAX_SPLINE_ORDER;
+    const int k = c.k, nb = c.G + c.k;
+    float N[8][KMAX + 1];
+    int jb[8];   // index of the first non-zero basis (j - k); far negative when x lies outside [t_0, t_last)
+#pragma unroll
+    for (int q = 0; q < 8; ++q) effkan_local_basis(c, i0 + q, x[q], N[q], jb[q]);
+    for (int m = max(m0, 0); m < min(nb, m0 + Mt); ++m) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const int r = m - jb[q];
+        float val = 0.0f;
+#pragma unroll
+        for (int rr = 0; rr <= KMAX; ++rr) val = (r == rr) ? N[q][rr] : val;
+        v[q] = val;
       }
+      emit(m);
+    }
+    if (nb >= m0 && nb < m0 + Mt) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = (i0 + q < c.in) ? fast_silu(x[q]) : 0.0f;
+      emit(nb);
     }
     return;
   }
@@ -504,6 +578,14 @@ __device__ __forceinline__ void basis_octet(uint8_t* dst, int stride, int m0, in
   }
 }
 
+// out-of-line copy for kernels whose hot path must not inherit the register pressure of the arbitrary-knot branch
+// (the persistent forward kernel runs 448 threads: 128 registers per thread)
+template <int F>
+__device__ __noinline__ void basis_octet_call(uint8_t* dst, int stride, int m0, int Mt, const float (&x)[8],
+                                              const BasisCtx& c, int i0, float mu, float rs) {
+  basis_octet<F>(dst, stride, m0, Mt, x, c, i0, mu, rs);
+}
+
 template <int F>
 __device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const float (&x)[8], const BasisCtx& c,
                                                   int i0, float mu, float rs) {
@@ -584,8 +666,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
   const Geom gm = p.gm;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();  // 0 = leader of the CTA pair
-  const int n_tile = blockIdx.y % gm.n_tiles;
-  const int m_tile = (blockIdx.y / gm.n_tiles) * 2 + (int)rank;
+  const int n_tile = (blockIdx.x >> 1) % gm.n_tiles;
+  const int m_tile = ((blockIdx.x >> 1) / gm.n_tiles) * 2 + (int)rank;
   const int g = blockIdx.z;
   const int M = d.M;
   const int n_units = gm.n_units;
@@ -614,7 +696,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   // timing experiments only (d.reserved & 32): first tile stamps clock64 into the head of Y
-  const bool dbg = (d.reserved & 32) && blockIdx.y == 0 && blockIdx.z == 0;
+  const bool dbg = (d.reserved & 32) && (blockIdx.x >> 1) == 0 && blockIdx.z == 0;
   uint32_t* dbuf = reinterpret_cast<uint32_t*>(smem + A_RING_BYTES + B_RING_BYTES + BAR_BYTES);
   auto stamp = [&](int role, int u, int k) {
     if (dbg && u < 64) dbuf[(role * 64 + u) * 4 + k] = (uint32_t)clock64();
@@ -705,8 +787,45 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
           if (++sc == NCH) { sc = 0; phA ^= 1; }
         }
         ptx::tc_commit2_elect(tmem_full);
+      } else if (!(d.reserved & (4 | 32 | 2048))) {
+        // parts that do not split into whole stages of 3 (M = 14: two parts of 7, ...): the same warp-wide issue with
+        // the stage bookkeeping per unit
+        const uint32_t a_hi = (uint32_t)(da0 >> 32), b1_hi = (uint32_t)(db1_0 >> 32), b2_hi = (uint32_t)(db2_0 >> 32);
+        const uint32_t a_lo0 = (uint32_t)da0, b1_lo0 = (uint32_t)db1_0, b2_lo0 = (uint32_t)db2_0;
+        const uint32_t a_unit = A_UNIT_BYTES >> 4;
+        int sc = 0, sb = 0, ub = 0, u = 0;
+        uint32_t phA = 0, phB = 0, acc = 0;
+        for (int ch = 0; ch < gm.loopC; ++ch) {
+          for (int m0 = 0; m0 < LM; m0 += Mp) {
+            const int m1 = min(LM, m0 + Mp);
+            ptx::mbar_wait(fullA(sc), phA);
+            ptx::tc_fence_after();
+            uint32_t a_lo = a_lo0 + (uint32_t)sc * a_slot_step;
+            for (int q = m0; q < m1; ++q, ++u) {
+              if (ub == 0) {
+                ptx::mbar_wait(fullB(sb), phB);
+                ptx::tc_fence_after();
+              }
+              const uint32_t boff = (uint32_t)(sb * S + ub) * b_unit_step;
+              ptx::mma2_bf16_ss_lohi_elect(tmem_base, a_lo, a_hi, b1_lo0 + boff, b1_hi, idesc1, acc);
+              if (n2) ptx::mma2_bf16_ss_lohi_elect(tmem_base + 256, a_lo, a_hi, b2_lo0 + boff, b2_hi, idesc2, acc);
+              acc = 1;
+              a_lo += a_unit;
+              if (ub + 1 == S || u + 1 == n_units) {
+                ptx::tc_commit2_elect(emptyB(sb));
+                ub = 0;
+                if (++sb == NB) { sb = 0; phB ^= 1; }
+              } else {
+                ++ub;
+              }
+            }
+            ptx::tc_commit2_elect(emptyA(sc));
+            if (++sc == NCH) { sc = 0; phA ^= 1; }
+          }
+        }
+        ptx::tc_commit2_elect(tmem_full);
       } else if (lane == 0) {
-        // generic loop (parts that do not split into whole stages, timing experiments): one thread
+        // timing experiments (stamps, no-MMA runs): one thread
         int sc = 0, sb = 0, ub = 0, u = 0;
         uint32_t phA = 0, phB = 0;
         uint64_t db1 = db1_0, db2 = db2_0;   // B descriptors of the current unit
@@ -774,7 +893,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
     const bool row_ok = t < d.T;
     const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
     const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0);
-    const BasisCtx c = make_ctx(d, p.fparams, g);
+    const BasisCtx c = make_ctx_tc(d, p.fparams, g);
     const int layout = group_layout(d, gm, p.fparams, g);
     float gt0 = 0.f, ginv_h = 0.f;
     if (layout == LAYOUT_EFFKAN8) {
@@ -847,16 +966,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
           if constexpr (FPT == 8) effkan8_chunk(base, wg, cur, gt0, ginv_h);
           else effkan8_chunk4(base, wg, cur, gt0, ginv_h);
         } else {
-          // arbitrary knots: Cox-de Boor per feature, scattered 2-byte stores; feature f = wg*FPT + q of the chunk
-          // sits in k-half f / 8 at element f % 8
+          // arbitrary knots: span search + local de Boor per feature, 16-byte rows (basis_octet)
+          if constexpr (FPT == 8) {
+            basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, m0, Mt, cur, c, i0, mu, rs);
+          } else {
 #pragma unroll 1
-          for (int q = 0; q < FPT; ++q) {
-            const int f = wg * FPT + q;
-            StrideSink sink{base + (f >> 3) * 2048 + (f & 7) * 2, A_UNIT_BYTES, m0, Mt};
-            if (i0 + q < in) {
-              basis_eval<F>(c, i0 + q, cur[q], cur[q], sink);
-            } else {
-              for (int m = m0; m < m0 + Mt; ++m) sink.put(m, 0.0f);
+            for (int q = 0; q < FPT; ++q) {   // feature f = wg*FPT + q of the chunk sits in k-half f / 8 at element f % 8
+              const int f = wg * FPT + q;
+              StrideSink sink{base + (f >> 3) * 2048 + (f & 7) * 2, A_UNIT_BYTES, m0, Mt};
+              if (i0 + q < in) {
+                basis_eval<F>(c, i0 + q, cur[q], cur[q], sink);
+              } else {
+                for (int m = m0; m < m0 + Mt; ++m) sink.put(m, 0.0f);
+              }
             }
           }
         }
@@ -1022,13 +1144,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
 //     burst of every CTA at once) and the per-tile set-up (TMEM allocation, barrier init, cluster sync, first
 //     operand fetch: ~6000 cycles) no longer sit between two main loops -- in the one-tile-per-CTA kernel they took
 //     ~30 % of a 768 -> 3072 tile and most of a 64 -> 192 (q/k/v) tile;
-//   * the operand rings simply keep running across tiles (loader and producers run ahead into the next tile).
+//   * the operand rings simply keep running across tiles (loader and producers run ahead into the next tile);
+//   * WEIGHT-RESIDENT mode: when the weight image of a whole output tile fits the B ring (the per-head q/k/v maps:
+//     36 units x 6 KB = 108 KB per CTA), each pair walks a CONTIGUOUS range of row blocks of one (group, output tile)
+//     and the image is fetched once per range instead of once per tile -- the q/k/v layer re-read 108 KB per CTA
+//     and tile from L2 for a 3 500-cycle main loop;
+//   * the producers fetch the first chunk of the next tile's X while they evaluate the last chunk of the current one,
+//     and keep the per-group prologue constants while the group does not change.
 // Warps: 0 loader, 1 MMA issuer (leader) / B relay (peer), 2-9 basis producers, 10-13 epilogue.
 // =========================================================================================
 constexpr int P_NPW = 8;                       // producer warps
 constexpr int P_NEW = 4;                       // epilogue warps (one per TMEM lane quadrant)
 constexpr int P_THREADS = 32 * (2 + P_NPW + P_NEW);
-constexpr int P_B_RING = 96 * 1024;
+constexpr int P_B_RING = 112 * 1024;
 constexpr int P_STG_BYTES = P_NEW * 32 * 36 * 4;   // epilogue staging: 32 rows x 36 floats per warp
 constexpr int P_SMEM = A_RING_BYTES + P_B_RING + P_STG_BYTES + BAR_BYTES;
 
@@ -1062,14 +1190,29 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
   // tile list: output tiles of one row block adjacent (their X tile is shared through L2 at the same time)
   const int n_pairs = ceil_div(d.T, 2 * BM);
   const int total_tiles = d.n_groups * n_pairs * gm.n_tiles;
-  const int n_my = (total_tiles - (int)blockIdx.y + (int)gridDim.y - 1) / (int)gridDim.y;
+  // weight-resident mode: the B ring holds the whole weight image of a tile (stage st lives in ring slot st)
+  const bool resident = n_stages <= NB;
+  const int G = (int)gridDim.y, y = (int)blockIdx.y;
+  const int per = total_tiles / G, rem = total_tiles % G;
+  const int n_my = resident ? per + (y < rem ? 1 : 0) : (total_tiles - y + G - 1) / G;
+  const int first = y * per + (y < rem ? y : rem);
   auto tile_of = [&](int it, int& g, int& mp, int& n_tile) {
-    const int tile = (int)blockIdx.y + it * (int)gridDim.y;
-    n_tile = tile % gm.n_tiles;
-    const int r = tile / gm.n_tiles;
-    mp = r % n_pairs;
-    g = r / n_pairs;
+    if (resident) {            // contiguous range, row block fastest: (g, n_tile) changes at most a few times
+      const int tile = first + it;
+      mp = tile % n_pairs;
+      const int r = tile / n_pairs;
+      n_tile = r % gm.n_tiles;
+      g = r / gm.n_tiles;
+    } else {                   // interleaved, output tile fastest: the pairs running together share the X rows
+      const int tile = y + it * G;
+      n_tile = tile % gm.n_tiles;
+      const int r = tile / gm.n_tiles;
+      mp = r % n_pairs;
+      g = r / n_pairs;
+    }
   };
+  // resident mode: tile `it` needs a fresh weight image iff its (g, n_tile) differs from the previous tile's
+  auto reload = [&](int it) { return it == 0 || (first + it) / n_pairs != (first + it - 1) / n_pairs; };
 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < NCH_MAX; ++s) {
@@ -1105,14 +1248,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
         tile_of(it, g, mp, n_tile);
         const uint8_t* src = reinterpret_cast<const uint8_t*>(p.wt) +
                              (((size_t)g * gm.n_tiles + n_tile) * 2 + rank) * (size_t)n_units * b_unit_bytes;
+        if (resident) {
+          if (!reload(it)) continue;
+          s = 0;               // slot = stage; ph flips once per reload (set below)
+        }
         for (int st = 0; st < n_stages; ++st) {
           const int nu = min(S, n_units - st * S);
           ptx::mbar_wait(emptyB(s), ph);
           ptx::mbar_arrive_expect_tx(fullB(s), nu * b_unit_bytes);
           ptx::bulk_g2s(ptx::smem_u32(sB) + s * S * b_unit_bytes, src + (size_t)st * S * b_unit_bytes,
                         nu * b_unit_bytes, fullB(s));
-          if (++s == NB) { s = 0; ph ^= 1; }
+          if (++s == NB && !resident) { s = 0; ph ^= 1; }
         }
+        if (resident) ph ^= 1;
       }
     }
     __syncwarp();
@@ -1130,7 +1278,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
       const bool fast = S == 3 && (LM % Mp) == 0 && (Mp % 3) == 0;
       const int n_parts_total = gm.loopC * gm.npart;
       int sc = 0, sb = 0;
-      uint32_t phA = 0, phB = 0;
+      uint32_t phA = 0, phB = 0, n_reloads = 0;
       for (int it = 0; it < n_my; ++it) {
         const int buf = it & 1;
         // the epilogue warps of both CTAs have drained this accumulator (its use two tiles ago)
@@ -1138,6 +1286,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
         ptx::tc_fence_after();
         const uint32_t tacc = tmem_base + buf * 256;
         uint32_t acc = 0;
+        // resident weights: wait for the image only when it was (re)loaded for this tile, hand the slots back to the
+        // loader only when the next tile needs another image
+        const bool wait_b = !resident || reload(it);
+        const bool free_b = !resident || (it + 1 < n_my && reload(it + 1));
+        if (resident) {
+          sb = 0;
+          if (wait_b) phB = n_reloads++ & 1u;
+        }
         if (fast) {
           const int stages_per_part = Mp / 3;
           for (int part = 0; part < n_parts_total; ++part) {
@@ -1145,15 +1301,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
             ptx::tc_fence_after();
             uint32_t a_lo = a_lo0 + (uint32_t)sc * a_slot_step;
             for (int st = 0; st < stages_per_part; ++st) {
-              ptx::mbar_wait(fullB(sb), phB);
-              ptx::tc_fence_after();
+              if (wait_b) {
+                ptx::mbar_wait(fullB(sb), phB);
+                ptx::tc_fence_after();
+              }
               const uint32_t b_lo = b_lo0 + (uint32_t)sb * 3u * b_unit_step;
 #pragma unroll
               for (int k = 0; k < 3; ++k) {
                 ptx::mma2_bf16_ss_lohi_elect(tacc, a_lo + k * a_unit, a_hi, b_lo + k * b_unit_step, b_hi, idesc, acc);
                 acc = 1;
               }
-              ptx::tc_commit2_elect(emptyB(sb));
+              if (free_b) ptx::tc_commit2_elect(emptyB(sb));
               if (++sb == NB) { sb = 0; phB ^= 1; }
               a_lo += 3 * a_unit;
             }
@@ -1169,7 +1327,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
               ptx::tc_fence_after();
               uint32_t a_lo = a_lo0 + (uint32_t)sc * a_slot_step;
               for (int q = m0; q < m1; ++q, ++u) {
-                if (ub == 0) {
+                if (ub == 0 && wait_b) {
                   ptx::mbar_wait(fullB(sb), phB);
                   ptx::tc_fence_after();
                 }
@@ -1177,7 +1335,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
                 acc = 1;
                 a_lo += a_unit;
                 if (ub + 1 == S || u + 1 == n_units) {
-                  ptx::tc_commit2_elect(emptyB(sb));
+                  if (free_b) ptx::tc_commit2_elect(emptyB(sb));
                   ub = 0;
                   if (++sb == NB) { sb = 0; phB ^= 1; }
                 } else {
@@ -1195,10 +1353,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
       // ================= peer CTA: tell the leader when our half of each B stage has landed ===========
       int s = 0;
       uint32_t ph = 0;
-      for (int st = 0; st < n_stages * n_my; ++st) {
-        ptx::mbar_wait(fullB(s), ph);
-        ptx::mbar_arrive_cluster(ptx::mapa(fullB(s), 0));
-        if (++s == NB) { s = 0; ph ^= 1; }
+      if (resident) {
+        for (int it = 0; it < n_my; ++it) {
+          if (!reload(it)) continue;
+          for (int st = 0; st < n_stages; ++st) {
+            ptx::mbar_wait(fullB(st), ph);
+            ptx::mbar_arrive_cluster(ptx::mapa(fullB(st), 0));
+          }
+          ph ^= 1;
+        }
+      } else {
+        for (int st = 0; st < n_stages * n_my; ++st) {
+          ptx::mbar_wait(fullB(s), ph);
+          ptx::mbar_arrive_cluster(ptx::mapa(fullB(s), 0));
+          if (++s == NB) { s = 0; ph ^= 1; }
+        }
       }
     }
     __syncwarp();
@@ -1210,87 +1379,97 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
     const int in = d.in_features;
     const int row_off = (r >> 3) * 128 + (r & 7) * 16;
     int slot_i = 0;   // running ring-slot counter (parts produced so far, all tiles)
-    for (int it = 0; it < n_my; ++it) {
+    // X rows of this thread in tile `it`
+    struct TileX { const float* xrow; bool row_ok, vec; int g, t, slice; };
+    auto tile_x = [&](int it) {
       int g, mp, n_tile;
       tile_of(it, g, mp, n_tile);
-      const int t0 = (mp * 2 + (int)rank) * BM;
-      const int slice = g / d.x_share;
-      const int xoff = slice * in;
-      const bool vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0);
-      const bool mvec = vec && ((reinterpret_cast<uintptr_t>(p.in_mask) & 15) == 0);
-      const int t = t0 + r;
-      const bool row_ok = t < d.T;
-      const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
-      const BasisCtx c = make_ctx(d, p.fparams, g);
-      const int layout = group_layout(d, gm, p.fparams, g);
+      TileX x;
+      x.g = g;
+      x.slice = g / d.x_share;
+      const int xoff = x.slice * in;
+      x.t = (mp * 2 + (int)rank) * BM + r;
+      x.row_ok = x.t < d.T;
+      x.vec = ((d.ldx & 3) == 0) && ((xoff & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0);
+      x.xrow = p.X + (size_t)(x.row_ok ? x.t : 0) * d.ldx + xoff;
+      return x;
+    };
+    if constexpr (F == KV_LINEAR) {
+      for (int it = 0; it < n_my; ++it) {
+        const TileX x = tile_x(it);
+        // Linear as the input gradient of a ReLU layer: dY is gated by the layer's own forward output
+        const float* mrow = p.in_mask != nullptr ? p.in_mask + (x.xrow - p.X) : nullptr;
+        const bool mvec = x.vec && ((reinterpret_cast<uintptr_t>(p.in_mask) & 15) == 0);
+        linear_produce_tile(gm, x.xrow, mrow, x.row_ok, x.vec, mvec, in, wg, sA + row_off, bar0, NCH, lane, slot_i);
+      }
+    } else {
+      // per-group prologue constants: reloaded only when the group changes
+      int g_cached = -1, layout = LAYOUT_BASIS_MAJOR;
       float gt0 = 0.f, ginv_h = 0.f;
-      if (layout == LAYOUT_EFFKAN8) {
-        const float* probe = c.fp + (size_t)in * (d.grid_size + 2 * d.spline_order + 1);
-        gt0 = probe[1];
-        ginv_h = probe[2];
-      }
-      float mu = 0.f, rs = 1.f;
-      if (F == KV_FASTKAN && !(d.flags & KV_FLAG_NO_LAYERNORM) && row_ok) {
-        mu = p.mean[(size_t)t * n_slices + slice];
-        rs = p.rstd[(size_t)t * n_slices + slice];
-      }
-      // Linear as the input gradient of a ReLU layer: dY is gated by the layer's own forward output
-      const float* mrow = (F == KV_LINEAR && p.in_mask != nullptr)
-                              ? p.in_mask + (size_t)(row_ok ? t : 0) * d.ldx + xoff : nullptr;
-      auto gate = [&](int i0g, float (&v)[8]) {
-        if (F == KV_LINEAR && mrow != nullptr) {
-          float mk[8];
-          load_x8(mrow, i0g, in, row_ok, mvec, mk);
-#pragma unroll
-          for (int q = 0; q < 8; ++q) v[q] = mk[q] > 0.0f ? v[q] : 0.0f;
-        }
-      };
-      if constexpr (F == KV_LINEAR) {
-        linear_produce_tile(gm, xrow, mrow, row_ok, vec, mvec, in, wg, sA + row_off, bar0, NCH, lane, slot_i);
-        continue;
-      }
       float cur[8];
-      load_x8(xrow, wg * 8, in, row_ok, vec, cur);
-      gate(wg * 8, cur);
-      for (int ch = 0; ch < gm.n_chunks; ++ch) {
-        float nxt[8];
-        if (ch + 1 < gm.n_chunks) {
-          load_x8(xrow, (ch + 1) * KU + wg * 8, in, row_ok, vec, nxt);
-          gate((ch + 1) * KU + wg * 8, nxt);
-        } else {
-#pragma unroll
-          for (int q = 0; q < 8; ++q) nxt[q] = 0.0f;
-        }
-        const int i0 = ch * KU + wg * 8;
-        for (int pt = 0; pt < gm.npart; ++pt, ++slot_i) {   // one ring slot per part: bases [m0, m0 + Mt) of the chunk
-          const int sc = slot_i % NCH;
-          const int m0 = pt * Mp, Mt = min(Mp, M - m0);
-          ptx::mbar_wait(emptyA(sc), ((slot_i / NCH) & 1) ^ 1);
-          uint8_t* base = sA + sc * Mp * A_UNIT_BYTES + row_off;
-          if constexpr (F == KV_EFFKAN) {
-            if (layout == LAYOUT_EFFKAN8) {            // M = 9: one part
-              effkan8_chunk(base, wg, cur, gt0, ginv_h);
-            } else {
-              // arbitrary knots: Cox-de Boor per feature, scattered 2-byte stores
-#pragma unroll 1
-              for (int q = 0; q < 8; ++q) {
-                StrideSink sink{base + wg * 2048 + q * 2, A_UNIT_BYTES, m0, Mt};
-                if (i0 + q < in) {
-                  basis_eval<F>(c, i0 + q, cur[q], cur[q], sink);
-                } else {
-                  for (int m = m0; m < m0 + Mt; ++m) sink.put(m, 0.0f);
-                }
-              }
-            }
-          } else {
-            basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, m0, Mt, cur, c, i0, mu, rs);
+      TileX x = tile_x(0);
+      if (n_my > 0) load_x8(x.xrow, wg * 8, in, x.row_ok, x.vec, cur);
+      for (int it = 0; it < n_my; ++it) {
+        if (x.g != g_cached) {
+          g_cached = x.g;
+          layout = group_layout(d, gm, p.fparams, x.g);
+          if (layout == LAYOUT_EFFKAN8) {
+            const float* probe = p.fparams + (size_t)x.g * d.fparam_stride +
+                                 (size_t)in * (d.grid_size + 2 * d.spline_order + 1);
+            gt0 = probe[1];
+            ginv_h = probe[2];
           }
-          ptx::fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(sc), 0));  // the leader's barrier
         }
+        float mu = 0.f, rs = 1.f;
+        if (F == KV_FASTKAN && !(d.flags & KV_FLAG_NO_LAYERNORM) && x.row_ok) {
+          mu = p.mean[(size_t)x.t * n_slices + x.slice];
+          rs = p.rstd[(size_t)x.t * n_slices + x.slice];
+        }
+        TileX xn = x;
+        // two copies of the chunk loop (closed-form default grid / everything else): the register-hungry arbitrary-knot
+        // prologue must not push spills into the default path
+        auto run_tile = [&](auto fast_tag) {
+          constexpr bool FAST = decltype(fast_tag)::value;
+          // (the context is rebuilt per tile rather than kept across tiles: it would stay live through the fast copy)
+          BasisCtx c;
+          if constexpr (!FAST) c = make_ctx_tc(d, p.fparams, x.g);
+          for (int ch = 0; ch < gm.n_chunks; ++ch) {
+            float nxt[8];
+            if (ch + 1 < gm.n_chunks) {
+              load_x8(x.xrow, (ch + 1) * KU + wg * 8, in, x.row_ok, x.vec, nxt);
+            } else if (it + 1 < n_my) {           // the next tile's first chunk rides under this tile's last one
+              xn = tile_x(it + 1);
+              load_x8(xn.xrow, wg * 8, in, xn.row_ok, xn.vec, nxt);
+            } else {
 #pragma unroll
-        for (int q = 0; q < 8; ++q) cur[q] = nxt[q];
+              for (int q = 0; q < 8; ++q) nxt[q] = 0.0f;
+            }
+            const int i0 = ch * KU + wg * 8;
+            for (int pt = 0; pt < gm.npart; ++pt, ++slot_i) {   // one ring slot per part: bases [m0, m0 + Mt) of the chunk
+              const int sc = slot_i % NCH;
+              const int m0 = pt * Mp, Mt = min(Mp, M - m0);
+              ptx::mbar_wait(emptyA(sc), ((slot_i / NCH) & 1) ^ 1);
+              uint8_t* base = sA + sc * Mp * A_UNIT_BYTES + row_off;
+              if constexpr (FAST) {
+                effkan8_chunk(base, wg, cur, gt0, ginv_h);   // M = 9: one part
+              } else {
+                // every other family; effkan on arbitrary knots: span search + local de Boor, 16-byte rows
+                basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, m0, Mt, cur, c, i0, mu, rs);
+              }
+              ptx::fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(fullA(sc), 0));  // the leader's barrier
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) cur[q] = nxt[q];
+          }
+        };
+        if (F == KV_EFFKAN && layout == LAYOUT_EFFKAN8) {
+          if constexpr (F == KV_EFFKAN) run_tile(std::true_type{});
+        } else {
+          run_tile(std::false_type{});
+        }
+        x = xn;
       }
     }
   } else {
@@ -1490,8 +1669,10 @@ static int launch_fwd(const FwdParams& p, cudaStream_t st) {
   if (p.gm.BN <= 256 && fwd_persistent_enabled() && !(p.d.reserved & 0xfff)) return launch_fwd_persistent<F>(p, st);
   KV_SMEM_OPT_IN((kan_tc_fwd_kernel<F, NPW>), SMEM_BYTES, "tc_fwd smem attribute");
   const int n_pairs = ceil_div(p.d.T, 2 * BM);
-  if ((long long)n_pairs * p.gm.n_tiles > 65535 || p.d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
-  dim3 grid(2, n_pairs * p.gm.n_tiles, p.d.n_groups);  // x = CTA pair; output tiles of one row pair adjacent
+  if ((long long)n_pairs * p.gm.n_tiles > 0x3fffffffLL || p.d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
+  // x = 2 * (row pair, output tile): consecutive CTAs form the pair (grid.y / z stop at 65535, x does not); output
+  // tiles of one row pair adjacent
+  dim3 grid(2 * n_pairs * p.gm.n_tiles, 1, p.d.n_groups);
   kan_tc_fwd_kernel<F, NPW><<<grid, 32 * (2 + NPW), SMEM_BYTES, st>>>(p);
   KV_CHECK_LAUNCH("kan_tc_fwd_kernel");
   return KV_OK;
@@ -1665,9 +1846,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8
   // one CTA pair = one 256-row block x `tpc` consecutive column tiles (set-up, TMEM allocation and pipeline fill
   // are paid once; the loader runs ahead into the next tile while the epilogue drains the accumulator)
   const int n_tgroups = (b.n_tiles + p.tpc - 1) / p.tpc;
-  const int tile0 = (blockIdx.y % n_tgroups) * p.tpc;
+  const int tile0 = ((blockIdx.x >> 1) % n_tgroups) * p.tpc;
   const int tile1 = min(tile0 + p.tpc, b.n_tiles);
-  const int m_tile = (blockIdx.y / n_tgroups) * 2 + (int)rank;
+  const int m_tile = ((blockIdx.x >> 1) / n_tgroups) * 2 + (int)rank;
   const int g = blockIdx.z;
   const int t0 = m_tile * BM;
   const int SW = b.SW, n_sub = b.n_sub;
@@ -1902,8 +2083,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
   const BwdGeom b = p.b;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
-  const int tile = blockIdx.y % b.n_tiles;
-  const int m_tile = (blockIdx.y / b.n_tiles) * 2 + (int)rank;
+  const int tile = (blockIdx.x >> 1) % b.n_tiles;
+  const int m_tile = ((blockIdx.x >> 1) / b.n_tiles) * 2 + (int)rank;
   const int g = blockIdx.z;
   const int t0 = m_tile * BM;
   const int SW = b.SW, n_sub = b.n_sub;
@@ -2000,7 +2181,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
     const int te = t0 + q4 * 32 + lane;
     const bool row_ok = te < d.T;
     const int in = d.in_features, M = d.M;
-    const BasisCtx c = make_ctx(d, p.fparams, g);
+    const BasisCtx c = make_ctx_tc(d, p.fparams, g);
     const int n_slices = d.n_groups / d.x_share, slice = g / d.x_share;
     const int xoff = slice * in;
     const bool shared_slice = d.x_share > 1;  // several groups add into the same dX columns (zeroed by the host)
@@ -2172,8 +2353,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
   const BwdGeom b = p.b;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
-  const int n_tile = blockIdx.y % p.gm.n_tiles;
-  const int kt = (blockIdx.y / p.gm.n_tiles) * 2 + (int)rank;   // this CTA's K' tile
+  const int n_tile = (blockIdx.x >> 1) % p.gm.n_tiles;
+  const int kt = ((blockIdx.x >> 1) / p.gm.n_tiles) * 2 + (int)rank;   // this CTA's K' tile
   const int g = blockIdx.z / p.tsplits, ts = blockIdx.z % p.tsplits;
   const int BN = p.gm.BN;
   const int n1 = BN > 256 ? 256 : BN, n2 = BN - n1;
@@ -2312,7 +2493,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
     uint32_t ph = 1;
     if (generic) {
       // ---- generic producers: thread = (row tl, part fb); part fb evaluates octets fb, fb + 4, ... of the tile
-      const BasisCtx c = make_ctx(d, p.fparams, g);
+      const BasisCtx c = make_ctx_tc(d, p.fparams, g);
       const int n_slices = d.n_groups / d.x_share, slice = g / d.x_share;
       const bool ln = (F == KV_FASTKAN) && !(d.flags & KV_FLAG_NO_LAYERNORM);
       int s = 0;
@@ -2744,8 +2925,8 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
     if (rc != KV_OK) return rc;
   }
   const int n_pairs = ceil_div(d.T, 2 * tc::BM);
-  if ((long long)n_pairs * p.b.n_tiles > 65535 || d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
-  dim3 grid(2, n_pairs * p.b.n_tiles, d.n_groups);
+  if ((long long)n_pairs * p.b.n_tiles > 0x3fffffffLL || d.n_groups > 65535) return KV_ERR_BAD_SHAPE;
+  dim3 grid(2 * n_pairs * p.b.n_tiles, 1, d.n_groups);   // x = 2 * (row pair, column tile)
   if (tc_bwd_generic(d)) {
     if (d.x_share > 1)
       KV_CUDA(cudaMemset2DAsync(dX, (size_t)d.ldx * sizeof(float), 0,
@@ -2772,7 +2953,7 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
       if (ctas >= 74 * 8) { p.tpc = t; break; }
     }
   }
-  grid = dim3(2, n_pairs * ((p.b.n_tiles + p.tpc - 1) / p.tpc), d.n_groups);
+  grid = dim3(2 * n_pairs * ((p.b.n_tiles + p.tpc - 1) / p.tpc), 1, d.n_groups);
   tc::effkan8_bwd_input_kernel<<<grid, tc::NTHREADS, tc::BI_SMEM_E8, st>>>(p);
   KV_CHECK_LAUNCH("effkan8_bwd_input_kernel");
   return KV_OK;
@@ -2848,8 +3029,8 @@ int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, 
   p.rows_per_split = (ceil_div(d.T, best) + 63) / 64 * 64;
   p.tsplits = ceil_div(d.T, p.rows_per_split);  // rounding to whole 64-row stages may empty the last splits
   best = p.tsplits;
-  if ((long long)p.n_kpairs * p.gm.n_tiles > 65535 || (long long)d.n_groups * best > 65535) return KV_ERR_BAD_SHAPE;
-  dim3 grid(2, p.n_kpairs * p.gm.n_tiles, d.n_groups * best);
+  if ((long long)p.n_kpairs * p.gm.n_tiles > 0x3fffffffLL || (long long)d.n_groups * best > 65535) return KV_ERR_BAD_SHAPE;
+  dim3 grid(2 * p.n_kpairs * p.gm.n_tiles, 1, d.n_groups * best);   // x = 2 * (K' pair, output tile)
   switch (d.family) {
     case KV_LINEAR: return launch_bwd_weight<KV_LINEAR>(p, grid, st);
     case KV_EFFKAN: return launch_bwd_weight<KV_EFFKAN>(p, grid, st);

@@ -133,6 +133,9 @@ class KANLinear(torch.nn.Module):
             self._ends = (float(t0), float(g[0, -1]))
         return self._uniform
 
+    def _uniform_flag(self) -> int:
+        return L.KV_FLAG_UNIFORM_GRID if self.grid_is_uniform() else 0
+
     def grid_ends(self):
         """(first, last) knot of feature 0, cached with grid_is_uniform()."""
         self.grid_is_uniform()
@@ -147,5 +150,9 @@ class KANLinear(torch.nn.Module):
         if not isinstance(self.base_activation, torch.nn.SiLU):
             raise L.KanVitError("the fused kernel implements base_activation=SiLU only")
         shape = x.shape[:-1] + (self.out_features,)
+        # a layer called on its own gets the closed-form uniform-grid prologue too (the model classes build their specs
+        # through _dispatch.make_spec, which installs the same per-call flag); bound here so that copies of the module
+        # look at their own grid
+        self._spec.dyn_flags = self._uniform_flag
         y = kan_apply(x.reshape(-1, self.in_features), self._spec, [self._slots()])
         return y.reshape(shape)
