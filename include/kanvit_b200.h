@@ -122,6 +122,21 @@ int kv_kan_fparam_count(const kv_kan_desc_t* d);
 int kv_kan_pack(const kv_kan_desc_t* d, const uint64_t* ptr_table, float* wp_f32,
                 void* wtiles_bf16, void* wtiles_t_bf16, float* fparams, float* bias, void* stream);
 
+/* kv_kan_pack + kv_kan_fwd (exact fp32 kernels) of one layer in ONE call that allocates nothing.
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch that
+ * kv_kan_pack otherwise writes into caller-allocated buffers (packed weights [g][out][in*M], prologue parameters
+ * [g][fparam_stride], bias [g][out], each rounded up to 64 floats) lives in a file-scope device array of
+ * KV_NOALLOC_SCRATCH_FLOATS floats (4 MiB) that every GPU loading the library holds until the process exits.
+ * A layer that needs more returns KV_ERR_BAD_SHAPE (nothing launched; kv_last_cuda_error() names both sizes);
+ * KV_FLAG_BF16_TC returns KV_ERR_UNSUPPORTED.  ptr_table as for kv_kan_pack; X, mean, rstd, residual, pos, Y as
+ * for kv_kan_fwd; d->fparam_stride >= kv_kan_fparam_count(d).  Every call shares the one array and it keeps the
+ * last call's contents: each call rewrites all it reads, but calls that OVERLAP on the GPU (two streams, two
+ * host threads) race -- serialise them. */
+#define KV_NOALLOC_SCRATCH_FLOATS (1 << 20)
+int kv_kan_fwd_noalloc(const kv_kan_desc_t* d, const uint64_t* ptr_table, const float* X, const float* mean,
+                       const float* rstd, const float* residual, const float* pos, float* Y, void* stream);
+
 /* Bytes of the tensor-core operand images of kv_kan_pack (KV_FLAG_BF16_TC path).  Returns
  * KV_ERR_UNSUPPORTED when the layer cannot run on the tensor-core kernels (M > 24);
  * *wtiles_t_bytes == 0 / *dy_image_bytes == 0 mean the gradients run on the fp32 kernels for this layer. */

@@ -64,6 +64,7 @@ _SIGNATURES = {
     "kv_attn_fwd_bf16": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "kv_attn_bwd_bf16": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "kv_kan_fwd_attn_image": [_DP] + [_P] * 7 + [_I, _P],
+    "kv_kan_fwd_noalloc": [_DP] + [_P] * 8,
     "kv_kan_dy_image_geom": [_DP, C.POINTER(C.c_int), C.POINTER(C.c_int)],
     "kv_attn_image_fwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "kv_attn_image_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P],

@@ -437,6 +437,64 @@ int kv_kan_fwd(const kv_kan_desc_t* d, const float* X, const float* wp_f32, cons
   return simt_fwd(*d, X, wp_f32, fparams, bias, mean, rstd, residual, pos, Y, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------------------
+// kv_kan_fwd_noalloc: pack + exact fp32 forward of one (small) KAN layer without any device allocation.
+// The packed weights, prologue parameters and bias -- the scratch that kv_kan_pack normally writes into buffers the
+// caller allocated -- live in ONE file-scope device array.  Every GPU that loads the library holds the array until
+// the process exits; every call shares it (calls that overlap on the GPU race), and it keeps the last call's
+// contents: each call rewrites every element it reads (pack_weights / pack_fparams cover the whole packed layer,
+// bias included), so nothing has to start at zero.
+// ------------------------------------------------------------------------------
+static __device__ __align__(256) float g_noalloc_scratch[KV_NOALLOC_SCRATCH_FLOATS];
+
+// The array's name is a host-side stand-in in host code, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int noalloc_scratch_ptr(float** out) {
+  static float* ptrs[64] = {nullptr};   // per device ordinal; every writer stores the same value
+  int dev = 0;
+  KV_CUDA(cudaGetDevice(&dev), "kv_kan_fwd_noalloc: cudaGetDevice");
+  if (dev < 0 || dev >= 64) return KV_ERR_UNSUPPORTED;
+  float* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    KV_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch),
+            "kv_kan_fwd_noalloc: cudaGetSymbolAddress");
+    if (p == nullptr) return KV_ERR_CUDA;
+    __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return KV_OK;
+}
+
+int kv_kan_fwd_noalloc(const kv_kan_desc_t* d, const uint64_t* ptr_table, const float* X, const float* mean,
+                       const float* rstd, const float* residual, const float* pos, float* Y, void* stream) {
+  int rc = check_desc(d);
+  if (rc != KV_OK) return rc;
+  if (d->flags & KV_FLAG_BF16_TC) return KV_ERR_UNSUPPORTED;   // exact fp32 kernels only: no operand images
+  if (ptr_table == nullptr) return KV_ERR_BAD_ARG;
+  // scratch layout (floats, every part 256-byte aligned): wp [g][out][in*M] | fparams [g][stride] | bias [g][out]
+  auto up64 = [](size_t n) { return (n + 63) / 64 * 64; };
+  const size_t n_wp = up64((size_t)d->n_groups * d->out_features * d->in_features * d->M);
+  const size_t n_fp = fparam_count(*d) > 0 ? up64((size_t)d->n_groups * (size_t)d->fparam_stride) : 0;
+  const size_t n_bias = up64((size_t)d->n_groups * d->out_features);
+  if (fparam_count(*d) > 0 && d->fparam_stride < fparam_count(*d)) return KV_ERR_BAD_ARG;
+  if (n_wp + n_fp + n_bias > (size_t)KV_NOALLOC_SCRATCH_FLOATS) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err),
+             "kv_kan_fwd_noalloc: the packed layer needs %zu scratch floats, the static scratch holds %d "
+             "(KV_NOALLOC_SCRATCH_FLOATS); use kv_kan_pack + kv_kan_fwd with caller-allocated buffers",
+             n_wp + n_fp + n_bias, (int)KV_NOALLOC_SCRATCH_FLOATS);
+    return KV_ERR_BAD_SHAPE;
+  }
+  float* scratch = nullptr;
+  rc = noalloc_scratch_ptr(&scratch);
+  if (rc != KV_OK) return rc;
+  float* wp = scratch;
+  float* fp = n_fp ? scratch + n_wp : nullptr;
+  float* bias = scratch + n_wp + n_fp;
+  rc = kv_kan_pack(d, ptr_table, wp, nullptr, nullptr, fp, bias, stream);
+  if (rc != KV_OK) return rc;
+  return kv_kan_fwd(d, X, wp, nullptr, fp, bias, mean, rstd, residual, pos, Y, stream);
+}
+
 int kv_kan_fwd_attn_image(const kv_kan_desc_t* d, const float* X, const void* wtiles_bf16, const float* fparams,
                           const float* bias, const float* mean, const float* rstd, void* attn_image,
                           int tokens_per_sample, void* stream) {
