@@ -166,6 +166,20 @@ attn_bwd_kernel(const float* __restrict__ qkv, const float* __restrict__ dout,
   }
 }
 
+// the grouped q/k/v layout [B*N][H][3][d_h] as the tiled kernels address it: q, k, v are column offsets 0, d_h, 2 d_h
+// of head column h * 3 d_h
+static AttnTiled msa_tiled(const float* qkv, int B, int N, int H, int dh) {
+  AttnTiled a;
+  a.q = qkv; a.k = qkv + dh; a.v = qkv + 2 * dh;
+  a.ldq = a.ldk = a.ldv = 3 * H * dh;
+  a.hs = 3 * dh;
+  a.mask = nullptr;
+  a.msb = a.msh = a.msq = 0;
+  a.causal = 0;
+  a.B = B; a.H = H; a.Nq = N; a.Nk = N; a.dh = dh;
+  return a;
+}
+
 static size_t attn_fwd_smem(int N, int dh) { return sizeof(float) * ((size_t)3 * N * (dh + 1) + ATT_WARPS * N); }
 static size_t attn_bwd_smem(int N, int dh) {
   return sizeof(float) * ((size_t)4 * N * (dh + 1) + 2 * N + ATT_WARPS * 2 * N);
@@ -180,7 +194,10 @@ extern "C" int kv_attn_fwd(const float* qkv, const float* residual, float* out, 
   if (qkv == nullptr || out == nullptr || B < 0 || N <= 0 || H <= 0 || d_head <= 0) return KV_ERR_BAD_ARG;
   if (d_head > ATT_MAX_DH) return KV_ERR_BAD_SHAPE;
   const size_t smem = attn_fwd_smem(N, d_head);
-  if (smem > 227 * 1024) return KV_ERR_BAD_SHAPE;
+  if (smem > 227 * 1024) {   // the head does not fit one CTA: tiled kernels (attn_tiled.cu)
+    if (B == 0) return KV_OK;
+    return attn_tiled_fwd(msa_tiled(qkv, B, N, H, d_head), residual, out, H * d_head, d_head, lse, (cudaStream_t)stream);
+  }
   if (B == 0) return KV_OK;
   KV_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
           "attn_fwd smem");
@@ -196,7 +213,11 @@ extern "C" int kv_attn_bwd(const float* qkv, const float* dout, const float* lse
     return KV_ERR_BAD_ARG;
   if (d_head > ATT_MAX_DH) return KV_ERR_BAD_SHAPE;
   const size_t smem = attn_bwd_smem(N, d_head);
-  if (smem > 227 * 1024) return KV_ERR_BAD_SHAPE;
+  if (smem > 227 * 1024) {
+    if (B == 0) return KV_OK;
+    return attn_tiled_bwd(msa_tiled(qkv, B, N, H, d_head), nullptr, dout, H * d_head, d_head, lse, dqkv, dqkv + d_head,
+                          dqkv + 2 * d_head, (cudaStream_t)stream);
+  }
   if (B == 0) return KV_OK;
   KV_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
           "attn_bwd smem");

@@ -225,6 +225,19 @@ static AttnGeneral ag_params(const kv_attn_general_t* a, const float* q, const f
   return p;
 }
 
+static AttnTiled ag_tiled(const kv_attn_general_t* a, const float* q, const float* k, const float* v,
+                          const unsigned char* mask) {
+  AttnTiled t;
+  t.q = q; t.k = k; t.v = v;
+  t.ldq = a->ldq; t.ldk = a->ldk; t.ldv = a->ldv;
+  t.hs = a->d_head;
+  t.mask = mask;
+  t.msb = a->mask_stride_b; t.msh = a->mask_stride_h; t.msq = a->mask_stride_q;
+  t.causal = a->causal;
+  t.B = a->B; t.H = a->H; t.Nq = a->Nq; t.Nk = a->Nk; t.dh = a->d_head;
+  return t;
+}
+
 }  // namespace kv
 
 using namespace kv;
@@ -234,9 +247,10 @@ extern "C" int kv_attn_general_fwd(const kv_attn_general_t* a, const float* q, c
   const int rc = ag_check(a);
   if (rc != KV_OK) return rc;
   const size_t smem = ag_fwd_smem(a->Nk, a->d_head);
-  if (smem > 227 * 1024) return KV_ERR_BAD_SHAPE;
   if (a->B == 0) return KV_OK;
   if (!q || !k || !v || !out || !lse) return KV_ERR_BAD_ARG;
+  if (smem > 227 * 1024)   // K / V do not fit one CTA: tiled kernels (attn_tiled.cu)
+    return attn_tiled_fwd(ag_tiled(a, q, k, v, mask), nullptr, out, a->ldo, a->d_head, lse, (cudaStream_t)stream);
   KV_CUDA(cudaFuncSetAttribute(attn_general_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
           "attn_general_fwd smem");
   attn_general_fwd_kernel<<<a->B * a->H, AG_THREADS, smem, (cudaStream_t)stream>>>(ag_params(a, q, k, v, mask), out,
@@ -251,9 +265,11 @@ extern "C" int kv_attn_general_bwd(const kv_attn_general_t* a, const float* q, c
   const int rc = ag_check(a);
   if (rc != KV_OK) return rc;
   const size_t smem = ag_bwd_smem(a->Nq, a->Nk, a->d_head);
-  if (smem > 227 * 1024) return KV_ERR_BAD_SHAPE;
   if (a->B == 0) return KV_OK;
   if (!q || !k || !v || !out || !dout || !lse || !dq || !dk || !dv) return KV_ERR_BAD_ARG;
+  if (smem > 227 * 1024)
+    return attn_tiled_bwd(ag_tiled(a, q, k, v, mask), out, dout, a->ldo, a->d_head, lse, dq, dk, dv,
+                          (cudaStream_t)stream);
   KV_CUDA(cudaFuncSetAttribute(attn_general_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
           "attn_general_bwd smem");
   attn_general_bwd_kernel<<<a->B * a->H, AG_THREADS, smem, (cudaStream_t)stream>>>(

@@ -39,6 +39,22 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
 int tc_bwd_weight(const kv_kan_desc_t& d, const float* X, const void* dy_image, const float* fparams,
                   const float* mean, const float* rstd, float* dWp, cudaStream_t st);
 
+// attn_tiled.cu -- exact fp32 attention for sequences that do not fit one CTA's shared memory (fallback of attn.cu and
+// attn_general.cu).  Head h of sample b = rows [b*N, (b+1)*N), columns [h*hs, h*hs + dh) of a matrix with row stride ld.
+struct AttnTiled {
+  const float *q, *k, *v;
+  int ldq, ldk, ldv, hs;
+  const unsigned char* mask;  // nullable; element (b, h, i, j) at b*msb + h*msh + i*msq + j (0 stride = broadcast)
+  long long msb, msh, msq;
+  int causal;
+  int B, H, Nq, Nk, dh;
+};
+int attn_tiled_fwd(const AttnTiled& a, const float* residual, float* out, int ldo, int hso, float* lse,
+                   cudaStream_t st);
+// o == nullptr: D_i is recomputed (MSA entry point); dq / dk / dv use the layouts of q / k / v
+int attn_tiled_bwd(const AttnTiled& a, const float* o, const float* dout, int ldo, int hso, const float* lse,
+                   float* dq, float* dk, float* dv, cudaStream_t st);
+
 // parameter pointer table of kv_kan_pack
 __device__ __forceinline__ const float* slot(const uint64_t* tbl, int g, int s) {
   return reinterpret_cast<const float*>(tbl[(size_t)g * KV_PTRS_PER_GROUP + s]);
