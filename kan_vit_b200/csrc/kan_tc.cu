@@ -441,6 +441,42 @@ struct StrideSink {  // per-feature scattered bf16 stores (generic Cox-de Boor p
   }
 };
 
+// effkan on a grid other than the default one: the non-zero splines of the 8 features of an octet (once per chunk) ...
+struct EffkanOctet {
+  float N[8][KV_MAX_SPLINE_ORDER + 1];
+  int jb[8];   // index of the first non-zero basis (span - k); far negative when x lies outside [t_0, t_last)
+};
+__device__ __forceinline__ void effkan_octet_basis(const BasisCtx& c, int i0, const float (&x)[8], EffkanOctet& e) {
+#pragma unroll
+  for (int q = 0; q < 8; ++q) effkan_local_basis(c, i0 + q, x[q], e.N[q], e.jb[q]);
+}
+// ... and the rows m0 <= m < m0 + Mt of its operand image (row m = 8 features x basis m = 16 bytes, at dst + (m - m0) *
+// stride): M 16-byte stores of zeros, then the (k + 1) values of each feature as 2-byte stores into the rows of its
+// span's window (same thread, same addresses: program order), then the SiLU row.  ~50 stores per octet and part instead
+// of a select chain per (basis, feature): the producers of grid 10 / 20 layers were issue-bound on those chains.
+__device__ __forceinline__ void effkan_scatter_part(uint8_t* dst, int stride, int m0, int Mt, const BasisCtx& c, int i0,
+                                                    const float (&x)[8], const EffkanOctet& e) {
+  const int nb = c.G + c.k;
+  const int mlo = max(m0, 0), mhi = min(nb, m0 + Mt);
+  for (int m = mlo; m < mhi; ++m) sts128(dst + (m - m0) * stride, 0u, 0u, 0u, 0u);
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+#pragma unroll
+    for (int r = 0; r <= KV_MAX_SPLINE_ORDER; ++r) {
+      const int m = e.jb[q] + r;
+      if (r <= c.k && m >= mlo && m < mhi)
+        *reinterpret_cast<__nv_bfloat16*>(dst + (m - m0) * stride + q * 2) = __float2bfloat16_rn(e.N[q][r]);
+    }
+  }
+  if (nb >= m0 && nb < m0 + Mt) {
+    float v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = (i0 + q < c.in) ? fast_silu(x[q]) : 0.0f;
+    sts128(dst + (nb - m0) * stride, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+           pack_bf16(v[6], v[7]));
+  }
+}
+
 template <int F>
 __device__ __forceinline__ void basis_octet(uint8_t* dst, int stride, int m0, int Mt, const float (&x)[8],
                                             const BasisCtx& c, int i0, float mu, float rs) {
@@ -456,30 +492,11 @@ __device__ __forceinline__ void basis_octet(uint8_t* dst, int stride, int m0, in
     // At most k + 1 bases are non-zero at x: those of the knot span j that holds it.  Per feature: find the span (a
     // guess from the grid ends, corrected by a short walk), load the 2k knots around it and run the triangular
     // de Boor scheme (k (k + 1) / 2 divisions) -- every term the reference's full recursion forms for a non-zero
-    // basis, none of the zero ones.  Then one 16-byte row per basis index: for feature q the value is N[q][m - jb[q]]
-    // inside the span's window and 0 elsewhere.
-    constexpr int KMAX = KV_MAX_SPLINE_ORDER;
-    const int k = c.k, nb = c.G + c.k;
-    float N[8][KMAX + 1];
-    int jb[8];   // index of the first non-zero basis (j - k); far negative when x lies outside [t_0, t_last)
-#pragma unroll
-    for (int q = 0; q < 8; ++q) effkan_local_basis(c, i0 + q, x[q], N[q], jb[q]);
-    for (int m = max(m0, 0); m < min(nb, m0 + Mt); ++m) {
-#pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        const int r = m - jb[q];
-        float val = 0.0f;
-#pragma unroll
-        for (int rr = 0; rr <= KMAX; ++rr) val = (r == rr) ? N[q][rr] : val;
-        v[q] = val;
-      }
-      emit(m);
-    }
-    if (nb >= m0 && nb < m0 + Mt) {
-#pragma unroll
-      for (int q = 0; q < 8; ++q) v[q] = (i0 + q < c.in) ? fast_silu(x[q]) : 0.0f;
-      emit(nb);
-    }
+    // basis, none of the zero ones.  The rows of the part are then written as zeros (one 16-byte store per basis index)
+    // and the k + 1 values of each feature scattered over them (effkan_scatter_part).
+    EffkanOctet e;
+    effkan_octet_basis(c, i0, x, e);
+    effkan_scatter_part(dst, stride, m0, Mt, c, i0, x, e);
     return;
   }
   if (F == KV_LINEAR) {
@@ -939,6 +956,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       int slot_i = 0;
       linear_produce_tile(gm, xrow, mrow, row_ok, vec, mvec, in, wg, sA + row_off, bar0, NCH, lane, slot_i);
     } else {
+    // two copies of the chunk loop (default-grid closed form / everything else): the registers of the other-grid
+    // route (EffkanOctet: 40 values per thread) must not push spills into the default route
+    auto run_chunks = [&](auto e8_tag) {
+    constexpr bool E8 = decltype(e8_tag)::value;
     float cur[FPT];
     load_xf(xrow, vec, wg * FPT, cur);
     gate(wg * FPT, cur);
@@ -952,6 +973,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         for (int q = 0; q < FPT; ++q) nxt[q] = 0.0f;
       }
       const int i0 = ch * KU + wg * FPT;
+      // effkan on a non-default grid: the non-zero splines of the thread's 8 features, once per chunk (all parts)
+      EffkanOctet eo;
+      if constexpr (F == KV_EFFKAN && FPT == 8 && !E8) {
+        if (!(d.reserved & 8)) effkan_octet_basis(c, i0, cur, eo);
+      }
       for (int pt = 0; pt < gm.npart; ++pt) {      // one ring slot per part: bases [m0, m0 + Mt) of the chunk
       const int slot_i = ch * gm.npart + pt;
       const int sc = slot_i % NCH;
@@ -962,13 +988,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       if (d.reserved & 8) {              // timing experiments: no basis evaluation
       } else
       if constexpr (F == KV_EFFKAN) {
-        if (layout == LAYOUT_EFFKAN8) {            // M = 9: one part
+        if constexpr (E8) {                         // default grid, M = 9: one part
           if constexpr (FPT == 8) effkan8_chunk(base, wg, cur, gt0, ginv_h);
           else effkan8_chunk4(base, wg, cur, gt0, ginv_h);
         } else {
-          // arbitrary knots: span search + local de Boor per feature, 16-byte rows (basis_octet)
+          // any other grid: zero rows + the k + 1 values of each feature scattered (effkan_scatter_part)
           if constexpr (FPT == 8) {
-            basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, m0, Mt, cur, c, i0, mu, rs);
+            effkan_scatter_part(base + wg * 2048, A_UNIT_BYTES, m0, Mt, c, i0, cur, eo);
           } else {
 #pragma unroll 1
             for (int q = 0; q < FPT; ++q) {   // feature f = wg*FPT + q of the chunk sits in k-half f / 8 at element f % 8
@@ -993,6 +1019,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       }
 #pragma unroll
       for (int q = 0; q < FPT; ++q) cur[q] = nxt[q];
+    }
+    };
+    if (F == KV_EFFKAN && layout == LAYOUT_EFFKAN8) {
+      if constexpr (F == KV_EFFKAN) run_chunks(std::true_type{});
+    } else {
+      run_chunks(std::false_type{});
     }
     }
     // ================= epilogue: TMEM -> registers -> smem transpose -> coalesced global stores =========
@@ -1071,13 +1103,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       }
     } else
     for (int cb = half; cb * 32 < BN; cb += NPW / 4) {
+      const int sidx = 60 - (cb - half) / (NPW / 4);     // timing experiments: the first two column blocks of warp 2
+      const bool st_on = ptid == 0 && sidx >= 59;
+      if (st_on) stamp(2, sidx, 0);
       uint32_t rr[32];
       ptx::tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + cb * 32, rr);
       ptx::tmem_ld_wait();
+      if (st_on) stamp(2, sidx, 1);
 #pragma unroll
       for (int k = 0; k < 8; ++k)
         *reinterpret_cast<uint4*>(stg + lane * LDT + 4 * k) = make_uint4(rr[4 * k], rr[4 * k + 1], rr[4 * k + 2], rr[4 * k + 3]);
       __syncwarp();
+      if (st_on) stamp(2, sidx, 2);
       const int cl = cb * 32 + c4;           // column inside the tile
       const int o = n_tile * BN + cl;        // output feature of the group
       const int col = colbase + cl;          // column of Y
@@ -1119,6 +1156,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
         }
       }
       __syncwarp();
+      if (st_on) stamp(2, sidx, 3);
     }
     ptx::tc_fence_before();
     if (ptid == 0) stamp(2, 62, 3);
@@ -1445,6 +1483,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
               for (int q = 0; q < 8; ++q) nxt[q] = 0.0f;
             }
             const int i0 = ch * KU + wg * 8;
+            EffkanOctet eo;    // effkan on a non-default grid: once per chunk
+            if constexpr (!FAST && F == KV_EFFKAN) effkan_octet_basis(c, i0, cur, eo);
             for (int pt = 0; pt < gm.npart; ++pt, ++slot_i) {   // one ring slot per part: bases [m0, m0 + Mt) of the chunk
               const int sc = slot_i % NCH;
               const int m0 = pt * Mp, Mt = min(Mp, M - m0);
@@ -1453,8 +1493,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
               if constexpr (FAST) {
                 effkan8_chunk(base, wg, cur, gt0, ginv_h);   // M = 9: one part
               } else {
-                // every other family; effkan on arbitrary knots: span search + local de Boor, 16-byte rows
-                basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, m0, Mt, cur, c, i0, mu, rs);
+                if constexpr (F == KV_EFFKAN) effkan_scatter_part(base + wg * 2048, A_UNIT_BYTES, m0, Mt, c, i0, cur, eo);
+                else basis_octet<F>(base + wg * 2048, A_UNIT_BYTES, m0, Mt, cur, c, i0, mu, rs);
               }
               ptx::fence_proxy_async_smem();
               __syncwarp();
@@ -2498,18 +2538,53 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
       const bool ln = (F == KV_FASTKAN) && !(d.flags & KV_FLAG_NO_LAYERNORM);
       int s = 0;
       uint32_t ph = 1;
-      for (int st = 0; st < n_stages; ++st) {
+      // A tile with fewer octets than thread parts (M >= 5: 3, 2 or 1 octets for 4 parts) splits the BASES of an octet
+      // over npo parts instead of leaving parts idle: part fb owns octet fb % no and the bases [ms, me) of the tile's
+      // range (the families' routines emit only the rows of the range they are given).  Such a thread has exactly one
+      // octet per stage, whose X values are loaded one stage ahead.
+      const int npo = p.no < NFB ? NFB / p.no : 1;
+      const bool one_octet = p.no <= NFB;
+      const int my_oq = npo > 1 ? fb % p.no : fb;
+      const int sub = npo > 1 ? fb / p.no : 0;
+      const int per = (g_Mt + npo - 1) / npo;
+      const int ms = g_m0 + sub * per, me = min(g_m0 + g_Mt, ms + per);
+      const bool part_live = tile_live && my_oq < p.no && sub < npo && ms < me;
+      auto rows_of = [&](int st, bool& row_ok) {
         const int t = row0 + st * 64 + tl;
-        const bool row_ok = t < row1;
-        const float* xrow = p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
+        row_ok = t < row1;
+        return p.X + (size_t)(row_ok ? t : 0) * d.ldx + xoff;
+      };
+      float xcur[8], xnxt[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) xcur[q] = xnxt[q] = 0.0f;
+      if (one_octet && part_live && n_stages > 0) {
+        bool ok;
+        const float* xr = rows_of(0, ok);
+        load_x8(xr, (g_oc0 + my_oq) * 8, in, ok && (g_oc0 + my_oq) * 8 < in, vec, xcur);
+      }
+      for (int st = 0; st < n_stages; ++st) {
+        bool row_ok;
+        const float* xrow = rows_of(st, row_ok);
+        const int t = row0 + st * 64 + tl;
         float mu = 0.f, rs = 1.f;
         if (ln && row_ok) {
           mu = p.mean[(size_t)t * n_slices + slice];
           rs = p.rstd[(size_t)t * n_slices + slice];
         }
+        if (one_octet && part_live && st + 1 < n_stages) {
+          bool ok;
+          const float* xr = rows_of(st + 1, ok);
+          load_x8(xr, (g_oc0 + my_oq) * 8, in, ok && (g_oc0 + my_oq) * 8 < in, vec, xnxt);
+        }
         ptx::mbar_wait(emptyA(s), ph);
         uint8_t* base = sA + s * BW_A_STAGE + row_off;
-        if (tile_live) {
+        if (one_octet) {
+          if (part_live && !(d.reserved & 8))   // (bit 8, timing experiments: no basis evaluation)
+            basis_octet<F>(base + my_oq * g_Mt * 128 + (ms - g_m0) * 128, 128, ms, me - ms, xcur, c, (g_oc0 + my_oq) * 8,
+                           mu, rs);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) xcur[q] = xnxt[q];
+        } else if (tile_live) {
           for (int oq = fb; oq < p.no; oq += NFB) {
             const int i0 = (g_oc0 + oq) * 8;
             float x8[8];

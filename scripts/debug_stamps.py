@@ -21,6 +21,9 @@ for rank in range(2):
     print("CTA rank", rank, "roles: 0=mma(stage: before fullB wait, after, before fullA wait (part start), -) 1=loader(u: emptyB ok, issued) 2=producer(chunk: emptyA ok, arrived) 3=relay(u: fullB, arrived)")
     print("tile: after set-up sync", f(d[2, 61, 1]), "producers start", f(d[2, 62, 0]), "producers done", f(d[2, 62, 1]),
           "accumulator complete", f(d[2, 62, 2]), "epilogue done (warp 2)", f(d[2, 62, 3]), "all warps done", f(d[2, 61, 2]))
+    for blk in (60, 59):
+        print("  epilogue column block", 60 - blk, "of warp 2: before tcgen05.ld", f(d[2, blk, 0]), "loaded", f(d[2, blk, 1]),
+              "staged in smem", f(d[2, blk, 2]), "stores issued", f(d[2, blk, 3]))
     if os.environ.get("KV_STAMPS_SHORT"):
         continue
     for u in list(range(0, 64)):
