@@ -375,58 +375,57 @@ __device__ __forceinline__ void effkan8_chunk4(uint8_t* base, int qg, const floa
       make_uint2(pack_bf16(sv[0], sv[1]), pack_bf16(sv[2], sv[3]));
 }
 
-// The k + 1 B-splines that are non-zero at x for feature i: N[r] = B_{jb + r, k}(x), jb = j - k for the knot span j that
-// holds x (far negative, N = 0, when x lies outside [t_0, t_last) or i is beyond the layer's features).
-//   c.uniform: one uniform knot vector t0 + j h (any grid_size) -- span and triangle in units of h, no knot loads;
-//   otherwise: span search on the feature's own knots (a guess from the grid ends, corrected by a short walk), the 2k
-//   knots around the span, and the triangular de Boor scheme with k (k + 1) / 2 divisions -- every term the
-//   reference's full recursion (models/effkan.py:99-132) forms for a non-zero basis, none of the zero ones.
-__device__ __forceinline__ void effkan_local_basis(const BasisCtx& c, int i, float xv, float (&N)[KV_MAX_SPLINE_ORDER + 1],
-                                                   int& jb) {
-  constexpr int KMAX = KV_MAX_SPLINE_ORDER;
-  const int k = c.k, nk = c.G + 2 * c.k + 1;
-#pragma unroll
-  for (int r = 0; r <= KMAX; ++r) N[r] = 0.0f;
+// Cubic splines (spline_order 3, the only order the reference's models build): the 4 B-splines that are non-zero at x
+// for feature i, N[r] = B_{jb + r, 3}(x), jb = j - 3 for the knot span j that holds x (far negative, N = 0, when x lies
+// outside [t_0, t_last) or i is beyond the layer's features).
+//   c.uniform: one uniform knot vector t0 + j h (any grid_size) -- the four cubic pieces in closed form, no knot loads,
+//   no divisions;
+//   otherwise: span search on the feature's own knots (a guess from the grid ends, corrected by a short walk), the 6
+//   knots around the span and the triangular de Boor scheme (6 divisions) -- every term the reference's full recursion
+//   (models/effkan.py:99-132) forms for a non-zero basis, none of the zero ones.
+// (An earlier version unrolled the triangle up to KV_MAX_SPLINE_ORDER = 7 with run-time order checks: ~560 instructions
+// per feature, a producer loop that no longer fitted the instruction cache -- 22 % of the stall samples were no_inst.)
+__device__ __forceinline__ void effkan_local_basis3(const BasisCtx& c, int i, float xv, float (&N)[4], int& jb) {
+  const int nk = c.G + 7;
+  N[0] = N[1] = N[2] = N[3] = 0.0f;
   jb = -(1 << 20);
   if (i >= c.in) return;
-  float left[KMAX + 1], right[KMAX + 1];
-  int j;
   if (c.uniform) {
     const float sx = (xv - c.t0) * c.inv_h;
     if (!(sx >= 0.0f) || !(sx < (float)(nk - 1))) return;
-    j = min((int)sx, nk - 2);
+    const int j = min((int)sx, nk - 2);
     const float u = sx - (float)j;
+    const float s2 = u * u, s3 = s2 * u, om = 1.0f - u;
+    N[0] = om * om * om * (1.0f / 6.0f);
+    N[1] = fmaf(0.5f, s3, fmaf(-1.0f, s2, 2.0f / 3.0f));
+    N[2] = fmaf(-0.5f, s3, fmaf(0.5f, s2, fmaf(0.5f, u, 1.0f / 6.0f)));
+    N[3] = s3 * (1.0f / 6.0f);
+    jb = j - 3;
+    return;
+  }
+  const float* t = c.fp + (size_t)i * nk;
+  const int j = bspline_find_span(t, nk, xv);
+  if (j < 0) return;
+  float left[4], right[4];
 #pragma unroll
-    for (int pp = 1; pp <= KMAX; ++pp) {
-      left[pp] = u + (float)(pp - 1);
-      right[pp] = (float)pp - u;
-    }
-  } else {
-    const float* t = c.fp + (size_t)i * nk;
-    j = bspline_find_span(t, nk, xv);
-    if (j < 0) return;
-#pragma unroll
-    for (int pp = 1; pp <= KMAX; ++pp) {
-      left[pp] = xv - t[max(j + 1 - pp, 0)];
-      right[pp] = t[min(j + pp, nk - 1)] - xv;
-    }
+  for (int pp = 1; pp <= 3; ++pp) {
+    left[pp] = xv - t[max(j + 1 - pp, 0)];
+    right[pp] = t[min(j + pp, nk - 1)] - xv;
   }
   N[0] = 1.0f;
 #pragma unroll
-  for (int pp = 1; pp <= KMAX; ++pp) {
-    if (pp <= k) {
-      float saved = 0.0f;
+  for (int pp = 1; pp <= 3; ++pp) {
+    float saved = 0.0f;
 #pragma unroll
-      for (int r = 0; r < pp; ++r) {
-        const float den = right[r + 1] + left[pp - r];      // uniform: exactly pp
-        const float temp = den != 0.0f ? __fdividef(N[r], den) : 0.0f;
-        N[r] = saved + right[r + 1] * temp;
-        saved = left[pp - r] * temp;
-      }
-      N[pp] = saved;
+    for (int r = 0; r < pp; ++r) {
+      const float den = right[r + 1] + left[pp - r];
+      const float temp = den != 0.0f ? __fdividef(N[r], den) : 0.0f;
+      N[r] = saved + right[r + 1] * temp;
+      saved = left[pp - r] * temp;
     }
+    N[pp] = saved;
   }
-  jb = j - k;
+  jb = j - 3;
 }
 
 // Basis-major layout, basis index outermost: 8 features x one m = one 16-byte store.
@@ -443,28 +442,42 @@ struct StrideSink {  // per-feature scattered bf16 stores (generic Cox-de Boor p
 
 // effkan on a grid other than the default one: the non-zero splines of the 8 features of an octet (once per chunk) ...
 struct EffkanOctet {
-  float N[8][KV_MAX_SPLINE_ORDER + 1];
-  int jb[8];   // index of the first non-zero basis (span - k); far negative when x lies outside [t_0, t_last)
+  float N[8][4];
+  int jb[8];   // index of the first non-zero basis (span - 3); far negative when x lies outside [t_0, t_last)
 };
 __device__ __forceinline__ void effkan_octet_basis(const BasisCtx& c, int i0, const float (&x)[8], EffkanOctet& e) {
+  if (c.k != 3) return;   // other orders: effkan_scatter_part takes the per-feature Cox-de Boor route
 #pragma unroll
-  for (int q = 0; q < 8; ++q) effkan_local_basis(c, i0 + q, x[q], e.N[q], e.jb[q]);
+  for (int q = 0; q < 8; ++q) effkan_local_basis3(c, i0 + q, x[q], e.N[q], e.jb[q]);
 }
 // ... and the rows m0 <= m < m0 + Mt of its operand image (row m = 8 features x basis m = 16 bytes, at dst + (m - m0) *
-// stride): M 16-byte stores of zeros, then the (k + 1) values of each feature as 2-byte stores into the rows of its
-// span's window (same thread, same addresses: program order), then the SiLU row.  ~50 stores per octet and part instead
-// of a select chain per (basis, feature): the producers of grid 10 / 20 layers were issue-bound on those chains.
+// stride): M 16-byte stores of zeros, then the 4 values of each feature as 2-byte stores into the rows of its span's
+// window (same thread, same addresses: program order), then the SiLU row.  ~50 stores per octet and part instead of a
+// select chain per (basis, feature): the producers of grid 10 / 20 layers were issue-bound on those chains.
 __device__ __forceinline__ void effkan_scatter_part(uint8_t* dst, int stride, int m0, int Mt, const BasisCtx& c, int i0,
                                                     const float (&x)[8], const EffkanOctet& e) {
   const int nb = c.G + c.k;
+  if (c.k != 3) {
+    // any other spline order: the full recursion per feature, dense 2-byte stores (slow, never built by the reference)
+#pragma unroll 1
+    for (int q = 0; q < 8; ++q) {
+      StrideSink sink{dst + q * 2, stride, m0, Mt};
+      if (i0 + q < c.in) {
+        basis_eval<KV_EFFKAN>(c, i0 + q, x[q], x[q], sink);
+      } else {
+        for (int m = m0; m < m0 + Mt; ++m) sink.put(m, 0.0f);
+      }
+    }
+    return;
+  }
   const int mlo = max(m0, 0), mhi = min(nb, m0 + Mt);
   for (int m = mlo; m < mhi; ++m) sts128(dst + (m - m0) * stride, 0u, 0u, 0u, 0u);
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
 #pragma unroll
-    for (int r = 0; r <= KV_MAX_SPLINE_ORDER; ++r) {
+    for (int r = 0; r < 4; ++r) {
       const int m = e.jb[q] + r;
-      if (r <= c.k && m >= mlo && m < mhi)
+      if (m >= mlo && m < mhi)
         *reinterpret_cast<__nv_bfloat16*>(dst + (m - m0) * stride + q * 2) = __float2bfloat16_rn(e.N[q][r]);
     }
   }
