@@ -232,7 +232,8 @@ int kv_kan_unpack_grads(const kv_kan_desc_t* d, const float* dWp, const float* d
  * online-softmax / log-sum-exp bookkeeping of utils.py:137-227.
  * qkv: [B*N][H][3][d_h] (the grouped layer's output), out: [B*N][H*d_h] (heads
  * concatenated in order, attention.py:201), residual nullable (model.py:34),
- * lse: [B][H][N] saved for the backward. */
+ * lse: [B][H][N] saved for the backward.  Any N: a head that does not fit one CTA's shared memory
+ * (N > ~280 forward, ~215 backward at d_h 64) runs on the tiled kernels of attn_tiled.cu; d_h <= 128. */
 int kv_attn_fwd(const float* qkv, const float* residual, float* out, float* lse,
                 int B, int N, int H, int d_head, void* stream);
 
@@ -264,8 +265,9 @@ int kv_attn_bwd_bf16(const float* qkv, const float* dout, const float* lse, floa
  * exponential and the row sum is clamped at 1e-10, so fully hidden rows behave as in the reference.
  * lse [B][H][Nq] and out are saved for the backward (D_i = sum(dO_i * O_i), utils.py:277).
  * The q/k bucket sizes of the reference only change the summation order and have no counterpart.
- * KV_ERR_BAD_SHAPE when a head does not fit in shared memory (roughly Nk <= 400 forward,
- * Nq + Nk <= 430 backward at d_head 64). */
+ * Any Nq / Nk: heads that fit one CTA's shared memory (roughly Nk <= 400 forward, Nq + Nk <= 430 backward at
+ * d_head 64) run resident, longer ones on the tiled kernels of attn_tiled.cu (same arithmetic, keys / queries
+ * streamed in tiles of 64).  KV_ERR_BAD_SHAPE only for d_head > 128. */
 typedef struct kv_attn_general {
   int32_t B, H, Nq, Nk, d_head;
   int32_t ldq, ldk, ldv, ldo;
