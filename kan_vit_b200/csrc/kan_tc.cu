@@ -2271,6 +2271,26 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
 #pragma unroll
         for (int f = 0; f < 8; ++f) scratch[(m - mlo) * MS + f * 256 + etid] = __uint_as_float(r8[f]);
       }
+      if (F == KV_SINE) {
+        // basis outermost: d freq_q (models/sinekan.py:87) is summed over the thread's 8 features before the warp
+        // reduction -- one shuffle tree and one shared-memory atomic per basis instead of one per (feature, basis)
+        const float* freq = c.fp;
+        const int i0s = cch * KU + half * 8;
+        for (int q = mlo; q < min(mhi, c.G); ++q) {
+          const float fr = freq[q];
+          float contrib = 0.0f;
+#pragma unroll
+          for (int f = 0; f < 8; ++f) {
+            const int ic = min(i0s + f, in - 1);
+            const float cs = cosf(fmaf(x8[f], fr, c.fp[c.G + (size_t)ic * c.G + q]));
+            const float sv = scratch[(q - mlo) * MS + f * 256 + etid];
+            dx[f] = fmaf(fr * cs, sv, dx[f]);
+            if (row_ok && i0s + f < in) contrib = fmaf(x8[f] * cs, sv, contrib);
+          }
+          contrib = warp_sum(contrib);
+          if (lane == 0) atomicAdd(&dfreq_s[q], contrib);
+        }
+      } else
 #pragma unroll
       for (int f = 0; f < 8; ++f) {
         const int i = cch * KU + half * 8 + f;
@@ -2279,18 +2299,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
         const float xv = x8[f];
         const float* srow = scratch + f * 256 + etid;
         float acc = 0.0f;
-        if (F == KV_SINE) {
-          const float* freq = c.fp;
-          const float* ph = c.fp + c.G + (size_t)ic * c.G;
-          for (int q = mlo; q < min(mhi, c.G); ++q) {
-            const float cs = cosf(fmaf(xv, freq[q], ph[q]));
-            const float sv = srow[(q - mlo) * MS];
-            acc = fmaf(freq[q] * cs, sv, acc);
-            float contrib = live ? xv * cs * sv : 0.0f;  // d freq_q (models/sinekan.py:87), reduced over the CTA
-            contrib = warp_sum(contrib);
-            if (lane == 0) atomicAdd(&dfreq_s[q], contrib);
-          }
-        } else if (F == KV_FASTKAN) {
+        (void)live;
+        if (F == KV_FASTKAN) {
           const float xn = fastkan_xn(c, ic, xv, mu, rs);
           StridedFastkanDotSink sk{srow, MS, c.G, mlo, mhi, 0.0f, 0.0f};
           basis_deriv<F>(c, ic, xv, xn, sk);
