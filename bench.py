@@ -36,7 +36,7 @@ CONFIGS = {
     "cfg3_fast": ((3, 32, 32), 4, 6, 192, 8, 10, "fast", False, 1024, 32),
     "cfg3_sine": ((3, 32, 32), 4, 6, 192, 8, 10, "sine", False, 1024, 32),
     "cfg4": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", True, 336, 4),
-    "cfg4_faithful": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", False, 64, 2),
+    "cfg4_faithful": ((3, 224, 224), 14, 12, 768, 12, 10, "efficientkan", False, 336, 2),
 }
 DEFAULT_PRECISION = {"cfg1": "fp32", "cfg2": "fp32", "cfg3_fast": "bf16", "cfg3_sine": "bf16", "cfg4": "bf16",
                      "cfg4_faithful": "bf16"}
