@@ -637,19 +637,46 @@ def run_layer_arm(args):
     def resident_step(i):
         fwd_bwd(dev_x[i % n_host], dev_dy[i % n_host])
 
-    stage_x = torch.empty_like(dev_x[0]).requires_grad_()
-    stage_dy = torch.empty_like(dev_dy[0])
-    host_y = torch.empty(T, LAYER_SHAPES[-1][1]).pin_memory()
-    host_dx = torch.empty(T, LAYER_SHAPES[0][0]).pin_memory()
+    # end-to-end leg: rows and output gradient come from pinned host memory, the layer output and the input gradient go
+    # back to pinned host memory, EVERY step, inside the timed region.  Copies run on two side streams against two
+    # device slots (step i + 1's input lands while step i computes, step i's results leave while step i + 1 computes),
+    # event-ordered, no host synchronisation; the last step's results are waited for before the closing event.
+    main = torch.cuda.current_stream()
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    slot_x = [torch.empty_like(dev_x[0]).requires_grad_() for _ in range(2)]
+    slot_dy = [torch.empty_like(dev_dy[0]) for _ in range(2)]
+    ev_in = [torch.cuda.Event() for _ in range(2)]      # slot k holds its input
+    ev_used = [torch.cuda.Event() for _ in range(2)]    # the step that read slot k has been issued and finished
+    host_y = [torch.empty(T, LAYER_SHAPES[-1][1]).pin_memory() for _ in range(2)]
+    host_dx = [torch.empty(T, LAYER_SHAPES[0][0]).pin_memory() for _ in range(2)]
+
+    def submit(i):
+        k = i % 2
+        with torch.cuda.stream(s_in), torch.no_grad():
+            if i >= 2:
+                s_in.wait_event(ev_used[k])
+            slot_x[k].copy_(host_x[i % n_host], non_blocking=True)
+            slot_dy[k].copy_(host_dy[i % n_host], non_blocking=True)
+            ev_in[k].record(s_in)
 
     def e2e_step(i):
-        # host rows in (x and dy from pinned memory), the layer output and the input gradient back out to the host
-        with torch.no_grad():
-            stage_x.copy_(host_x[i % n_host], non_blocking=True)
-            stage_dy.copy_(host_dy[i % n_host], non_blocking=True)
-        y = fwd_bwd(stage_x, stage_dy)
-        host_y.copy_(y.detach(), non_blocking=True)
-        host_dx.copy_(stage_x.grad, non_blocking=True)
+        k = i % 2
+        if i == 0:
+            submit(0)
+        if i + 1 < args.steps:
+            submit(i + 1)
+        main.wait_event(ev_in[k])
+        y = fwd_bwd(slot_x[k], slot_dy[k])
+        dx = slot_x[k].grad
+        ev_used[k].record(main)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(ev_used[k])
+            host_y[k].copy_(y.detach(), non_blocking=True)
+            host_dx[k].copy_(dx, non_blocking=True)
+            y.record_stream(s_out)
+            dx.record_stream(s_out)
+        if i + 1 == args.steps:
+            main.wait_stream(s_out)      # the closing event sees the last results on the host
 
     def barrier():
         if world > 1:
@@ -708,7 +735,7 @@ def run_layer_arm(args):
     if rank == 0:
         ms_step = ms_total / args.steps
         h2d = sum(t.numel() * t.element_size() for t in (host_x[0], host_dy[0]))
-        d2h = sum(t.numel() * t.element_size() for t in (host_y, host_dx))
+        d2h = sum(t.numel() * t.element_size() for t in (host_y[0], host_dx[0]))
         line = {"metric": LAYER_METRIC, "value": world * layer_flops(T) / (ms_step * 1e-3) / 1e12, "unit": LAYER_UNIT,
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",

@@ -138,8 +138,9 @@ int kv_kan_fwd_noalloc(const kv_kan_desc_t* d, const uint64_t* ptr_table, const 
                        const float* rstd, const float* residual, const float* pos, float* Y, void* stream);
 
 /* Bytes of the tensor-core operand images of kv_kan_pack (KV_FLAG_BF16_TC path).  Returns
- * KV_ERR_UNSUPPORTED when the layer cannot run on the tensor-core kernels (M > 24);
- * *wtiles_t_bytes == 0 / *dy_image_bytes == 0 mean the gradients run on the fp32 kernels for this layer. */
+ * KV_ERR_UNSUPPORTED when the layer cannot run on the tensor-core kernels (M > KV_MAX_M);
+ * *wtiles_t_bytes == 0 (input gradient: more than 32 basis functions) / *dy_image_bytes == 0 mean that gradient runs on
+ * the fp32 kernels for this layer. */
 int kv_kan_tc_bytes(const kv_kan_desc_t* d, size_t* wtiles_bytes, size_t* wtiles_t_bytes,
                     size_t* dy_image_bytes);
 
