@@ -1758,6 +1758,9 @@ struct BwdGeom {
   // (256 + W1): few wide instructions instead of n_sub narrow ones (a 144-column instruction runs at ~60 % of the
   // rate of a 256-column one, scripts/mma_pace.cu)
   int W1;        // columns of the second MMA, 0 = one MMA
+  // More than 32 basis functions (16 * M > 512 TMEM columns): the generic input-gradient kernel is launched nsplit
+  // times, each launch on Ms consecutive bases with its own transposed weight image, the later ones adding to dX
+  int Ms, nsplit;
   __host__ __device__ int tile_cols() const { return n_sub * SW; }
   __host__ __device__ int W0() const { return n_sub * SW > 256 ? 256 : n_sub * SW; }
 };
@@ -1765,9 +1768,11 @@ struct BwdGeom {
 __host__ __device__ inline BwdGeom make_bwd_geom(const kv_kan_desc_t& d) {
   BwdGeom b;
   b.n_chunks = (d.in_features + KU - 1) / KU;
-  b.SW = KU * d.M;
+  b.nsplit = (d.M + MAX_M_TC_DX - 1) / MAX_M_TC_DX;
+  b.Ms = (d.M + b.nsplit - 1) / b.nsplit;
+  b.SW = KU * b.Ms;
   b.n_sub = 512 / b.SW;
-  if (b.n_sub < 1) b.n_sub = 1;  // M > 32: no tensor-core input gradient (tc_bwd_ok); the dY image geometry still applies
+  if (b.n_sub < 1) b.n_sub = 1;
   if (b.n_sub > b.n_chunks) b.n_sub = b.n_chunks;
   if (b.n_sub * b.SW * 64 > BI_B_STAGE) b.n_sub = BI_B_STAGE / (b.SW * 64);
   if (b.n_sub < 1) b.n_sub = 1;
@@ -1822,7 +1827,7 @@ __global__ void dy_image_kernel(const kv_kan_desc_t d, const float* __restrict__
 __global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, const uint64_t* __restrict__ tbl,
                                  __nv_bfloat16* __restrict__ wtt, BwdGeom b, int layout) {
   const int xs = d.n_groups == d0.n_groups ? 1 : d0.x_share;
-  const size_t total64 = (size_t)d.n_groups * b.n_tiles * b.n_stages * b.tile_cols();  // core matrices
+  const size_t total64 = (size_t)b.nsplit * d.n_groups * b.n_tiles * b.n_stages * b.tile_cols();  // core matrices
   for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total64;
        idx += (size_t)gridDim.x * blockDim.x) {
     size_t r = idx;
@@ -1833,19 +1838,21 @@ __global__ void tc_pack_t_kernel(const kv_kan_desc_t d, const kv_kan_desc_t d0, 
     const int rank = r % 2; r /= 2;
     const int st = r % b.n_stages; r /= b.n_stages;
     const int tile = r % b.n_tiles; r /= b.n_tiles;
-    const int g = (int)r;
+    const int g = (int)(r % d.n_groups);
+    const int sp = (int)(r / d.n_groups);   // basis split (M > 32): bases [sp * Ms, (sp + 1) * Ms)
     int n8, o8, C;   // C = first tile column of this core matrix
     if (qi < W0 / 2) { n8 = qi % (W0 / 16); o8 = qi / (W0 / 16); C = rank * (W0 / 2) + n8 * 8; }
     else { qi -= W0 / 2; n8 = qi % (W1 / 16); o8 = qi / (W1 / 16); C = W0 + rank * (W1 / 2) + n8 * 8; }
     const int j = C / b.SW, cc = C - j * b.SW;
     const int c = tile * b.n_sub + j;
-    const int q = cc / 16, h = (cc / 8) & 1;
+    const int q = sp * b.Ms + cc / 16, h = (cc / 8) & 1;
+    const bool q_ok = b.nsplit == 1 || q < d.M;
     uint32_t w[8][4];  // [column r8][4 output pairs]
     float v[8][8];     // [output oe][column r8]
 #pragma unroll
     for (int oe = 0; oe < 8; ++oe) {
       const int o = st * 64 + o8 * 8 + oe;
-      if (o < d.out_features && c < b.n_chunks) {
+      if (o < d.out_features && c < b.n_chunks && q_ok) {
         load_w8(d0, tbl, g * xs + o / d0.out_features, o % d0.out_features, layout, c, q, h, v[oe]);
       } else {
 #pragma unroll
@@ -1877,6 +1884,7 @@ struct BwdInParams {
   float* dXn;
   float* dfparams;
   int tpc;  // effkan8 kernel: column tiles per CTA pair
+  int m_lo, m_cnt, accum;   // generic kernel: this launch's bases [m_lo, m_lo + m_cnt); accum: add to dX / dXn
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) effkan8_bwd_input_kernel(const __grid_constant__ BwdInParams p) {
@@ -2261,12 +2269,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
       float dx[8], dxn_acc[8];
 #pragma unroll
       for (int f = 0; f < 8; ++f) dx[f] = dxn_acc[f] = 0.0f;
-      const int n_pass = M > 24 ? 2 : 1, Mh = (M + n_pass - 1) / n_pass;
+      // this launch's bases [m_lo, m_lo + Mloc) sit at TMEM columns (m - m_lo) * 16 + f of the chunk
+      const int m_lo = p.m_lo, Mloc = p.m_cnt;
+      const int n_pass = Mloc > 24 ? 2 : 1, Mh = (Mloc + n_pass - 1) / n_pass;
       for (int pass = 0; pass < n_pass; ++pass) {
-      const int mlo = pass * Mh, mhi = min(M, mlo + Mh);
+      const int mlo = m_lo + pass * Mh, mhi = min(m_lo + Mloc, mlo + Mh);
       for (int m = mlo; m < mhi; ++m) {
         uint32_t r8[8];
-        ptx::tmem_ld8(trow + j * SW + m * 16 + half * 8, r8);
+        ptx::tmem_ld8(trow + j * SW + (m - m_lo) * 16 + half * 8, r8);
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int f = 0; f < 8; ++f) scratch[(m - mlo) * MS + f * 256 + etid] = __uint_as_float(r8[f]);
@@ -2319,7 +2329,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
 #pragma unroll
         for (int f = 0; f < 8; ++f) {
           const int i = cch * KU + half * 8 + f;
-          if (row_ok && i < in) p.dXn[(size_t)te * ((size_t)d.n_groups * in) + (size_t)g * in + i] = dxn_acc[f];
+          if (row_ok && i < in) {
+            float* dst = &p.dXn[(size_t)te * ((size_t)d.n_groups * in) + (size_t)g * in + i];
+            *dst = p.accum ? *dst + dxn_acc[f] : dxn_acc[f];
+          }
         }
       }
       if (row_ok && shared_slice) {
@@ -2329,7 +2342,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) kan_tc_
           if (i0 + f < in) atomicAdd(dxrow + i0 + f, dx[f]);
       } else if (row_ok) {
         const int i0 = cch * KU + half * 8;
-        if (vec && i0 + 8 <= in) {
+        if (p.accum) {     // a later basis split: this thread owns the element, the launches are stream-ordered
+#pragma unroll
+          for (int f = 0; f < 8; ++f)
+            if (i0 + f < in) dxrow[i0 + f] += dx[f];
+        } else if (vec && i0 + 8 <= in) {
           *reinterpret_cast<float4*>(dxrow + i0) = make_float4(dx[0], dx[1], dx[2], dx[3]);
           *reinterpret_cast<float4*>(dxrow + i0 + 4) = make_float4(dx[4], dx[5], dx[6], dx[7]);
         } else {
@@ -2868,7 +2885,7 @@ static bool tc_bwd_generic(const kv_kan_desc_t& d) {
 }
 // input-gradient kernel: one chunk (16 features x M bases) is one MMA of N = 16 M <= 256 columns
 static bool tc_bwd_ok(const kv_kan_desc_t& d) {
-  return tc_bwd_effkan8(d) || tc_bwd_linear(d) || (tc_bwd_generic(d) && d.M <= tc::MAX_M_TC_DX);
+  return tc_bwd_effkan8(d) || tc_bwd_linear(d) || tc_bwd_generic(d);   // M > 32: basis splits (BwdGeom::nsplit)
 }
 static bool tc_bwd_w_ok(const kv_kan_desc_t& d) { return tc_bwd_effkan8(d) || tc_bwd_linear(d) || tc_bwd_generic(d); }
 // Linear: dX = dY . W runs as the forward kernel of the transposed layer
@@ -2886,7 +2903,7 @@ size_t tc_wtiles_t_bytes(const kv_kan_desc_t& d) {
   if (!tc_bwd_ok(d)) return 0;
   if (d.family == KV_LINEAR) return tc_wtiles_bytes(linear_transposed(d));
   const tc::BwdGeom b = tc::make_bwd_geom(d);
-  return (size_t)d.n_groups * b.n_tiles * b.n_stages * 2 * b.n_sub * b.SW * 64;
+  return (size_t)b.nsplit * d.n_groups * b.n_tiles * b.n_stages * 2 * b.n_sub * b.SW * 64;
 }
 void tc_dy_image_geom(const kv_kan_desc_t& d, int* t8, int* o8) {
   const tc::BwdGeom b = tc::make_bwd_geom(d);
@@ -3018,6 +3035,9 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
   p.dXn = dXn;
   p.dfparams = dfparams;
   p.b = tc::make_bwd_geom(d);
+  p.m_lo = 0;
+  p.m_cnt = d.M;
+  p.accum = 0;
   {
     const int rc = encode_dy_image_map(&p.tm_dy, dy_image, d.n_groups, p.b.T8, p.b.O8, 8, 16);
     if (rc != KV_OK) return rc;
@@ -3030,14 +3050,25 @@ int tc_bwd_input(const kv_kan_desc_t& d, const float* X, const float* dY, const 
       KV_CUDA(cudaMemset2DAsync(dX, (size_t)d.ldx * sizeof(float), 0,
                                 (size_t)(d.n_groups / d.x_share) * d.in_features * sizeof(float), (size_t)d.T, st),
               "tc_bwd_input zero dX");
-    switch (d.family) {
-      case KV_EFFKAN: return launch_bwd_input_generic<KV_EFFKAN>(p, grid, st);
-      case KV_CHEBY: return launch_bwd_input_generic<KV_CHEBY>(p, grid, st);
-      case KV_FASTKAN: return launch_bwd_input_generic<KV_FASTKAN>(p, grid, st);
-      case KV_SINE: return launch_bwd_input_generic<KV_SINE>(p, grid, st);
-      case KV_FOURIER: return launch_bwd_input_generic<KV_FOURIER>(p, grid, st);
+    // one launch per basis split (M <= 32: one), each with its own transposed weight image
+    const size_t split_elems = tc_wtiles_t_bytes(d) / 2 / p.b.nsplit;
+    const __nv_bfloat16* wtt0 = p.wtt;
+    for (int sp = 0; sp < p.b.nsplit; ++sp) {
+      p.wtt = wtt0 + (size_t)sp * split_elems;
+      p.m_lo = sp * p.b.Ms;
+      p.m_cnt = d.M - p.m_lo < p.b.Ms ? d.M - p.m_lo : p.b.Ms;
+      p.accum = sp > 0 ? 1 : 0;
+      int rc = KV_ERR_BAD_FAMILY;
+      switch (d.family) {
+        case KV_EFFKAN: rc = launch_bwd_input_generic<KV_EFFKAN>(p, grid, st); break;
+        case KV_CHEBY: rc = launch_bwd_input_generic<KV_CHEBY>(p, grid, st); break;
+        case KV_FASTKAN: rc = launch_bwd_input_generic<KV_FASTKAN>(p, grid, st); break;
+        case KV_SINE: rc = launch_bwd_input_generic<KV_SINE>(p, grid, st); break;
+        case KV_FOURIER: rc = launch_bwd_input_generic<KV_FOURIER>(p, grid, st); break;
+      }
+      if (rc != KV_OK) return rc;
     }
-    return KV_ERR_BAD_FAMILY;
+    return KV_OK;
   }
   // column tiles per CTA pair: as many (up to 8) as still leave ~8 waves of CTA pairs
   p.tpc = 1;

@@ -139,13 +139,11 @@ def test_tensor_core_coverage_table():
     for name, spec in dense.items():
         rc, fwd, bwd_in, dyimg = sizes(spec, flags=L.KV_FLAG_UNIFORM_GRID if name == "effkan" else 0)
         assert rc == 0 and fwd > 0 and bwd_in > 0 and dyimg > 0, name
-    # up to 32 basis functions every kernel runs on the tensor cores (two accumulator passes in the input gradient)
-    for G in (20, 28):
+    # any number of basis functions (<= KV_MAX_M) runs on the tensor cores: the forward and the weight gradient walk the
+    # bases in parts, the input gradient takes two accumulator passes above 24 and two launches (basis splits) above 32
+    for G in (20, 28, 40, 64):
         rc, fwd, bwd_in, dyimg = sizes(KanSpec(L.KV_SINE, 192, 192, grid_size=G))
         assert rc == 0 and fwd > 0 and bwd_in > 0 and dyimg > 0, G
-    # more than 32: forward and weight gradient walk the bases in parts, the input gradient stays on the exact kernel
-    rc, fwd, bwd_in, dyimg = sizes(KanSpec(L.KV_SINE, 192, 192, grid_size=40))
-    assert rc == 0 and fwd > 0 and bwd_in == 0 and dyimg > 0
     # per-head q/k/v maps: merged (effkan on a uniform grid) or served as groups sharing a slice (fastkan)
     for spec, fl in ((KanSpec(L.KV_EFFKAN, 64, 64, n_groups=36, x_share=3, grid_size=5, spline_order=3),
                       L.KV_FLAG_UNIFORM_GRID),
