@@ -623,55 +623,85 @@ __device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const f
 }
 
 // NPW = producer / epilogue warps: 8 (a thread owns 8 features of a chunk) or 16 (4 features; effkan only)
-// nn.Linear A producer of one tile (both forward kernels; 256 producer threads: row r, k-half wg): the operand is the
-// bf16 image of X itself.  A ring slot carries Mp consecutive 16-feature chunks (one 16-byte store per chunk and
-// thread); the loads of the next slot are in flight while the current one is converted.  mrow != nullptr: the ReLU
-// gate of a transposed layer (input gradient of Linear + ReLU), applied while converting.
-__device__ __forceinline__ void linear_produce_tile(const Geom& gm, const float* __restrict__ xrow, const float* __restrict__ mrow,
-                                                    bool row_ok, bool vec, bool mvec, int in, int wg, uint8_t* sA_row,
-                                                    uint32_t bar0, int NCH, int lane, int& slot_i) {
-  constexpr int LC = 6;   // >= Geom::Mp of a Linear layer
+// nn.Linear A producer of one tile (both forward kernels, 256 producer threads = 8 warps): the operand is the bf16
+// image of X itself.  A ring slot carries Mp (<= 6) consecutive 16-feature chunks of the tile's 128 rows = 16 row
+// groups x Mp chunks of (8 rows x 16 features); a warp instruction moves one such block: lane = (row of the group,
+// float4 of the chunk), i.e. 8 rows x 64 contiguous bytes on the load side and the 8-row core matrices of the operand
+// layout on the store side (one 8-byte store per lane, two shared-memory wavefronts).  The first version gave each
+// thread a row (32 cache lines, 16 bytes each, per warp instruction): clock stamps showed the producers at 35 k cycles
+// per 256 x 256 x 768 tile (7 k of MMA work) and the epilogue's stores queueing behind them in the load / store unit.
+// The next slot's loads are in flight while the current one is converted.  mtile != nullptr: the ReLU gate of a
+// transposed layer (input gradient of Linear + ReLU), applied while converting.  xtile / mtile point at (row t0 of
+// the tile, first feature of the slice).
+__device__ __forceinline__ void linear_produce_tile(const Geom& gm, const float* __restrict__ xtile,
+                                                    const float* __restrict__ mtile, int rows_valid, int ldx, bool vec,
+                                                    bool mvec, int in, uint8_t* sA, uint32_t bar0, int NCH, int ptid,
+                                                    int lane, int& slot_i) {
+  constexpr int LC = 6;          // >= Geom::Mp of a Linear layer
+  constexpr int NV = 2 * LC;     // blocks per warp and slot: 16 row groups x 6 chunks / 8 warps
   const int Mp = gm.Mp, n_chunks = gm.n_chunks;
-  float cur[LC][8];
-  auto load_part = [&](int c0, float (&v)[LC][8]) {
+  const int warp = ptid >> 5;
+  const int rl = lane >> 2, f4 = lane & 3;               // row of the 8-row group, float4 of the 16-feature chunk
+  // block j of this warp: chunk u = j % LC of the slot, row group 2 * warp + j / LC
+  auto load_slot = [&](int c0, float4 (&v)[NV]) {
 #pragma unroll
-    for (int u = 0; u < LC; ++u) {
-      if (u < Mp && c0 + u < n_chunks) {
-        load_x8(xrow, (c0 + u) * KU + wg * 8, in, row_ok, vec, v[u]);
-        if (mrow != nullptr) {
-          float mk[8];
-          load_x8(mrow, (c0 + u) * KU + wg * 8, in, row_ok, mvec, mk);
-#pragma unroll
-          for (int q = 0; q < 8; ++q) v[u][q] = mk[q] > 0.0f ? v[u][q] : 0.0f;
-        }
+    for (int j = 0; j < NV; ++j) {
+      const int u = j % LC, row = (2 * warp + j / LC) * 8 + rl;
+      const int i0 = (c0 + u) * KU + f4 * 4;               // first feature of the float4
+      v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (u >= Mp || c0 + u >= n_chunks || row >= rows_valid || i0 >= in) continue;
+      const float* src = xtile + (size_t)row * ldx + i0;
+      if (vec && i0 + 4 <= in) {
+        v[j] = __ldg(reinterpret_cast<const float4*>(src));
       } else {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) v[u][q] = 0.0f;
+        v[j].x = __ldg(src);
+        if (i0 + 1 < in) v[j].y = __ldg(src + 1);
+        if (i0 + 2 < in) v[j].z = __ldg(src + 2);
+        if (i0 + 3 < in) v[j].w = __ldg(src + 3);
+      }
+      if (mtile != nullptr) {
+        const float* ms = mtile + (size_t)row * ldx + i0;
+        float4 mk = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (mvec && i0 + 4 <= in) {
+          mk = __ldg(reinterpret_cast<const float4*>(ms));
+        } else {
+          mk.x = __ldg(ms);
+          if (i0 + 1 < in) mk.y = __ldg(ms + 1);
+          if (i0 + 2 < in) mk.z = __ldg(ms + 2);
+          if (i0 + 3 < in) mk.w = __ldg(ms + 3);
+        }
+        v[j].x = mk.x > 0.0f ? v[j].x : 0.0f;
+        v[j].y = mk.y > 0.0f ? v[j].y : 0.0f;
+        v[j].z = mk.z > 0.0f ? v[j].z : 0.0f;
+        v[j].w = mk.w > 0.0f ? v[j].w : 0.0f;
       }
     }
   };
-  load_part(0, cur);
+  float4 cur[NV];
+  load_slot(0, cur);
+  // byte offset of this lane inside a unit: k-half f4 / 2, row group, row, half of the 16-byte row
+  const int lane_off = (f4 >> 1) * 2048 + rl * 16 + (f4 & 1) * 8;
   for (int pt = 0; pt < gm.npart; ++pt, ++slot_i) {
-    float nxt[LC][8];
-    load_part((pt + 1) * Mp, nxt);    // beyond the last part: zeros, no loads
+    float4 nxt[NV];
+    if (pt + 1 < gm.npart) load_slot((pt + 1) * Mp, nxt);
     const int sc = slot_i % NCH;
     const int Mt = min(Mp, n_chunks - pt * Mp);
     ptx::mbar_wait(bar0 + 8u * (NCH_MAX + sc), ((slot_i / NCH) & 1) ^ 1);   // emptyA(sc)
-    uint8_t* base = sA_row + sc * Mp * A_UNIT_BYTES + wg * 2048;
+    uint8_t* base = sA + sc * Mp * A_UNIT_BYTES + lane_off;
 #pragma unroll
-    for (int u = 0; u < LC; ++u) {
+    for (int j = 0; j < NV; ++j) {
+      const int u = j % LC, rg = 2 * warp + j / LC;
       if (u < Mt)
-        *reinterpret_cast<uint4*>(base + u * A_UNIT_BYTES) =
-            make_uint4(pack_bf16(cur[u][0], cur[u][1]), pack_bf16(cur[u][2], cur[u][3]), pack_bf16(cur[u][4], cur[u][5]),
-                       pack_bf16(cur[u][6], cur[u][7]));
+        *reinterpret_cast<uint2*>(base + u * A_UNIT_BYTES + rg * 128) =
+            make_uint2(pack_bf16(cur[j].x, cur[j].y), pack_bf16(cur[j].z, cur[j].w));
     }
     ptx::fence_proxy_async_smem();
     __syncwarp();
     if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(bar0 + 8u * sc, 0));  // the leader's fullA(sc)
+    if (pt + 1 < gm.npart) {
 #pragma unroll
-    for (int u = 0; u < LC; ++u)
-#pragma unroll
-      for (int q = 0; q < 8; ++q) cur[u][q] = nxt[u][q];
+      for (int j = 0; j < NV; ++j) cur[j] = nxt[j];
+    }
   }
 }
 
@@ -967,7 +997,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
     if constexpr (F == KV_LINEAR) {
       static_assert(F != KV_LINEAR || FPT == 8, "the Linear producers own 8 features per thread");
       int slot_i = 0;
-      linear_produce_tile(gm, xrow, mrow, row_ok, vec, mvec, in, wg, sA + row_off, bar0, NCH, lane, slot_i);
+      const size_t toff = (size_t)t0 * d.ldx + xoff;   // (row t0 of the tile, first feature of the slice)
+      linear_produce_tile(gm, p.X + toff, p.in_mask != nullptr ? p.in_mask + toff : nullptr, min(BM, d.T - t0), d.ldx, vec,
+                          mvec, in, sA, bar0, NCH, ptid, lane, slot_i);
     } else {
     // two copies of the chunk loop (default-grid closed form / everything else): the registers of the other-grid
     // route (EffkanOctet: 40 values per thread) must not push spills into the default route
@@ -1449,9 +1481,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
       for (int it = 0; it < n_my; ++it) {
         const TileX x = tile_x(it);
         // Linear as the input gradient of a ReLU layer: dY is gated by the layer's own forward output
-        const float* mrow = p.in_mask != nullptr ? p.in_mask + (x.xrow - p.X) : nullptr;
         const bool mvec = x.vec && ((reinterpret_cast<uintptr_t>(p.in_mask) & 15) == 0);
-        linear_produce_tile(gm, x.xrow, mrow, x.row_ok, x.vec, mvec, in, wg, sA + row_off, bar0, NCH, lane, slot_i);
+        const int t0t = x.t - r;                        // first row of this CTA's 128-row tile
+        const size_t toff = (size_t)t0t * d.ldx + (size_t)x.slice * in;
+        linear_produce_tile(gm, p.X + toff, p.in_mask != nullptr ? p.in_mask + toff : nullptr, min(BM, d.T - t0t), d.ldx,
+                            x.vec, mvec, in, sA, bar0, NCH, ptid, lane, slot_i);
       }
     } else {
       // per-group prologue constants: reloaded only when the group changes
