@@ -1234,17 +1234,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
 //     and tile from L2 for a 3 500-cycle main loop;
 //   * the producers fetch the first chunk of the next tile's X while they evaluate the last chunk of the current one,
 //     and keep the per-group prologue constants while the group does not change.
-// Warps: 0 loader, 1 MMA issuer (leader) / B relay (peer), 2-9 basis producers, 10-13 epilogue.
+// Warps: 0 loader, 1 MMA issuer (leader) / B relay (peer), 2-9 basis producers, 10-17 epilogue (nn.Linear: 10-13).
 // =========================================================================================
 constexpr int P_NPW = 8;                       // producer warps
-constexpr int P_NEW = 4;                       // epilogue warps (one per TMEM lane quadrant)
-constexpr int P_THREADS = 32 * (2 + P_NPW + P_NEW);
+// epilogue warps: two per TMEM lane quadrant, alternating column blocks (q/k/v forward 0.52 -> 0.45 ms against one per
+// quadrant: a warp's stores are latency-bound).  nn.Linear keeps one per quadrant: its producers hold two slots of X in
+// registers and spill at the 96 registers that 576 threads leave (356 -> 217 TFLOP/s, measured).
+__host__ __device__ constexpr int p_new(int F) { return F == KV_LINEAR ? 4 : 8; }
+__host__ __device__ constexpr int p_threads(int F) { return 32 * (2 + P_NPW + p_new(F)); }
 constexpr int P_B_RING = 112 * 1024;
-constexpr int P_STG_BYTES = P_NEW * 32 * 36 * 4;   // epilogue staging: 32 rows x 36 floats per warp
+constexpr int P_STG_BYTES = 8 * 32 * 36 * 4;   // epilogue staging: 32 rows x 36 floats per warp, up to 8 warps
 constexpr int P_SMEM = A_RING_BYTES + P_B_RING + P_STG_BYTES + BAR_BYTES;
 
 template <int F>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc_fwd_persistent_kernel(const FwdParams p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(p_threads(F), 1) kan_tc_fwd_persistent_kernel(const FwdParams p) {
+  constexpr int P_NEW = p_new(F);
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
   uint8_t* sB = smem + A_RING_BYTES;
@@ -1589,7 +1593,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
           return reinterpret_cast<uint4*>(hb + part * part_elems + ((size_t)(nn >> 3) * (DHP >> 3) + (dd >> 3)) * 64 + (nn & 7) * 8);
         };
         const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
-        for (int cb = 0; cb * 32 < BN; ++cb) {
+        for (int cb = ew >> 2; cb * 32 < BN; cb += P_NEW / 4) {
           uint32_t rr[32];
           ptx::tmem_ld32(trow + cb * 32, rr);
           ptx::tmem_ld_wait();
@@ -1637,7 +1641,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1) kan_tc
                            (!p.residual || (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0) &&
                            (!p.pos || (reinterpret_cast<uintptr_t>(p.pos) & 15) == 0) &&
                            (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
-        for (int cb = 0; cb * 32 < BN; ++cb) {
+        for (int cb = ew >> 2; cb * 32 < BN; cb += P_NEW / 4) {
           uint32_t rr[32];
           ptx::tmem_ld32(trow + cb * 32, rr);
           ptx::tmem_ld_wait();
@@ -1743,7 +1747,7 @@ static int launch_fwd_persistent(const FwdParams& p, cudaStream_t st) {
   }
   const int pairs = sms / 2;
   dim3 grid(2, (unsigned)(tiles < pairs ? tiles : pairs), 1);  // x = CTA pair; each pair walks tiles y, y + gridDim.y, ...
-  kan_tc_fwd_persistent_kernel<F><<<grid, P_THREADS, P_SMEM, st>>>(p);
+  kan_tc_fwd_persistent_kernel<F><<<grid, p_threads(F), P_SMEM, st>>>(p);
   KV_CHECK_LAUNCH("kan_tc_fwd_persistent_kernel");
   return KV_OK;
 }
