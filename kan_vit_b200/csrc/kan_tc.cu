@@ -630,7 +630,8 @@ __device__ __forceinline__ void basis_major_chunk(uint8_t* base, int wg, const f
 // layout on the store side (one 8-byte store per lane, two shared-memory wavefronts).  The first version gave each
 // thread a row (32 cache lines, 16 bytes each, per warp instruction): clock stamps showed the producers at 35 k cycles
 // per 256 x 256 x 768 tile (7 k of MMA work) and the epilogue's stores queueing behind them in the load / store unit.
-// The next slot's loads are in flight while the current one is converted.  mtile != nullptr: the ReLU gate of a
+// (Loads are not prefetched across slots: three ring slots and eight warps cover the latency, and the registers go to
+// the eight epilogue warps of the persistent kernel.)  mtile != nullptr: the ReLU gate of a
 // transposed layer (input gradient of Linear + ReLU), applied while converting.  xtile / mtile point at (row t0 of
 // the tile, first feature of the slice).
 __device__ __forceinline__ void linear_produce_tile(const Geom& gm, const float* __restrict__ xtile,
@@ -678,12 +679,10 @@ __device__ __forceinline__ void linear_produce_tile(const Geom& gm, const float*
     }
   };
   float4 cur[NV];
-  load_slot(0, cur);
   // byte offset of this lane inside a unit: k-half f4 / 2, row group, row, half of the 16-byte row
   const int lane_off = (f4 >> 1) * 2048 + rl * 16 + (f4 & 1) * 8;
   for (int pt = 0; pt < gm.npart; ++pt, ++slot_i) {
-    float4 nxt[NV];
-    if (pt + 1 < gm.npart) load_slot((pt + 1) * Mp, nxt);
+    load_slot(pt * Mp, cur);
     const int sc = slot_i % NCH;
     const int Mt = min(Mp, n_chunks - pt * Mp);
     ptx::mbar_wait(bar0 + 8u * (NCH_MAX + sc), ((slot_i / NCH) & 1) ^ 1);   // emptyA(sc)
@@ -698,10 +697,6 @@ __device__ __forceinline__ void linear_produce_tile(const Geom& gm, const float*
     ptx::fence_proxy_async_smem();
     __syncwarp();
     if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(bar0 + 8u * sc, 0));  // the leader's fullA(sc)
-    if (pt + 1 < gm.npart) {
-#pragma unroll
-      for (int j = 0; j < NV; ++j) cur[j] = nxt[j];
-    }
   }
 }
 
@@ -1234,13 +1229,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + NPW), 1) k
 //     and tile from L2 for a 3 500-cycle main loop;
 //   * the producers fetch the first chunk of the next tile's X while they evaluate the last chunk of the current one,
 //     and keep the per-group prologue constants while the group does not change.
-// Warps: 0 loader, 1 MMA issuer (leader) / B relay (peer), 2-9 basis producers, 10-17 epilogue (nn.Linear: 10-13).
+// Warps: 0 loader, 1 MMA issuer (leader) / B relay (peer), 2-9 basis producers, 10-17 epilogue.
 // =========================================================================================
 constexpr int P_NPW = 8;                       // producer warps
-// epilogue warps: two per TMEM lane quadrant, alternating column blocks (q/k/v forward 0.52 -> 0.45 ms against one per
-// quadrant: a warp's stores are latency-bound).  nn.Linear keeps one per quadrant: its producers hold two slots of X in
-// registers and spill at the 96 registers that 576 threads leave (356 -> 217 TFLOP/s, measured).
-__host__ __device__ constexpr int p_new(int F) { return F == KV_LINEAR ? 4 : 8; }
+// epilogue warps: two per TMEM lane quadrant, alternating column blocks (q/k/v forward 0.52 -> 0.44 ms against one per
+// quadrant: a warp's stores are latency-bound).  576 threads leave 96 registers per thread; the nn.Linear producers
+// therefore hold ONE slot of X in registers (with the next slot prefetched as well they spilled: 356 -> 217 TFLOP/s;
+// single-buffered with eight epilogue warps: 385).
+__host__ __device__ constexpr int p_new(int F) { return 8; }
 __host__ __device__ constexpr int p_threads(int F) { return 32 * (2 + P_NPW + p_new(F)); }
 constexpr int P_B_RING = 112 * 1024;
 constexpr int P_STG_BYTES = 8 * 32 * 36 * 4;   // epilogue staging: 32 rows x 36 floats per warp, up to 8 warps
